@@ -1,0 +1,187 @@
+"""Generate golden fixtures by running the LIVE reference (bennevans/mjrl).
+
+Run in the build container only (needs /root/reference):
+    python tests/golden/make_golden.py
+It imports the reference's own modules (with empty `gym` / `matplotlib` stubs,
+because mjrl.algos imports its samplers and logger at module level), feeds them
+synthetic batches from `mjrl_b200.utils.synthetic`, and stores inputs and the
+reference's outputs in `tests/golden/*.npz`.  Nothing here runs on the GPU box.
+
+Versions recorded in each fixture: numpy / torch of this container.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+REF = os.environ.get("MJRL_REFERENCE", "/root/reference")
+
+
+def import_reference():
+    for name in ("gym", "matplotlib", "matplotlib.pyplot"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    sys.modules["matplotlib"].use = lambda *a, **k: None
+    sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+    sys.path.insert(0, REF)
+    saved = {k: os.environ.get(k) for k in ("CUDA_VISIBLE_DEVICES", "CUDA_DEVICE_ORDER")}
+    import mjrl.utils.process_samples as ps
+    import mjrl.utils.cg_solve as cg
+    import mjrl.baselines.linear_baseline as lb
+    import mjrl.baselines.mlp_baseline as mb   # sets CUDA_VISIBLE_DEVICES at import (F10)
+    import mjrl.policies.gaussian_mlp as gm
+    import mjrl.policies.gaussian_linear as gl
+    import mjrl.algos.npg_cg as npg
+    import mjrl.algos.trpo as trpo
+    import mjrl.algos.dapg as dapg
+    import mjrl.algos.batch_reinforce as br
+    from mjrl.utils.gym_env import EnvSpec
+    for k, v in saved.items():
+        if v is None:
+            os.environ.pop(k, None)
+        else:
+            os.environ[k] = v
+    return types.SimpleNamespace(ps=ps, cg=cg, lb=lb, mb=mb, gm=gm, gl=gl, npg=npg,
+                                 trpo=trpo, dapg=dapg, br=br, EnvSpec=EnvSpec)
+
+
+def build_ref_policy(R, n, m, hidden, seed, flat=None, transforms=None, min_log_std=-3):
+    spec = R.EnvSpec(n, m, 1000, 1)
+    if hidden:
+        pol = R.gm.MLP(spec, hidden_sizes=tuple(hidden), seed=seed, min_log_std=min_log_std)
+    else:
+        pol = R.gl.LinearPolicy(spec, seed=seed, min_log_std=min_log_std)
+    init = pol.get_param_values()
+    if transforms is not None:
+        pol.model.set_transformations(**transforms)
+        pol.old_model.set_transformations(**transforms)
+    if flat is not None:
+        pol.set_param_values(flat.copy(), set_new=True, set_old=True)
+    return pol, init
+
+
+def run_case(R, name, n, m, hidden, horizon, N, seed, mid, algo="npg"):
+    import torch
+    from mjrl_b200.utils import synthetic as syn
+    spec = R.EnvSpec(n, m, horizon, 1)
+    pol, init = build_ref_policy(R, n, m, hidden, seed=123)
+    flat, tr = init, None
+    if mid:
+        flat, tr = syn.mid_training_variant(init, n, m, seed)
+        pol, _ = build_ref_policy(R, n, m, hidden, seed=123, flat=flat, transforms=tr)
+    gamma, lam = 0.995, 0.97
+    out = dict(n=n, m=m, hidden=np.asarray(hidden, dtype=np.int64), horizon=horizon, N=N,
+               seed=seed, gamma=gamma, gae_lambda=lam, init_params=init, params=flat,
+               numpy_version=np.__version__, torch_version=torch.__version__)
+    if tr is not None:
+        out.update({"tr_" + k: v for k, v in tr.items()})
+
+    # two batches: batch 0 warms the baseline (F8), batch 1 is the measured update
+    b0 = syn.make_flat_batch(N, n, m, horizon, seed, flat, hidden, tr)
+    b1 = syn.make_flat_batch(N, n, m, horizon, seed + 1, flat, hidden, tr)
+    for tag, b in (("b0_", b0), ("b1_", b1)):
+        out.update({tag + k: v for k, v in b.items()})
+    p0, p1 = syn.flat_to_paths(b0), syn.flat_to_paths(b1)
+
+    base = R.lb.LinearBaseline(spec)
+    R.ps.compute_returns(p0, gamma)
+    out["b0_returns"] = np.concatenate([p["returns"] for p in p0])
+    # iteration 0: predict() returns zeros (F8)
+    R.ps.compute_advantages(p0, base, gamma, lam)
+    out["b0_adv_zero_baseline"] = np.concatenate([p["advantages"] for p in p0])
+    eb, ea = base.fit(p0, return_errors=True)
+    out["fit0_coeffs"] = base._coeffs.copy()
+    out["fit0_errors"] = np.asarray([eb, ea])
+
+    R.ps.compute_returns(p1, gamma)
+    R.ps.compute_advantages(p1, base, gamma, lam)
+    out["b1_returns"] = np.concatenate([p["returns"] for p in p1])
+    out["b1_baseline"] = np.concatenate([p["baseline"] for p in p1])
+    out["b1_adv"] = np.concatenate([p["advantages"] for p in p1])
+    # plain (non-GAE) mode and the normalize flag
+    import copy
+    pp = copy.deepcopy(p1)
+    R.ps.compute_advantages(pp, base, gamma, None, normalize=True)
+    out["b1_adv_plain_norm"] = np.concatenate([p["advantages"] for p in pp])
+
+    obs = np.concatenate([p["observations"] for p in p1])
+    act = np.concatenate([p["actions"] for p in p1])
+    adv = np.concatenate([p["advantages"] for p in p1])
+    adv = (adv - np.mean(adv)) / (np.std(adv) + 1e-6)
+    out["b1_adv_white"] = adv
+
+    agent = R.npg.NPG(None, pol, base, normalized_step_size=0.01,
+                      FIM_invert_args={"iters": 10, "damping": 1e-4})
+    out["LL"] = pol.log_likelihood(obs, act)
+    out["mean"] = pol.mean_LL(obs, act)[0].data.numpy()
+    out["surr_before"] = agent.CPI_surrogate(obs, act, adv).data.numpy().ravel()[0]
+    g = agent.flat_vpg(obs, act, adv)
+    out["vpg_grad"] = g
+    out["hvp_of_grad"] = agent.HVP(obs, act, g, 1e-4)
+    out["hvp_of_grad_nodamp"] = agent.HVP(obs, act, g, 0.0)
+    hv = agent.build_Hvp_eval([obs, act], regu_coef=1e-4)
+    for k in (1, 2, 3, 5, 10):
+        out["cg_k%d" % k] = R.cg.cg_solve(hv, g, x_0=g.copy(), cg_iters=k)
+
+    # perturbed "new" parameters: exercises LR != 1 and KL > 0 evaluation
+    rng = np.random.default_rng(seed + 17)
+    pert = flat + np.float32(0.02) * rng.standard_normal(flat.shape).astype(np.float32)
+    pol.set_param_values(pert.copy(), set_new=True, set_old=False)
+    out["pert_params"] = pert
+    out["pert_surr"] = agent.CPI_surrogate(obs, act, adv).data.numpy().ravel()[0]
+    out["pert_kl"] = agent.kl_old_new(obs, act).data.numpy().ravel()[0]
+    out["pert_vpg"] = agent.flat_vpg(obs, act, adv)
+    out["pert_LL"] = pol.log_likelihood(obs, act)
+    pol.set_param_values(flat.copy(), set_new=True, set_old=True)
+
+    # full updates
+    agent.train_from_paths(p1)
+    out["npg_new_params"] = pol.get_param_values()
+    eb, ea = base.fit(p1, return_errors=True)
+    out["fit1_coeffs"] = base._coeffs.copy()
+    out["fit1_errors"] = np.asarray([eb, ea])
+
+    # TRPO from the same starting point (captures per-trial decisions via stdout-free replay)
+    pol, _ = build_ref_policy(R, n, m, hidden, seed=123, flat=flat, transforms=tr)
+    t = R.trpo.TRPO(None, pol, base, kl_dist=0.01, FIM_invert_args={"iters": 10, "damping": 1e-4})
+    import io, contextlib
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        t.train_from_paths(p1)
+    out["trpo_new_params"] = pol.get_param_values()
+    out["trpo_backtracks"] = buf.getvalue().count("Backtracking")
+
+    # DAPG with 5 demo paths
+    pol, _ = build_ref_policy(R, n, m, hidden, seed=123, flat=flat, transforms=tr)
+    db = syn.make_flat_batch(5 * min(horizon, 50), n, m, min(horizon, 50), seed + 2, flat, hidden, tr)
+    out.update({"demo_" + k: v for k, v in db.items()})
+    dp = syn.flat_to_paths(db)
+    dg = R.dapg.DAPG(None, pol, base, demo_paths=dp, kl_dist=0.01,
+                     FIM_invert_args={"iters": 10, "damping": 1e-4}, lam_0=1.0, lam_1=0.95)
+    dg.train_from_paths(p1)
+    out["dapg_new_params"] = pol.get_param_values()
+
+    # batch REINFORCE
+    pol, _ = build_ref_policy(R, n, m, hidden, seed=123, flat=flat, transforms=tr)
+    br = R.br.BatchREINFORCE(None, pol, base, learn_rate=0.01)
+    br.train_from_paths(p1)
+    out["reinforce_new_params"] = pol.get_param_values()
+
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
+
+
+if __name__ == "__main__":
+    R = import_reference()
+    #            name            n   m  hidden    hor   N     seed  mid
+    run_case(R, "c1_linear",     6,  2, (),        25, 1000, 1000, False)
+    run_case(R, "c2_swimmer",   12,  4, (32, 32), 500, 4000, 2000, False)
+    run_case(R, "c3_hopper",    11,  3, (64, 64), 200, 3000, 3000, False)
+    run_case(R, "c3_hopper_mid", 11, 3, (64, 64), 200, 3000, 3001, True)
+    run_case(R, "c5_adroit_mid", 45, 24, (32, 32), 100, 2000, 5000, True)
+    run_case(R, "c1_linear_mid", 6,  2, (),        25, 1000, 1001, True)
