@@ -1,0 +1,110 @@
+"""ctypes binding of the C-ABI library (include/mjrl_b200.h).
+
+There is no CPU fallback: if the library is missing or no sm_100a device is present the
+first call raises.  Loading the library (symbol table only) works without a GPU so that the
+CPU test-suite can verify that every declared entry point is exported.
+"""
+import ctypes
+import os
+import re
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libmjrl_b200.so")
+HEADER = os.path.join(HERE, "..", "include", "mjrl_b200.h")
+
+_lib = None
+
+
+class MjrlError(RuntimeError):
+    pass
+
+
+def declared_symbols():
+    """Names of every `int|const char* mjrl_*(` entry point declared in the header."""
+    txt = open(HEADER).read()
+    return sorted(set(re.findall(r"\b(mjrl_[a-z0-9_]+)\s*\(", txt)))
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MjrlError(
+            "mjrl_b200: %s is missing -- run `python -m mjrl_b200.build` (no CPU fallback exists)"
+            % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.mjrl_last_error.restype = ctypes.c_char_p
+    for name in declared_symbols():
+        fn = getattr(lib, name)  # raises AttributeError if a declared symbol is not exported
+        if name != "mjrl_last_error":
+            fn.restype = ctypes.c_int
+    _lib = lib
+    return lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = load().mjrl_last_error().decode(errors="replace")
+        raise MjrlError("mjrl_b200 %s failed (rc=%d): %s" % (what, rc, msg))
+
+
+# ---- argument marshalling helpers ------------------------------------------------------
+c_void_p, c_int, c_i64, c_double = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_double
+c_float = ctypes.c_float
+
+
+def ptr(t):
+    """Device (or host) pointer of a torch tensor / None as c_void_p."""
+    if t is None:
+        return c_void_p(0)
+    if isinstance(t, int):
+        return c_void_p(t)
+    return c_void_p(t.data_ptr())
+
+
+class Context:
+    """One per process / GPU (mjrl_ctx_create)."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        h = c_void_p()
+        check(self.lib.mjrl_ctx_create(ctypes.byref(h), c_int(int(device))), "ctx_create")
+        self.h = h
+        self.device = int(device)
+        self.sm_count = self.lib.mjrl_ctx_sm_count(self.h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.mjrl_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def call(self, name, *args):
+        check(getattr(self.lib, name)(self.h, *args), name)
+
+
+_ctx = {}
+
+
+def context(device=None):
+    """Process-wide context for `device` (default: torch's current CUDA device)."""
+    import torch
+    if not torch.cuda.is_available():
+        raise MjrlError("mjrl_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    if device is None:
+        device = torch.cuda.current_device()
+    device = int(device)
+    if device not in _ctx:
+        _ctx[device] = Context(device)
+    return _ctx[device]
+
+
+def stream_ptr():
+    import torch
+    return c_void_p(torch.cuda.current_stream().cuda_stream)

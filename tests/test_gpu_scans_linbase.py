@@ -1,0 +1,133 @@
+"""GPU parity: segmented scans and LinearBaseline vs the oracle / reference goldens.
+
+Tolerance (north_star): returns, advantages and baseline predictions within 1e-6 relative
+(fp64).  We assert 1e-9 on the scans (they are fp64 re-associations of the same sums)."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import batch_of, rel_l2
+from mjrl_b200.utils import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+
+
+def _mods():
+    from mjrl_b200.utils import process_samples as ps
+    from mjrl_b200.baselines.linear_baseline import LinearBaseline
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.batch import drop_cache
+    return ps, LinearBaseline, EnvSpec, drop_cache
+
+
+def test_returns_gae_baseline_match_reference_goldens(golden):
+    g = golden
+    ps, LinearBaseline, EnvSpec, drop_cache = _mods()
+    spec = EnvSpec(g["n"], g["m"], g["horizon"], 1)
+    base = LinearBaseline(spec)
+    p0 = syn.flat_to_paths(batch_of(g, "b0_"))
+    p1 = syn.flat_to_paths(batch_of(g, "b1_"))
+    ps.compute_returns(p0, g["gamma"])
+    r0 = np.concatenate([p["returns"] for p in p0])
+    assert r0.dtype == np.float64
+    assert rel_l2(r0, g["b0_returns"]) < 1e-12
+    assert np.max(np.abs(r0 - g["b0_returns"]) / np.maximum(1.0, np.abs(g["b0_returns"]))) < 1e-12
+    ps.compute_advantages(p0, base, g["gamma"], g["gae_lambda"])   # zero baseline (F8)
+    a0 = np.concatenate([p["advantages"] for p in p0])
+    assert rel_l2(a0, g["b0_adv_zero_baseline"]) < 1e-12
+    eb, ea = base.fit(p0, return_errors=True)
+    # predictions with the fitted coefficients, not the coefficients, are the contract
+    from oracle import mjrl_oracle as O
+    X0 = np.concatenate([O.linear_features(p) for p in p0])
+    assert rel_l2(X0 @ np.asarray(base._coeffs), X0 @ g["fit0_coeffs"]) < 1e-8
+    assert abs(eb - g["fit0_errors"][0]) < 1e-9 and abs(ea - g["fit0_errors"][1]) < 1e-7
+    ps.compute_returns(p1, g["gamma"])
+    ps.compute_advantages(p1, base, g["gamma"], g["gae_lambda"])
+    b1 = np.concatenate([p["baseline"] for p in p1])
+    a1 = np.concatenate([p["advantages"] for p in p1])
+    assert rel_l2(b1, g["b1_baseline"]) < 1e-6
+    assert rel_l2(a1, g["b1_adv"]) < 1e-6
+    pp = copy.deepcopy(p1)
+    drop_cache()
+    ps.compute_advantages(pp, base, g["gamma"], None, normalize=True)
+    assert rel_l2(np.concatenate([p["advantages"] for p in pp]), g["b1_adv_plain_norm"]) < 1e-6
+    eb, ea = base.fit(p1, return_errors=True)
+    X1 = np.concatenate([O.linear_features(p) for p in p1])
+    assert rel_l2(X1 @ np.asarray(base._coeffs), X1 @ g["fit1_coeffs"]) < 1e-8
+    assert abs(eb - g["fit1_errors"][0]) < 1e-6 * max(1, g["fit1_errors"][0])
+    assert abs(ea - g["fit1_errors"][1]) < 1e-6
+
+
+@pytest.mark.parametrize("lens", [[1], [2, 1, 3], [1023, 1024, 1025], [5000, 7, 2049], [1] * 300])
+@pytest.mark.parametrize("gamma,lam", [(0.995, 0.97), (1.0, 1.0), (0.9, 0.0)])
+def test_ragged_paths_scan_vs_oracle(lens, gamma, lam):
+    from oracle import mjrl_oracle as O
+    ps, LinearBaseline, EnvSpec, drop_cache = _mods()
+    rng = np.random.default_rng(sum(lens))
+    n = 5
+    paths = []
+    for i, T in enumerate(lens):
+        paths.append(dict(observations=rng.standard_normal((T, n)).astype(np.float32).astype(np.float64) * 4,
+                          actions=rng.standard_normal((T, 2)),
+                          rewards=rng.standard_normal(T), terminated=bool(i % 2)))
+    ref = copy.deepcopy(paths)
+    ob = O.LinearBaseline()
+    ob._coeffs = rng.standard_normal(n + 4)
+    gb = LinearBaseline(EnvSpec(n, 2, 1000, 1))
+    gb._coeffs = ob._coeffs.copy()
+    O.compute_returns(ref, gamma)
+    O.compute_advantages(ref, ob, gamma, lam)
+    ps.compute_returns(paths, gamma)
+    ps.compute_advantages(paths, gb, gamma, lam)
+    for k in ("returns", "baseline", "advantages"):
+        a = np.concatenate([p[k] for p in paths])
+        b = np.concatenate([p[k] for p in ref])
+        assert a.shape == b.shape
+        assert rel_l2(a, b) < 1e-10, k
+    # per-path predict and discount_sum entry points
+    np.testing.assert_allclose(gb.predict(paths[0]), ob.predict(ref[0]), rtol=1e-10, atol=1e-10)
+    x = rng.standard_normal(37)
+    np.testing.assert_allclose(ps.discount_sum(x, gamma), O.discount_sum(x, gamma), rtol=1e-12, atol=1e-12)
+
+
+def test_segment_indexing_bit_exact():
+    """Constant rewards of 1 with gamma=1: returns[t] = T - t exactly (integers in fp64), so
+    any mistake in path segmentation shows up as a bit difference."""
+    ps, LinearBaseline, EnvSpec, drop_cache = _mods()
+    rng = np.random.default_rng(5)
+    lens = rng.integers(1, 3000, size=200)
+    paths = [dict(observations=np.zeros((T, 3)), actions=np.zeros((T, 1)), rewards=np.ones(T),
+                  terminated=False) for T in lens]
+    ps.compute_returns(paths, 1.0)
+    for p, T in zip(paths, lens):
+        np.testing.assert_array_equal(p["returns"], np.arange(T, 0, -1, dtype=np.float64))
+
+
+def test_linbase_nan_retry_and_large_feature_count():
+    """NaN returns -> 10 tries, NaN coefficients (linear_baseline.py:30-38); Ant-sized F=115."""
+    from oracle import mjrl_oracle as O
+    ps, LinearBaseline, EnvSpec, drop_cache = _mods()
+    rng = np.random.default_rng(11)
+    n, T, P = 111, 300, 12
+    paths = [dict(observations=3 * rng.standard_normal((T, n)).astype(np.float32).astype(np.float64),
+                  actions=np.zeros((T, 8)), rewards=rng.standard_normal(T), terminated=False)
+             for _ in range(P)]
+    ref = copy.deepcopy(paths)
+    O.compute_returns(ref, 0.99)
+    ps.compute_returns(paths, 0.99)
+    gb, ob = LinearBaseline(EnvSpec(n, 8, T, 1)), O.LinearBaseline()
+    eg = gb.fit(paths, return_errors=True)
+    eo = ob.fit(ref, return_errors=True)
+    X = np.concatenate([O.linear_features(p) for p in ref])
+    assert rel_l2(X @ np.asarray(gb._coeffs), X @ ob._coeffs) < 1e-7
+    assert abs(eg[0] - eo[0]) < 1e-9 and abs(eg[1] - eo[1]) < 1e-7
+    bad = copy.deepcopy(paths)
+    drop_cache()
+    bad[0]["returns"] = bad[0]["returns"].copy()
+    bad[0]["returns"][3] = np.nan
+    gb2 = LinearBaseline(EnvSpec(n, 8, T, 1))
+    gb2.fit(bad)
+    assert np.all(np.isnan(np.asarray(gb2._coeffs)))
+    assert gb2.last_fit_info["retries"] == 9
