@@ -100,6 +100,91 @@ int mjrl_linbase_solve(mjrl_ctx* ctx, const double* gram, int32_t F, double reg_
                        const double* coeffs_prev, double* coeffs, double* info4,
                        void* stream);
 
+/* ---- (c)(d)(e) Gaussian policy: mjrl/policies/gaussian_mlp.py, gaussian_linear.py ---- */
+/* Network description.  h1 == h2 == 0 selects the affine policy (LinearModel.forward,
+ * gaussian_linear.py:171-175); otherwise the two-hidden-layer tanh MuNet
+ * (gaussian_mlp.py:176-182).  Transform pointers are DEVICE fp32 arrays ([n],[n],[m],[m])
+ * or NULL for identity: x~ = (x - in_shift)/(in_scale + 1e-8), mu = y*out_scale + out_shift. */
+typedef struct mjrl_policy_desc {
+  int32_t n, m, h1, h2;
+  const float* in_shift;
+  const float* in_scale;
+  const float* out_shift;
+  const float* out_scale;
+} mjrl_policy_desc;
+
+/* number of parameters d (gaussian_mlp.py:51-53); <0 on a bad description */
+int64_t mjrl_policy_param_count(const mjrl_policy_desc* desc);
+/* set_param_values' clamp (gaussian_mlp.py:75-76,87-88): params[d-m..d) = max(., min_log_std) */
+int mjrl_policy_clamp_log_std(mjrl_ctx* ctx, const mjrl_policy_desc* desc, float* params,
+                              float min_log_std, void* stream);
+/* mean_LL (gaussian_mlp.py:100-110).  mean_out [N,m] and/or ll_out [N] may be NULL; act may be
+ * NULL when ll_out is NULL. */
+int mjrl_policy_forward(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                        const float* obs, const float* act, int64_t N, float* mean_out,
+                        float* ll_out, void* stream);
+/* CPI_surrogate + kl_old_new in one pass (batch_reinforce.py:37-49, gaussian_mlp.py:124-140).
+ * old_ll [N], old_mean [N,m], old_log_std [m] describe the old policy on the same samples.
+ * sums2 (fp64, device) = { sum_t exp(LL_new-LL_old)*w_t , sum_t KL_t(old||new) }; the caller
+ * divides by the (global) sample count.  w may be NULL (surrogate sum = 0). */
+int mjrl_policy_eval(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                     const float* obs, const float* act, const float* w, const float* old_ll,
+                     const float* old_mean, const float* old_log_std, int64_t N, double* sums2,
+                     void* stream);
+/* flat_vpg (batch_reinforce.py:51-55): grad_sum[d] (fp64, device) = sum_t w_t LR_t dLL_t/dtheta,
+ * LR_t = exp(LL_t - old_ll[t]) or 1 when old_ll is NULL (new == old).  surr_sum (fp64[1]) =
+ * sum_t LR_t w_t.  Optionally caches LL [N] and mean [N,m] of this parameter set for later
+ * mjrl_policy_eval calls.  The caller scales by sample_coef/N after any all-reduce. */
+int mjrl_policy_grad(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                     const float* obs, const float* act, const float* w, const float* old_ll,
+                     int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
+                     float* mean_out, void* stream);
+/* Analytic Hessian-of-KL (Gauss-Newton / Fisher) product at new == old, replacing the double
+ * backprop of npg_cg.py:55-74:  fvp_sum[d] (fp64, device) = sum_t J_t^T diag(2/(2 sigma^2+1e-8)) J_t vec
+ * on the network block; the log_std block is N_local * h(sigma) * vec (exact second
+ * derivative of the KL expression of gaussian_mlp.py:137-139).  No damping, no 1/N: the CG
+ * update applies both after the all-reduce.  If stop_flag (device int32) is non-NULL and
+ * non-zero the kernel exits immediately (CG already converged). */
+int mjrl_policy_fvp(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                    const float* obs, int64_t N, const float* vec, double* fvp_sum,
+                    const int32_t* stop_flag, void* stream);
+
+/* ---- (d) conjugate gradient on device: mjrl/utils/cg_solve.py:3-22 ------------------- */
+/* CG state: caller-allocated DEVICE arrays.  x, r, p, z are fp64 [d] (z is the operator
+ * output slot that mjrl_policy_fvp fills and the caller all-reduces); p32 is p cast to fp32
+ * [d] (the operator input); scal fp64 [8] = {rdotr, p.z, v, mu, rdotr0, -, -, -};
+ * flags int32 [2] = {stop, iterations done}. */
+typedef struct mjrl_cg_state {
+  double* x;
+  double* r;
+  double* p;
+  double* z;
+  double* scal;
+  float* p32;
+  int32_t* flags;
+} mjrl_cg_state;
+/* x = 0, r = p = b (cg_solve.py:4-7; x_0 is ignored exactly like the reference, :4-5). */
+int mjrl_cg_init(mjrl_ctx* ctx, const mjrl_cg_state* state, int64_t d, const double* b, double b_scale,
+                 void* stream);
+/* One iteration (cg_solve.py:10-20) given z_sum = sum over samples of the operator applied to
+ * p32, as left in state->z by mjrl_policy_fvp (+ all-reduce):  z = z_sum*inv_count + damping*p;
+ * v = rdotr/p.z; x += v p; r -= v z; mu = r.r/rdotr; p = r + mu p; stop when r.r < tol. */
+int mjrl_cg_update(mjrl_ctx* ctx, const mjrl_cg_state* state, int64_t d, double inv_count, double damping,
+                   double residual_tol, void* stream);
+/* Step-size rule + parameter update (npg_cg.py:130-141 / trpo.py:100-108 / dapg.py:111-118):
+ * gx = g.x; alpha = const_alpha >= 0 ? const_alpha : sqrt(|delta/(gx + 1e-20)|);
+ * new_params = curr + (alpha*alpha_scale)*x with log_std clamped at min_log_std.
+ * scal4 (fp64, device) = {alpha, gx, n_step_size, alpha*alpha_scale}. */
+int mjrl_npg_step(mjrl_ctx* ctx, int64_t d, int32_t m, const double* g, double g_scale,
+                  const double* x, const float* curr, double delta, double const_alpha,
+                  double alpha_scale, float min_log_std, float* new_params, double* scal4,
+                  void* stream);
+/* (e) batched get_action (gaussian_mlp.py:92-98): act = mean + exp(log_std)*eps, eps ~ N(0,1)
+ * from Philox4x32-10 keyed by (seed, row index + offset). */
+int mjrl_policy_act(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                    const float* obs, int64_t B, uint64_t seed, uint64_t offset, float* act_out,
+                    float* mean_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

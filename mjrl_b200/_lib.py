@@ -37,7 +37,9 @@ def load():
     lib.mjrl_last_error.restype = ctypes.c_char_p
     for name in declared_symbols():
         fn = getattr(lib, name)  # raises AttributeError if a declared symbol is not exported
-        if name != "mjrl_last_error":
+        if name == "mjrl_policy_param_count":
+            fn.restype = ctypes.c_int64
+        elif name != "mjrl_last_error":
             fn.restype = ctypes.c_int
     _lib = lib
     return lib
@@ -108,3 +110,18 @@ def context(device=None):
 def stream_ptr():
     import torch
     return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# ---- C structs of include/mjrl_b200.h ---------------------------------------------------
+class PolicyDesc(ctypes.Structure):
+    _fields_ = [("n", ctypes.c_int32), ("m", ctypes.c_int32), ("h1", ctypes.c_int32),
+                ("h2", ctypes.c_int32), ("in_shift", c_void_p), ("in_scale", c_void_p),
+                ("out_shift", c_void_p), ("out_scale", c_void_p)]
+
+
+class CGState(ctypes.Structure):
+    _fields_ = [("x", c_void_p), ("r", c_void_p), ("p", c_void_p), ("z", c_void_p),
+                ("scal", c_void_p), ("p32", c_void_p), ("flags", c_void_p)]
+
+
+c_u64 = ctypes.c_uint64

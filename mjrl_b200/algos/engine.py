@@ -1,0 +1,148 @@
+"""On-device update engine shared by BatchREINFORCE / NPG / TRPO / DAPG.
+
+It strings the C-ABI calls of one update together on the current CUDA stream without any
+host synchronisation until the final scalars are read:
+
+    whiten -> gradient (+surr_before, caches old LL/mean) -> [all-reduce]
+           -> K x ( FVP -> [all-reduce] -> CG update ) -> step -> eval (+surr_after, KL)
+
+Multi-GPU: every rank owns whole paths; `dist` (torch.distributed, NCCL) all-reduces only the
+small fp64 vectors (gradient+surrogate, each FVP, two scalars) -- SURVEY.md section 8(e).
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from .. import _lib
+from .._lib import CGState, c_double, c_float, c_i64, c_int, c_void_p, ptr, stream_ptr
+
+
+class Dist:
+    """Thin wrapper over torch.distributed: sum all-reduce on device tensors; identity when
+    the process group is absent (single GPU)."""
+
+    def __init__(self, group=None):
+        import torch.distributed as td
+        self.td = td if (td.is_available() and td.is_initialized()) else None
+        self.group = group
+        self.world = self.td.get_world_size(group) if self.td else 1
+        self.rank = self.td.get_rank(group) if self.td else 0
+        self.calls = 0
+
+    def allreduce(self, t):
+        if self.td is not None and self.world > 1:
+            self.td.all_reduce(t, op=self.td.ReduceOp.SUM, group=self.group)
+            self.calls += 1
+        return t
+
+
+class UpdateEngine:
+    def __init__(self, policy, dist=None):
+        self.policy = policy
+        self.dv = policy.device_view()
+        self.ctx = self.dv.ctx
+        self.device = self.dv.device
+        self.dist = dist or Dist()
+        d = self.dv.d
+        dev = self.device
+        f64 = lambda k: torch.zeros(k, dtype=torch.float64, device=dev)
+        self.grad = f64(d + 1)              # [gradient sum | surrogate sum] packed for one all-reduce
+        self.cg_x, self.cg_r, self.cg_p, self.cg_z = f64(d), f64(d), f64(d), f64(d)
+        self.cg_scal = f64(8)
+        self.cg_p32 = torch.zeros(d, dtype=torch.float32, device=dev)
+        self.cg_flags = torch.zeros(2, dtype=torch.int32, device=dev)
+        self.cg = CGState(*[c_void_p(t.data_ptr()) for t in
+                            (self.cg_x, self.cg_r, self.cg_p, self.cg_z, self.cg_scal, self.cg_p32,
+                             self.cg_flags)])
+        self.sums2 = f64(2)
+        self.scal4 = f64(4)
+        self.mom = f64(4)
+        self.new_params = torch.zeros(d, dtype=torch.float32, device=dev)
+        self.launches = 0  # kernels launched by this engine (bench's gpu_launches)
+
+    # ------------------------------------------------------------------ building blocks
+    def whiten(self, adv64, eps=1e-6, scale=1.0, N_global=None):
+        """npg_cg.py:91 on device: fp32 (adv-mean)/(std+eps).  Multi-GPU: global moments."""
+        N = adv64.numel()
+        w = torch.empty(N, dtype=torch.float32, device=self.device)
+        if self.dist.world == 1:
+            self.ctx.call("mjrl_moments", ptr(adv64), c_i64(N), ptr(self.mom), stream_ptr())
+            self.launches += 4
+        else:
+            # two-pass global moments: all-reduce (N, sum) then the centred sum of squares
+            part = torch.stack([torch.tensor(float(N), dtype=torch.float64, device=self.device),
+                                adv64.sum()])
+            self.dist.allreduce(part)
+            mean = part[1] / part[0]
+            ss = ((adv64 - mean) ** 2).sum().reshape(1)
+            self.dist.allreduce(ss)
+            self.mom.copy_(torch.stack([part[0], part[1], ss[0], mean]))
+        self.ctx.call("mjrl_whiten_f32", ptr(adv64), c_i64(N), ptr(self.mom), c_double(eps),
+                      c_double(scale), ptr(w), stream_ptr())
+        self.launches += 1
+        return w
+
+    def old_cache(self, params_old, obs, act):
+        """Old-policy LL [N] and mean [N,m] (what old_dist_info returns, gaussian_mlp.py:116-118)."""
+        mean, ll = self.dv.forward(params_old, obs, act)
+        self.launches += 1
+        return ll, mean
+
+    def gradient(self, params, obs, act, w, old_ll=None, cache=None, accumulate=False):
+        """flat_vpg sums (batch_reinforce.py:51-55) into self.grad[:d], surrogate sum into
+        self.grad[d].  `cache=(ll, mean)` tensors receive LL/mean of `params`."""
+        d = self.dv.d
+        N = obs.shape[0]
+        tgt = self.grad if not accumulate else torch.empty_like(self.grad)
+        ll_out, mean_out = cache if cache is not None else (None, None)
+        self.ctx.call("mjrl_policy_grad", self.dv.desc_ref(), ptr(params), ptr(obs), ptr(act), ptr(w),
+                      ptr(old_ll), c_i64(N), ptr(tgt), c_void_p(tgt.data_ptr() + 8 * d),
+                      ptr(ll_out), ptr(mean_out), stream_ptr())
+        self.launches += 3
+        if accumulate:
+            self.grad[:d] += tgt[:d]   # demo term: only the gradient, not the surrogate (dapg.py:93,98)
+        return self.grad
+
+    def fvp(self, params, obs, vec32, out64):
+        self.ctx.call("mjrl_policy_fvp", self.dv.desc_ref(), ptr(params), ptr(obs), c_i64(obs.shape[0]),
+                      ptr(vec32), ptr(out64), ptr(self.cg_flags), stream_ptr())
+        self.launches += 2
+
+    def cg_solve(self, params, obs, g_scale, N_global, iters, damping, tol=1e-10, trace=None,
+                 subsample=None):
+        """cg_solve.py:3-22 entirely on device; b = self.grad[:d]*g_scale.  Returns self.cg_x."""
+        d = self.dv.d
+        self.ctx.call("mjrl_cg_init", ctypes.byref(self.cg), c_i64(d), ptr(self.grad), c_double(g_scale),
+                      stream_ptr())
+        self.launches += 1
+        for _ in range(iters):
+            o = obs if subsample is None else subsample()
+            cnt = N_global if subsample is None else float(o.shape[0]) * self.dist.world
+            self.fvp(params, o, self.cg_p32, self.cg_z)
+            self.dist.allreduce(self.cg_z)
+            self.ctx.call("mjrl_cg_update", ctypes.byref(self.cg), c_i64(d), c_double(1.0 / cnt),
+                          c_double(damping), c_double(tol), stream_ptr())
+            self.launches += 1
+            if trace is not None:
+                trace.append(self.cg_x.cpu().numpy().copy())
+        return self.cg_x
+
+    def step(self, curr, g_scale, delta, const_alpha=None, alpha_scale=1.0):
+        """npg_cg.py:130-141: alpha, new_params = curr + alpha*alpha_scale*x, log_std clamped."""
+        self.ctx.call("mjrl_npg_step", c_i64(self.dv.d), c_int(self.dv.m), ptr(self.grad),
+                      c_double(g_scale), ptr(self.cg_x), ptr(curr), c_double(delta),
+                      c_double(-1.0 if const_alpha is None else const_alpha), c_double(alpha_scale),
+                      c_float(self.policy.min_log_std), ptr(self.new_params), ptr(self.scal4),
+                      stream_ptr())
+        self.launches += 1
+        return self.new_params
+
+    def evaluate(self, params_new, obs, act, w, old_ll, old_mean, old_log_std, N_global):
+        """(surrogate, KL) of params_new against the cached old policy -> device fp64 [2] means."""
+        self.ctx.call("mjrl_policy_eval", self.dv.desc_ref(), ptr(params_new), ptr(obs), ptr(act),
+                      ptr(w), ptr(old_ll), ptr(old_mean), ptr(old_log_std), c_i64(obs.shape[0]),
+                      ptr(self.sums2), stream_ptr())
+        self.launches += 2
+        self.dist.allreduce(self.sums2)
+        return self.sums2 / N_global

@@ -1,0 +1,1050 @@
+// (c)(d) Fused Gaussian-MLP passes over timestep tiles: forward/log-likelihood, surrogate+KL
+// evaluation, vanilla policy gradient, and the analytic Fisher-vector product.
+//
+// Replaces (reference = bennevans/mjrl):
+//   MuNet.forward + mean_LL          mjrl/policies/gaussian_mlp.py:100-110,176-182
+//   likelihood_ratio / mean_kl       mjrl/policies/gaussian_mlp.py:124-140
+//   CPI_surrogate / kl_old_new / flat_vpg   mjrl/algos/batch_reinforce.py:37-55 (torch autograd)
+//   NPG.HVP (double backprop)        mjrl/algos/npg_cg.py:55-74
+//
+// One persistent CTA per SM walks tiles of TS timesteps (tile = blockIdx.x + k*gridDim.x).
+// Per tile the obs rows are read ONCE from HBM (coalesced, contiguous TS*n floats), every
+// intermediate stays in shared memory / registers, and nothing but per-CTA partial sums is
+// written back: algorithmic bytes 4n (FVP), 4n+8m+12 (grad), 4n+8m+12 (eval) per timestep.
+// These passes are fp32-FMA bound, not HBM bound.
+#include "policy_tile.cuh"
+
+namespace pol {
+
+enum Mode { M_FWD = 0, M_EVAL = 1, M_GRAD = 2, M_FVP = 3 };
+
+struct Args {
+  const float* params;
+  const float* vec;
+  const float* obs;
+  const float* act;
+  const float* w;
+  const float* old_ll;
+  const float* old_mean;
+  const float* old_log_std;
+  float* mean_out;
+  float* ll_out;
+  const float* in_shift;
+  const float* in_scale;
+  const float* out_shift;
+  const float* out_scale;
+  float* partials;    // [grid][dstride]
+  double* spartials;  // [grid][2]
+  const int32_t* stop_flag;
+  long long N;
+  int n, m, h1, h2, dstride;
+};
+
+// Shared-memory carve-up (offsets in floats), identical on host and device.
+struct Layout {
+  int TS, LDH, NP, LDX, MP, LDM;
+  int X, H1, H2, B1, B2, U, E, ACT, S0, S1;
+  int W0t, b0, W1t, b1, W2t, b2, W1, W2, V0t, vb0, V1t, vb1, V2t, vb2;
+  int ishift, iden, oscale, oshift, sig, ls, ols_, fisher;
+  int total;
+  __host__ __device__ Layout(int HP, int n, int m, int mode) {
+    const int NF = HP / 4, NT = NTHREADS / NF;
+    TS = RT * NT; LDH = HP + 4; NP = round4(n); LDX = NP + 4; MP = round4(m); LDM = MP + 4;
+    int o = 0;
+    auto take = [&](int cnt) { int r = o; o += (cnt + 3) & ~3; return r; };
+    X = take(TS * LDX);
+    H1 = take(TS * LDH); H2 = take(TS * LDH);
+    const bool bwd = mode == M_GRAD || mode == M_FVP;
+    B1 = bwd ? take(TS * LDH) : 0; B2 = bwd ? take(TS * LDH) : 0;
+    U = take(TS * LDM);
+    E = mode == M_GRAD ? take(TS * LDM) : 0;
+    ACT = mode != M_FVP ? take(TS * LDM) : 0;
+    S0 = take(TS); S1 = take(TS);
+    W0t = take(NP * LDH); b0 = take(HP); W1t = take(HP * LDH); b1 = take(HP);
+    W2t = take(HP * LDM); b2 = take(MP);
+    W1 = bwd ? take(HP * LDH) : 0; W2 = bwd ? take(MP * LDH) : 0;
+    const bool fvp = mode == M_FVP;
+    V0t = fvp ? take(NP * LDH) : 0; vb0 = fvp ? take(HP) : 0; V1t = fvp ? take(HP * LDH) : 0;
+    vb1 = fvp ? take(HP) : 0; V2t = fvp ? take(HP * LDM) : 0; vb2 = fvp ? take(MP) : 0;
+    ishift = take(NP); iden = take(NP); oscale = take(MP); oshift = take(MP); sig = take(MP);
+    ls = take(MP); ols_ = take(MP); fisher = take(MP);
+    total = o;
+  }
+};
+
+// k-major (transposed) copy of a row-major (rows_out x cols_in) weight block of the flat vector:
+// dst[k][f] = src[f*cols_in + k], zero padded to [Kpad][ld].
+__device__ __forceinline__ void load_wt(float* dst, int ld, int Kpad, int Fpad, const float* src,
+                                        int rows_out, int cols_in) {
+  for (int i = threadIdx.x; i < Kpad * Fpad; i += NTHREADS) {
+    int f = i / Kpad, k = i - f * Kpad;  // consecutive threads walk k: coalesced global reads
+    float v = (f < rows_out && k < cols_in) ? __ldg(src + f * cols_in + k) : 0.f;
+    dst[k * ld + f] = v;
+  }
+}
+// natural copy: dst[r][c] = src[r*cols + c], zero padded to [Rpad][ld] (first Cpad columns)
+__device__ __forceinline__ void load_w(float* dst, int ld, int Rpad, int Cpad, const float* src,
+                                       int rows, int cols) {
+  for (int i = threadIdx.x; i < Rpad * Cpad; i += NTHREADS) {
+    int r = i / Cpad, c = i - r * Cpad;
+    dst[r * ld + c] = (r < rows && c < cols) ? __ldg(src + r * cols + c) : 0.f;
+  }
+}
+__device__ __forceinline__ void load_v(float* dst, int pad, const float* src, int cnt, float fill = 0.f) {
+  for (int i = threadIdx.x; i < pad; i += NTHREADS) dst[i] = (src && i < cnt) ? __ldg(src + i) : fill;
+}
+
+template <int HP, int MODE, int W0SLOTS>
+__global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
+  constexpr int NF = HP / 4, NT = NTHREADS / NF, TS = RT * NT, LDH = HP + 4;
+  constexpr bool BWD = MODE == M_GRAD || MODE == M_FVP;
+  extern __shared__ __align__(16) float sm[];
+  if (MODE == M_FVP && a.stop_flag && *a.stop_flag) return;
+
+  const Layout L(HP, a.n, a.m, MODE);
+  const Flat F(a.n, a.m, a.h1, a.h2);
+  const int tid = threadIdx.x;
+  const int NP = L.NP, LDX = L.LDX, MP = L.MP, LDM = L.LDM;
+  const int n = a.n, m = a.m;
+
+  float* sX = sm + L.X; float* sH1 = sm + L.H1; float* sH2 = sm + L.H2;
+  float* sB1 = sm + L.B1; float* sB2 = sm + L.B2; float* sU = sm + L.U; float* sE = sm + L.E;
+  float* sAct = sm + L.ACT; float* sS0 = sm + L.S0; float* sS1 = sm + L.S1;
+
+  // ---- one-time: zero activations (padding columns stay zero), stage weights -------------
+  for (int i = tid; i < L.W0t; i += NTHREADS) sm[i] = 0.f;
+  const float* P = a.params;
+  load_wt(sm + L.W0t, LDH, NP, HP, P + F.oW0, F.h1, n);
+  load_v(sm + L.b0, HP, P + F.ob0, F.h1);
+  load_wt(sm + L.W1t, LDH, HP, HP, P + F.oW1, F.h2, F.h1);
+  load_v(sm + L.b1, HP, P + F.ob1, F.h2);
+  load_wt(sm + L.W2t, LDM, HP, MP, P + F.oW2, m, F.h2);
+  load_v(sm + L.b2, MP, P + F.ob2, m);
+  if (BWD) {
+    load_w(sm + L.W1, LDH, HP, HP, P + F.oW1, F.h2, F.h1);
+    load_w(sm + L.W2, LDH, MP, HP, P + F.oW2, m, F.h2);
+  }
+  if (MODE == M_FVP) {
+    const float* V = a.vec;
+    load_wt(sm + L.V0t, LDH, NP, HP, V + F.oW0, F.h1, n);
+    load_v(sm + L.vb0, HP, V + F.ob0, F.h1);
+    load_wt(sm + L.V1t, LDH, HP, HP, V + F.oW1, F.h2, F.h1);
+    load_v(sm + L.vb1, HP, V + F.ob1, F.h2);
+    load_wt(sm + L.V2t, LDM, HP, MP, V + F.oW2, m, F.h2);
+    load_v(sm + L.vb2, MP, V + F.ob2, m);
+  }
+  load_v(sm + L.ishift, NP, a.in_shift, n, 0.f);
+  for (int i = tid; i < NP; i += NTHREADS)
+    sm[L.iden + i] = (a.in_scale && i < n ? __ldg(a.in_scale + i) : 1.f) + 1e-8f;
+  load_v(sm + L.oscale, MP, a.out_scale, m, 1.f);
+  load_v(sm + L.oshift, MP, a.out_shift, m, 0.f);
+  for (int j = tid; j < MP; j += NTHREADS) {
+    float ls = j < m ? __ldg(P + F.ols + j) : 0.f;
+    float sg = expf(ls);
+    sm[L.ls + j] = ls; sm[L.sig + j] = sg;
+    float os = (a.out_scale && j < m) ? __ldg(a.out_scale + j) : 1.f;
+    // d^2 KL / d mu^2 = 2/(2 sigma^2 + 1e-8)  (gaussian_mlp.py:137-138), chained through out_scale twice
+    sm[L.fisher + j] = j < m ? os * os * (2.f / (2.f * sg * sg + 1e-8f)) : 0.f;
+    sm[L.ols_ + j] = (MODE == M_EVAL && j < m) ? __ldg(a.old_log_std + j) : 0.f;
+  }
+  __syncthreads();
+
+  const int tf = tid % NF, tt = tid / NF;  // feature tile / timestep group of the layer products
+  const int row0 = tt * RT, col0 = tf * 4;
+
+  // persistent register accumulators
+  float acc0[W0SLOTS][16], acc1[16], acc2[16], cb0[4], cb1[4];
+  float gb2acc = 0.f, glsacc = 0.f;
+  double surr_acc = 0.0, kl_acc = 0.0;
+  if (BWD) {
+#pragma unroll
+    for (int s = 0; s < W0SLOTS; ++s)
+#pragma unroll
+      for (int e = 0; e < 16; ++e) acc0[s][e] = 0.f;
+#pragma unroll
+    for (int e = 0; e < 16; ++e) { acc1[e] = 0.f; acc2[e] = 0.f; }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { cb0[c] = 0.f; cb1[c] = 0.f; }
+  }
+  const int nt0 = NF * (NP / 4), nt1 = NF * NF, nt2 = (MP / 4) * NF;
+  const TileOwner own1(nt1, tid, 0), own2(nt2, tid, 0);
+
+  const long long ntiles = (a.N + TS - 1) / TS;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long t0 = tile * TS;
+    const int rows = (int)min((long long)TS, a.N - t0);
+    __syncthreads();  // previous tile fully consumed
+    // ---- P0: obs tile (+ actions) -> smem, input transform --------------------------------
+    {
+      const float* src = a.obs + t0 * n;
+      const int cnt = rows * n;
+      for (int i = tid; i < cnt; i += NTHREADS) {
+        int r = i / n, c = i - r * n;
+        sX[r * LDX + c] = (ld_stream(src + i) - sm[L.ishift + c]) / sm[L.iden + c];
+      }
+      if (rows < TS)
+        for (int i = tid; i < (TS - rows) * NP; i += NTHREADS) {
+          int r = rows + i / NP, c = i % NP;
+          sX[r * LDX + c] = 0.f;
+        }
+      if (MODE != M_FVP && a.act) {
+        const float* as = a.act + t0 * m;
+        for (int i = tid; i < rows * m; i += NTHREADS) {
+          int r = i / m, c = i - r * m;
+          sAct[r * LDM + c] = ld_stream(as + i);
+        }
+      }
+    }
+    __syncthreads();
+    // ---- P1: layer 0 ----------------------------------------------------------------------
+    {
+      float z[RT][4], dz[RT][4];
+      const float4 bias = *reinterpret_cast<const float4*>(sm + L.b0 + col0);
+#pragma unroll
+      for (int r = 0; r < RT; ++r) { z[r][0] = bias.x; z[r][1] = bias.y; z[r][2] = bias.z; z[r][3] = bias.w; }
+      if (MODE == M_FVP) {
+        const float4 vb = *reinterpret_cast<const float4*>(sm + L.vb0 + col0);
+#pragma unroll
+        for (int r = 0; r < RT; ++r) { dz[r][0] = vb.x; dz[r][1] = vb.y; dz[r][2] = vb.z; dz[r][3] = vb.w; }
+        mm_acc_dual<RT, false>(z, dz, sX + row0 * LDX, nullptr, LDX, sm + L.W0t + col0,
+                               sm + L.V0t + col0, LDH, NP);
+      } else {
+        mm_acc<RT>(z, sX + row0 * LDX, LDX, sm + L.W0t + col0, LDH, NP);
+      }
+#pragma unroll
+      for (int r = 0; r < RT; ++r) {
+        float4 h = make_float4(tanhf(z[r][0]), tanhf(z[r][1]), tanhf(z[r][2]), tanhf(z[r][3]));
+        *reinterpret_cast<float4*>(sH1 + (row0 + r) * LDH + col0) = h;
+        if (MODE == M_FVP) {
+          float4 d = make_float4((1.f - h.x * h.x) * dz[r][0], (1.f - h.y * h.y) * dz[r][1],
+                                 (1.f - h.z * h.z) * dz[r][2], (1.f - h.w * h.w) * dz[r][3]);
+          *reinterpret_cast<float4*>(sB1 + (row0 + r) * LDH + col0) = d;
+        }
+      }
+    }
+    __syncthreads();
+    // ---- P2: layer 1 ----------------------------------------------------------------------
+    {
+      float z[RT][4], dz[RT][4];
+      const float4 bias = *reinterpret_cast<const float4*>(sm + L.b1 + col0);
+#pragma unroll
+      for (int r = 0; r < RT; ++r) { z[r][0] = bias.x; z[r][1] = bias.y; z[r][2] = bias.z; z[r][3] = bias.w; }
+      if (MODE == M_FVP) {
+        const float4 vb = *reinterpret_cast<const float4*>(sm + L.vb1 + col0);
+#pragma unroll
+        for (int r = 0; r < RT; ++r) { dz[r][0] = vb.x; dz[r][1] = vb.y; dz[r][2] = vb.z; dz[r][3] = vb.w; }
+        mm_acc_dual<RT, true>(z, dz, sH1 + row0 * LDH, sB1 + row0 * LDH, LDH, sm + L.W1t + col0,
+                              sm + L.V1t + col0, LDH, HP);
+      } else {
+        mm_acc<RT>(z, sH1 + row0 * LDH, LDH, sm + L.W1t + col0, LDH, HP);
+      }
+#pragma unroll
+      for (int r = 0; r < RT; ++r) {
+        float4 h = make_float4(tanhf(z[r][0]), tanhf(z[r][1]), tanhf(z[r][2]), tanhf(z[r][3]));
+        *reinterpret_cast<float4*>(sH2 + (row0 + r) * LDH + col0) = h;
+        if (MODE == M_FVP) {
+          float4 d = make_float4((1.f - h.x * h.x) * dz[r][0], (1.f - h.y * h.y) * dz[r][1],
+                                 (1.f - h.z * h.z) * dz[r][2], (1.f - h.w * h.w) * dz[r][3]);
+          *reinterpret_cast<float4*>(sB2 + (row0 + r) * LDH + col0) = d;
+        }
+      }
+    }
+    __syncthreads();
+    // ---- P3a: head.  4 lanes split K for one timestep, shuffle-reduce -----------------------
+    {
+      const int q = tid & 3;
+      constexpr int KQ = HP / 4;
+      for (int t = tid >> 2; t < TS; t += NTHREADS / 4) {
+        const float* h2 = sH2 + t * LDH + q * KQ;
+        const float* d2 = sB2 + t * LDH + q * KQ;
+        for (int jt = 0; jt < MP; jt += 4) {
+          float s[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+          for (int k = 0; k < KQ; ++k) {
+            const float hv = h2[k];
+            const float4 wv = *reinterpret_cast<const float4*>(sm + L.W2t + (q * KQ + k) * LDM + jt);
+            if (MODE == M_FVP) {
+              const float dv = d2[k];
+              const float4 vv = *reinterpret_cast<const float4*>(sm + L.V2t + (q * KQ + k) * LDM + jt);
+              s[0] = fmaf(hv, vv.x, s[0]); s[1] = fmaf(hv, vv.y, s[1]);
+              s[2] = fmaf(hv, vv.z, s[2]); s[3] = fmaf(hv, vv.w, s[3]);
+              s[0] = fmaf(dv, wv.x, s[0]); s[1] = fmaf(dv, wv.y, s[1]);
+              s[2] = fmaf(dv, wv.z, s[2]); s[3] = fmaf(dv, wv.w, s[3]);
+            } else {
+              s[0] = fmaf(hv, wv.x, s[0]); s[1] = fmaf(hv, wv.y, s[1]);
+              s[2] = fmaf(hv, wv.z, s[2]); s[3] = fmaf(hv, wv.w, s[3]);
+            }
+          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            s[c] += __shfl_xor_sync(0xffffffffu, s[c], 1);
+            s[c] += __shfl_xor_sync(0xffffffffu, s[c], 2);
+          }
+          if (q == 0) {
+            float o[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const int j = jt + c;
+              if (MODE == M_FVP) {
+                // u = fisher_j * (dy_j + vb2_j); rows past N contribute nothing
+                o[c] = (t < rows) ? sm[L.fisher + j] * (s[c] + sm[L.vb2 + j]) : 0.f;
+              } else {
+                o[c] = (s[c] + sm[L.b2 + j]) * sm[L.oscale + j] + sm[L.oshift + j];  // mu
+              }
+            }
+            *reinterpret_cast<float4*>(sU + t * LDM + jt) = make_float4(o[0], o[1], o[2], o[3]);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- P3b: Gaussian head, one thread per timestep ----------------------------------------
+    if (MODE != M_FVP) {
+      for (int t = tid; t < TS; t += NTHREADS) {
+        const bool valid = t < rows;
+        const long long gt = t0 + t;
+        float ss = 0.f, kl = 0.f, sum_ls = 0.f;
+        const bool need_ll = (MODE != M_FWD) || a.ll_out != nullptr;
+        for (int j = 0; j < m; ++j) {
+          const float mu = sU[t * LDM + j];
+          if (MODE == M_FWD && a.mean_out && valid) a.mean_out[gt * m + j] = mu;
+          if (MODE == M_GRAD && a.mean_out && valid) a.mean_out[gt * m + j] = mu;
+          if (need_ll) {
+            const float z = (sAct[t * LDM + j] - mu) / sm[L.sig + j];
+            ss = fmaf(z, z, ss);
+            sum_ls += sm[L.ls + j];
+            if (MODE == M_GRAD) sE[t * LDM + j] = z;  // stash z, finished below once LR is known
+          }
+          if (MODE == M_EVAL && valid) {
+            // gaussian_mlp.py:137-139, KL(old || new) per dimension
+            const float mo = ld_stream(a.old_mean + gt * m + j);
+            const float so = expf(sm[L.ols_ + j]), sn = sm[L.sig + j];
+            const float nr = (mo - mu) * (mo - mu) + so * so - sn * sn;
+            const float dr = 2.f * sn * sn + 1e-8f;
+            kl += nr / dr + sm[L.ls + j] - sm[L.ols_ + j];
+          }
+        }
+        // gaussian_mlp.py:107-109: (-0.5*sum z^2 + -sum log_std) + -0.5*m*log(2 pi)
+        const float ll = (-0.5f * ss + -sum_ls) + (float)(-0.5 * (double)m * 1.8378770664093453);
+        if ((MODE == M_FWD || MODE == M_GRAD) && a.ll_out && valid) a.ll_out[gt] = ll;
+        if (MODE == M_EVAL || MODE == M_GRAD) {
+          float lr = 1.f;
+          if (a.old_ll && valid) lr = expf(ll - ld_stream(a.old_ll + gt));
+          const float wv = (a.w && valid) ? ld_stream(a.w + gt) : 0.f;
+          const float c = valid ? lr * wv : 0.f;
+          sS0[t] = c;
+          if (MODE == M_EVAL) sS1[t] = valid ? kl : 0.f;
+          if (MODE == M_GRAD) {
+            for (int j = 0; j < m; ++j) {
+              const float z = sE[t * LDM + j];
+              const float sg = sm[L.sig + j];
+              sU[t * LDM + j] = c * (z / sg) * sm[L.oscale + j];  // dL/dy_j
+              sE[t * LDM + j] = c * (z * z - 1.f);                 // dL/dlog_std_j
+            }
+            for (int j = m; j < MP; ++j) { sU[t * LDM + j] = 0.f; sE[t * LDM + j] = 0.f; }
+          }
+        }
+      }
+      __syncthreads();
+      if (MODE == M_EVAL || MODE == M_GRAD) {
+        if (tid < 32) {  // fixed-order fp64 sums of the tile's per-timestep terms
+          double s0 = 0.0, s1 = 0.0;
+          for (int t = tid; t < TS; t += 32) { s0 += (double)sS0[t]; if (MODE == M_EVAL) s1 += (double)sS1[t]; }
+          s0 = warp_sum(s0);
+          if (MODE == M_EVAL) s1 = warp_sum(s1);
+          surr_acc += s0; kl_acc += s1;
+        }
+      }
+    }
+    if (BWD) {
+      // ---- P4: back through the head: gz2 = (U W2) * (1 - h2^2); gW2 += U^T H2 ---------------
+      {
+        float g[RT][4];
+#pragma unroll
+        for (int r = 0; r < RT; ++r) { g[r][0] = g[r][1] = g[r][2] = g[r][3] = 0.f; }
+        mm_acc<RT>(g, sU + row0 * LDM, LDM, sm + L.W2 + col0, LDH, MP);
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+          const float4 h = *reinterpret_cast<const float4*>(sH2 + (row0 + r) * LDH + col0);
+          float4 o = make_float4(g[r][0] * (1.f - h.x * h.x), g[r][1] * (1.f - h.y * h.y),
+                                 g[r][2] * (1.f - h.z * h.z), g[r][3] * (1.f - h.w * h.w));
+          *reinterpret_cast<float4*>(sB2 + (row0 + r) * LDH + col0) = o;
+          cb1[0] += o.x; cb1[1] += o.y; cb1[2] += o.z; cb1[3] += o.w;
+        }
+        if (own2.active)
+          wgrad_acc(acc2, sU, LDM, sH2, LDH, 4 * (own2.tile / NF), 4 * (own2.tile % NF), own2.grp,
+                    own2.G, TS);
+        if (tid < MP) {
+          float s = 0.f, e = 0.f;
+          for (int t = 0; t < TS; ++t) { s += sU[t * LDM + tid]; if (MODE == M_GRAD) e += sE[t * LDM + tid]; }
+          gb2acc += s; glsacc += e;
+        }
+      }
+      __syncthreads();
+      // ---- P5: gz1 = (GZ2 W1) * (1 - h1^2); gW1 += GZ2^T H1 -----------------------------------
+      {
+        float g[RT][4];
+#pragma unroll
+        for (int r = 0; r < RT; ++r) { g[r][0] = g[r][1] = g[r][2] = g[r][3] = 0.f; }
+        mm_acc<RT>(g, sB2 + row0 * LDH, LDH, sm + L.W1 + col0, LDH, HP);
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+          const float4 h = *reinterpret_cast<const float4*>(sH1 + (row0 + r) * LDH + col0);
+          float4 o = make_float4(g[r][0] * (1.f - h.x * h.x), g[r][1] * (1.f - h.y * h.y),
+                                 g[r][2] * (1.f - h.z * h.z), g[r][3] * (1.f - h.w * h.w));
+          *reinterpret_cast<float4*>(sB1 + (row0 + r) * LDH + col0) = o;
+          cb0[0] += o.x; cb0[1] += o.y; cb0[2] += o.z; cb0[3] += o.w;
+        }
+        if (own1.active)
+          wgrad_acc(acc1, sB2, LDH, sH1, LDH, 4 * (own1.tile / NF), 4 * (own1.tile % NF), own1.grp,
+                    own1.G, TS);
+      }
+      __syncthreads();
+      // ---- P6: gW0 += GZ1^T X -----------------------------------------------------------------
+#pragma unroll
+      for (int s = 0; s < W0SLOTS; ++s) {
+        const TileOwner own0(nt0, tid, s);
+        if (own0.active)
+          wgrad_acc(acc0[s], sB1, LDH, sX, LDX, 4 * (own0.tile / (NP / 4)), 4 * (own0.tile % (NP / 4)),
+                    own0.grp, own0.G, TS);
+      }
+    }
+  }
+
+  // ---- per-CTA results ------------------------------------------------------------------------
+  if ((MODE == M_EVAL || MODE == M_GRAD) && tid == 0) {
+    a.spartials[2 * blockIdx.x + 0] = surr_acc;
+    a.spartials[2 * blockIdx.x + 1] = kl_acc;
+  }
+  if (BWD) {
+    // Reduce thread-group partials in a FIXED order into a flat [d] staging vector (reusing the
+    // activation buffers), then one coalesced store of the CTA's partial gradient.
+    __syncthreads();
+    float* sG = sH1;  // H1,H2,B1,B2 are contiguous: 4*TS*LDH floats >= d (checked on host)
+    for (int i = tid; i < F.d; i += NTHREADS) sG[i] = 0.f;
+    __syncthreads();
+    const int h1 = F.h1, h2 = F.h2;
+    int gmax = NT;
+    {
+      const TileOwner o0(nt0, tid, 0);
+      gmax = max(gmax, max(o0.G, max(own1.G, own2.G)));
+    }
+    for (int g = 0; g < gmax; ++g) {
+#pragma unroll
+      for (int s = 0; s < W0SLOTS; ++s) {
+        const TileOwner own0(nt0, tid, s);
+        if (own0.active && own0.grp == g) {
+          const int o0 = 4 * (own0.tile / (NP / 4)), i0 = 4 * (own0.tile % (NP / 4));
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const int o = o0 + (e >> 2), i = i0 + (e & 3);
+            if (o < h1 && i < n) sG[F.oW0 + o * n + i] += acc0[s][e];
+          }
+        }
+      }
+      if (own1.active && own1.grp == g) {
+        const int o0 = 4 * (own1.tile / NF), i0 = 4 * (own1.tile % NF);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const int o = o0 + (e >> 2), i = i0 + (e & 3);
+          if (o < h2 && i < h1) sG[F.oW1 + o * h1 + i] += acc1[e];
+        }
+      }
+      if (own2.active && own2.grp == g) {
+        const int j0 = 4 * (own2.tile / NF), f0 = 4 * (own2.tile % NF);
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const int j = j0 + (e >> 2), f = f0 + (e & 3);
+          if (j < m && f < h2) sG[F.oW2 + j * h2 + f] += acc2[e];
+        }
+      }
+      if (tt == g) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int f = col0 + c;
+          if (f < h1) sG[F.ob0 + f] += cb0[c];
+          if (f < h2) sG[F.ob1 + f] += cb1[c];
+        }
+      }
+      __syncthreads();
+    }
+    if (tid < m) {
+      sG[F.ob2 + tid] = gb2acc;
+      sG[F.ols + tid] = glsacc;  // FVP: 0 here, the log_std block is filled by the finalize kernel
+    }
+    __syncthreads();
+    float* out = a.partials + (size_t)blockIdx.x * a.dstride;
+    for (int i = tid; i < F.d; i += NTHREADS) out[i] = sG[i];
+  }
+}
+
+}  // namespace pol
+
+// =========================================================================================
+// Second-stage reductions (fixed order => bit-reproducible run to run)
+// =========================================================================================
+namespace pol {
+
+// out[i] = sum_c partials[c][i] in fp64.  FVP: the log_std block [ols, d) is
+// count * h(sigma_j) * vec_j with h = 4 s (2 s - eps)/(2 s + eps)^2, s = sigma^2, eps = 1e-8
+// (second derivative of the KL expression of gaussian_mlp.py:137-139 at new == old).
+__global__ void reduce_partials_kernel(const float* __restrict__ partials, int nparts, int dstride,
+                                       int d, double* __restrict__ out, int ols, double count,
+                                       const float* __restrict__ params, const float* __restrict__ vec,
+                                       const int32_t* __restrict__ stop_flag) {
+  if (stop_flag && *stop_flag) return;
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= d) return;
+  if (vec && i >= ols) {
+    const double ls = (double)params[i];
+    const double s = exp(2.0 * ls), eps = 1e-8;
+    const double h = 4.0 * s * (2.0 * s - eps) / ((2.0 * s + eps) * (2.0 * s + eps));
+    out[i] = count * h * (double)vec[i];
+    return;
+  }
+  double acc = 0.0;
+  for (int c = 0; c < nparts; ++c) acc += (double)partials[(size_t)c * dstride + i];
+  out[i] = acc;
+}
+
+__global__ void reduce_scalars_kernel(const double* __restrict__ sp, int nparts, double* __restrict__ out,
+                                      int which /*bit0: surr, bit1: kl*/, double* __restrict__ out1) {
+  double s0 = 0.0, s1 = 0.0;
+  for (int c = threadIdx.x; c < nparts; c += 32) { s0 += sp[2 * c]; s1 += sp[2 * c + 1]; }
+  s0 = warp_sum(s0); s1 = warp_sum(s1);
+  if (threadIdx.x == 0) {
+    if (which & 1) out[0] = s0;
+    if (which & 2) (out1 ? out1 : out + 1)[0] = s1;
+  }
+}
+
+__global__ void clamp_log_std_kernel(float* p, int ols, int m, float lo) {
+  int j = threadIdx.x;
+  if (j < m) p[ols + j] = fmaxf(p[ols + j], lo);
+}
+
+template <int HP, int MODE, int W0SLOTS>
+int launch_one(mjrl_ctx* ctx, const Args& a, int grid, size_t smem, cudaStream_t s) {
+  auto kern = mlp_kernel<HP, MODE, W0SLOTS>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         ctx->max_smem_optin);
+    if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    attr_set = true;
+  }
+  kern<<<grid, NTHREADS, smem, s>>>(a);
+  return mjrl_check_launch("mlp_kernel");
+}
+
+template <int MODE>
+int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
+  const int hmax = a.h1 > a.h2 ? a.h1 : a.h2;
+  MJRL_REQUIRE(a.h1 > 0 && a.h2 > 0, MJRL_E_SHAPE, "policy: MLP kernels need two hidden layers");
+  MJRL_REQUIRE(hmax <= 64, MJRL_E_SHAPE, "policy: hidden sizes (%d,%d) > 64 are not supported yet",
+               a.h1, a.h2);
+  const int HP = hmax <= 32 ? 32 : 64;
+  const Layout L(HP, a.n, a.m, MODE);
+  const size_t smem = sizeof(float) * (size_t)L.total;
+  MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE,
+               "policy: obs_dim=%d act_dim=%d hidden=%d needs %zu B of shared memory (max %d)", a.n,
+               a.m, HP, smem, ctx->max_smem_optin);
+  const Flat F(a.n, a.m, a.h1, a.h2);
+  const bool bwd = MODE == M_GRAD || MODE == M_FVP;
+  if (bwd)
+    MJRL_REQUIRE(F.d <= 4 * L.TS * L.LDH, MJRL_E_SHAPE, "policy: d=%d exceeds the staging area", F.d);
+  const int nt0 = (HP / 4) * (L.NP / 4);
+  MJRL_REQUIRE(nt0 <= 2 * NTHREADS, MJRL_E_SHAPE, "policy: obs_dim=%d too large (fc0 tiles %d)", a.n, nt0);
+  const int slots = (bwd && nt0 > NTHREADS) ? 2 : 1;
+  const long long ntiles = (a.N + L.TS - 1) / L.TS;
+  int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
+  if (grid < 1) grid = 1;
+  *grid_out = grid;
+  a.dstride = (F.d + 31) & ~31;
+  if (bwd) {
+    a.partials = (float*)mjrl_scratch(ctx, sizeof(float) * (size_t)grid * a.dstride);
+    if (!a.partials) return MJRL_E_STATE;
+  }
+  if (MODE == M_EVAL || MODE == M_GRAD) {
+    a.spartials = (double*)mjrl_scratch2(ctx, sizeof(double) * 2 * grid);
+    if (!a.spartials) return MJRL_E_STATE;
+  }
+  if (HP == 32) return slots == 1 ? launch_one<32, MODE, 1>(ctx, a, grid, smem, s)
+                                  : launch_one<32, MODE, 2>(ctx, a, grid, smem, s);
+  return slots == 1 ? launch_one<64, MODE, 1>(ctx, a, grid, smem, s)
+                    : launch_one<64, MODE, 2>(ctx, a, grid, smem, s);
+}
+
+inline void fill_desc(Args& a, const mjrl_policy_desc* d) {
+  a.n = d->n; a.m = d->m; a.h1 = d->h1; a.h2 = d->h2;
+  a.in_shift = d->in_shift; a.in_scale = d->in_scale;
+  a.out_shift = d->out_shift; a.out_scale = d->out_scale;
+}
+
+}  // namespace pol
+
+// =========================================================================================
+// Affine policy (LinearModel.forward, gaussian_linear.py:171-175): mu = (W0 x~ + b0)*os + osh.
+// The zero-hidden-layer case of the same passes; d = m*n + 2m is tiny, so one thread per
+// timestep for the head and one thread per weight entry for the outer-product sums.
+// =========================================================================================
+namespace pol {
+
+constexpr int LIN_TS = 256;
+
+template <int MODE>
+__global__ void __launch_bounds__(LIN_TS) linpol_kernel(const Args a) {
+  extern __shared__ __align__(16) float sm[];
+  if (MODE == M_FVP && a.stop_flag && *a.stop_flag) return;
+  const int n = a.n, m = a.m, tid = threadIdx.x;
+  const int ns = n | 1, ms = m | 1;
+  const Flat F(n, m, 0, 0);
+  float* sX = sm;                      // [TS][ns]
+  float* sU = sX + LIN_TS * ns;        // [TS][ms]  dL/dy
+  float* sE = sU + LIN_TS * ms;        // [TS][ms]  dL/dlog_std terms
+  float* sW = sE + LIN_TS * ms;        // [m][n]
+  float* sV = sW + m * n;              // [m][n]  (FVP)
+  float* sG = sV + m * n;              // [d] accumulators
+  float* sp = sG + F.d;                // per-dim constants: b, vb, os, osh, sig, ls, ols, fisher (8*m)
+  float* sish = sp + 8 * m;            // [n]
+  float* siden = sish + n;             // [n]
+  __shared__ double sred[32];
+  const float* P = a.params;
+  for (int i = tid; i < m * n; i += LIN_TS) { sW[i] = P[i]; sV[i] = MODE == M_FVP ? a.vec[i] : 0.f; }
+  for (int i = tid; i < F.d; i += LIN_TS) sG[i] = 0.f;
+  for (int j = tid; j < m; j += LIN_TS) {
+    const float ls = P[F.ols + j], sg = expf(ls);
+    const float os = a.out_scale ? a.out_scale[j] : 1.f;
+    sp[j] = P[F.ob0 + j];
+    sp[m + j] = MODE == M_FVP ? a.vec[F.ob0 + j] : 0.f;
+    sp[2 * m + j] = os;
+    sp[3 * m + j] = a.out_shift ? a.out_shift[j] : 0.f;
+    sp[4 * m + j] = sg;
+    sp[5 * m + j] = ls;
+    sp[6 * m + j] = MODE == M_EVAL ? a.old_log_std[j] : 0.f;
+    sp[7 * m + j] = os * os * (2.f / (2.f * sg * sg + 1e-8f));
+  }
+  for (int i = tid; i < n; i += LIN_TS) {
+    sish[i] = a.in_shift ? a.in_shift[i] : 0.f;
+    siden[i] = (a.in_scale ? a.in_scale[i] : 1.f) + 1e-8f;
+  }
+  double surr_acc = 0.0, kl_acc = 0.0;
+  const long long ntiles = (a.N + LIN_TS - 1) / LIN_TS;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long t0 = tile * LIN_TS;
+    const int rows = (int)min((long long)LIN_TS, a.N - t0);
+    __syncthreads();
+    const float* src = a.obs + t0 * n;
+    for (int i = tid; i < rows * n; i += LIN_TS) {
+      int r = i / n, c = i - r * n;
+      sX[r * ns + c] = (ld_stream(src + i) - sish[c]) / siden[c];
+    }
+    __syncthreads();
+    const int t = tid;
+    const bool valid = t < rows;
+    const long long gt = t0 + t;
+    float surr_t = 0.f, kl_t = 0.f;
+    if (valid) {
+      float ss = 0.f, sum_ls = 0.f;
+      const float* x = sX + t * ns;
+      for (int j = 0; j < m; ++j) {
+        float y = sp[j], dy = sp[m + j];
+        for (int k = 0; k < n; ++k) {
+          y = fmaf(sW[j * n + k], x[k], y);
+          if (MODE == M_FVP) dy = fmaf(sV[j * n + k], x[k], dy);
+        }
+        if (MODE == M_FVP) { sU[t * ms + j] = sp[7 * m + j] * dy; continue; }
+        const float mu = y * sp[2 * m + j] + sp[3 * m + j];
+        if ((MODE == M_FWD || MODE == M_GRAD) && a.mean_out) a.mean_out[gt * m + j] = mu;
+        if (a.act) {
+          const float z = (ld_stream(a.act + gt * m + j) - mu) / sp[4 * m + j];
+          ss = fmaf(z, z, ss);
+          sum_ls += sp[5 * m + j];
+          if (MODE == M_GRAD) sE[t * ms + j] = z;
+        }
+        if (MODE == M_EVAL) {
+          const float mo = ld_stream(a.old_mean + gt * m + j);
+          const float so = expf(sp[6 * m + j]), sn = sp[4 * m + j];
+          kl_t += ((mo - mu) * (mo - mu) + so * so - sn * sn) / (2.f * sn * sn + 1e-8f) + sp[5 * m + j] - sp[6 * m + j];
+        }
+      }
+      if (MODE != M_FVP) {
+        const float ll = (-0.5f * ss + -sum_ls) + (float)(-0.5 * (double)m * 1.8378770664093453);
+        if ((MODE == M_FWD || MODE == M_GRAD) && a.ll_out) a.ll_out[gt] = ll;
+        if (MODE == M_EVAL || MODE == M_GRAD) {
+          const float lr = a.old_ll ? expf(ll - ld_stream(a.old_ll + gt)) : 1.f;
+          const float c = lr * (a.w ? ld_stream(a.w + gt) : 0.f);
+          surr_t = c;
+          if (MODE == M_GRAD)
+            for (int j = 0; j < m; ++j) {
+              const float z = sE[t * ms + j];
+              sU[t * ms + j] = c * (z / sp[4 * m + j]) * sp[2 * m + j];
+              sE[t * ms + j] = c * (z * z - 1.f);
+            }
+        }
+      }
+    } else if (MODE == M_GRAD || MODE == M_FVP) {
+      for (int j = 0; j < m; ++j) { sU[t * ms + j] = 0.f; sE[t * ms + j] = 0.f; }
+    }
+    if (MODE == M_EVAL || MODE == M_GRAD) {
+      double s0 = block_sum((double)surr_t, sred);
+      double s1 = MODE == M_EVAL ? block_sum((double)kl_t, sred) : 0.0;
+      if (tid == 0) { surr_acc += s0; kl_acc += s1; }
+    }
+    if (MODE == M_GRAD || MODE == M_FVP) {
+      __syncthreads();
+      for (int e = tid; e < m * n + 2 * m; e += LIN_TS) {
+        float s = 0.f;
+        if (e < m * n) {
+          const int j = e / n, k = e - j * n;
+          for (int r = 0; r < rows; ++r) s = fmaf(sU[r * ms + j], sX[r * ns + k], s);
+          sG[e] += s;
+        } else if (e < m * n + m) {
+          const int j = e - m * n;
+          for (int r = 0; r < rows; ++r) s += sU[r * ms + j];
+          sG[F.ob0 + j] += s;
+        } else if (MODE == M_GRAD) {
+          const int j = e - m * n - m;
+          for (int r = 0; r < rows; ++r) s += sE[r * ms + j];
+          sG[F.ols + j] += s;
+        }
+      }
+    }
+  }
+  if ((MODE == M_EVAL || MODE == M_GRAD) && tid == 0) {
+    a.spartials[2 * blockIdx.x] = surr_acc;
+    a.spartials[2 * blockIdx.x + 1] = kl_acc;
+  }
+  if (MODE == M_GRAD || MODE == M_FVP) {
+    __syncthreads();
+    float* out = a.partials + (size_t)blockIdx.x * a.dstride;
+    for (int i = tid; i < F.d; i += LIN_TS) out[i] = sG[i];
+  }
+}
+
+template <int MODE>
+int launch_linear(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
+  const Flat F(a.n, a.m, 0, 0);
+  const int ns = a.n | 1, ms = a.m | 1;
+  size_t fl = (size_t)LIN_TS * ns + 2 * (size_t)LIN_TS * ms + 2 * (size_t)a.m * a.n + F.d + 8 * a.m +
+              2 * a.n + 8;
+  size_t smem = sizeof(float) * fl + sizeof(double) * 40;
+  MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE, "linear policy: n=%d m=%d too large", a.n, a.m);
+  const long long ntiles = (a.N + LIN_TS - 1) / LIN_TS;
+  int grid = (int)(ntiles < ctx->sm_count * 2 ? ntiles : ctx->sm_count * 2);
+  if (grid < 1) grid = 1;
+  *grid_out = grid;
+  a.dstride = (F.d + 31) & ~31;
+  if (MODE == M_GRAD || MODE == M_FVP) {
+    a.partials = (float*)mjrl_scratch(ctx, sizeof(float) * (size_t)grid * a.dstride);
+    if (!a.partials) return MJRL_E_STATE;
+  }
+  if (MODE == M_EVAL || MODE == M_GRAD) {
+    a.spartials = (double*)mjrl_scratch2(ctx, sizeof(double) * 2 * grid);
+    if (!a.spartials) return MJRL_E_STATE;
+  }
+  auto kern = linpol_kernel<MODE>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
+  if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+  kern<<<grid, LIN_TS, smem, s>>>(a);
+  return mjrl_check_launch("linpol_kernel");
+}
+
+template <int MODE>
+int launch_any(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
+  if (a.h1 == 0 && a.h2 == 0) return launch_linear<MODE>(ctx, a, grid_out, s);
+  return launch_mode<MODE>(ctx, a, grid_out, s);
+}
+
+}  // namespace pol
+
+// =========================================================================================
+// (d) CG vector algebra, step-size rule;  (e) batched action sampling
+// =========================================================================================
+namespace pol {
+
+constexpr int CG_THREADS = 1024;
+
+// block-wide fp64 dot helper for the single-CTA CG kernels
+__device__ __forceinline__ double cta_sum_bcast(double v, double* red) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  double r = (l < nw) ? red[l] : 0.0;
+  r = warp_sum(r);
+  return r;  // every thread holds the total
+}
+
+__global__ void __launch_bounds__(CG_THREADS)
+cg_init_kernel(mjrl_cg_state st, long long d, const double* __restrict__ b, double b_scale) {
+  __shared__ double red[32];
+  double acc = 0.0;
+  for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
+    const double v = b[i] * b_scale;
+    st.x[i] = 0.0; st.r[i] = v; st.p[i] = v; st.p32[i] = (float)v;
+    acc = fma(v, v, acc);
+  }
+  const double rr = cta_sum_bcast(acc, red);
+  if (threadIdx.x == 0) {
+    st.scal[0] = rr; st.scal[1] = 0.0; st.scal[2] = 0.0; st.scal[3] = 0.0; st.scal[4] = rr;
+    st.flags[0] = 0; st.flags[1] = 0;
+  }
+}
+
+// cg_solve.py:10-20 with z = z_sum*inv_count + damping*p (npg_cg.py:74)
+__global__ void __launch_bounds__(CG_THREADS)
+cg_update_kernel(mjrl_cg_state st, long long d, double inv_count, double damping, double tol) {
+  __shared__ double red[32];
+  if (st.flags[0]) return;
+  const double rdotr = st.scal[0];
+  double pz = 0.0;
+  for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
+    const double p = st.p[i];
+    const double z = fma(st.z[i], inv_count, damping * p);
+    st.z[i] = z;
+    pz = fma(p, z, pz);
+  }
+  pz = cta_sum_bcast(pz, red);
+  const double v = rdotr / pz;
+  double nrr = 0.0;
+  for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
+    st.x[i] = fma(v, st.p[i], st.x[i]);
+    const double r = fma(-v, st.z[i], st.r[i]);
+    st.r[i] = r;
+    nrr = fma(r, r, nrr);
+  }
+  nrr = cta_sum_bcast(nrr, red);
+  const double mu = nrr / rdotr;
+  for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
+    const double p = fma(mu, st.p[i], st.r[i]);
+    st.p[i] = p; st.p32[i] = (float)p;
+  }
+  if (threadIdx.x == 0) {
+    st.scal[0] = nrr; st.scal[1] = pz; st.scal[2] = v; st.scal[3] = mu;
+    st.flags[1] += 1;
+    if (nrr < tol) st.flags[0] = 1;
+  }
+}
+
+__global__ void __launch_bounds__(CG_THREADS)
+npg_step_kernel(long long d, int m, const double* __restrict__ g, double g_scale,
+                const double* __restrict__ x, const float* __restrict__ curr, double delta,
+                double const_alpha, double alpha_scale, float min_log_std,
+                float* __restrict__ newp, double* __restrict__ scal) {
+  __shared__ double red[32];
+  double gx = 0.0;
+  for (long long i = threadIdx.x; i < d; i += CG_THREADS) gx = fma(g[i] * g_scale, x[i], gx);
+  gx = cta_sum_bcast(gx, red);
+  double alpha, nstep;
+  if (const_alpha >= 0.0) { alpha = const_alpha; nstep = alpha * alpha * gx; }        // npg_cg.py:130-132
+  else { nstep = delta; alpha = sqrt(fabs(delta / (gx + 1e-20))); }                     // npg_cg.py:133-135
+  const double a = alpha * alpha_scale;
+  for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
+    float v = (float)((double)curr[i] + a * x[i]);
+    if (i >= d - m) v = fmaxf(v, min_log_std);  // set_param_values clamp, gaussian_mlp.py:75-76
+    newp[i] = v;
+  }
+  if (threadIdx.x == 0) { scal[0] = alpha; scal[1] = gx; scal[2] = nstep; scal[3] = a; }
+}
+
+// ---- Philox4x32-10 + Box-Muller ------------------------------------------------------------
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+  const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+  const uint32_t n0 = hi1 ^ c[1] ^ k0, n1 = lo1, n2 = hi0 ^ c[3] ^ k1, n3 = lo0;
+  c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+}
+__device__ __forceinline__ void philox4x32_10(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) { philox_round(c, k0, k1); k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+}
+
+// act[b][j] = mean[b][j] + exp(log_std_j) * eps, counter = (row + offset, j/4), key = seed
+__global__ void act_noise_kernel(const float* __restrict__ mean, const float* __restrict__ params, int ols,
+                                 int m, long long B, unsigned long long seed, unsigned long long offset,
+                                 float* __restrict__ act) {
+  const long long nblk = (m + 3) / 4;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = B * nblk, stride = (long long)gridDim.x * blockDim.x;
+  for (; i < total; i += stride) {
+    const long long b = i / nblk;
+    const int jb = (int)(i - b * nblk);
+    const unsigned long long row = (unsigned long long)b + offset;
+    uint32_t c[4] = {(uint32_t)row, (uint32_t)(row >> 32), (uint32_t)jb, 0u};
+    philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+    float e[4];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const float u1 = ((float)c[2 * h] + 0.5f) * 2.3283064365386963e-10f;   // (0,1)
+      const float u2 = ((float)c[2 * h + 1] + 0.5f) * 2.3283064365386963e-10f;
+      const float rad = sqrtf(-2.f * logf(u1));
+      float sn, cs;
+      sincospif(2.f * u2, &sn, &cs);
+      e[2 * h] = rad * cs; e[2 * h + 1] = rad * sn;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int j = jb * 4 + q;
+      if (j < m) act[b * m + j] = mean[b * m + j] + expf(params[ols + j]) * e[q];
+    }
+  }
+}
+
+}  // namespace pol
+
+// =========================================================================================
+// C-ABI entry points (include/mjrl_b200.h)
+// =========================================================================================
+using namespace pol;
+
+static int check_desc(const mjrl_policy_desc* d, const char* who) {
+  MJRL_REQUIRE(d != nullptr, MJRL_E_ARG, "%s: null policy description", who);
+  MJRL_REQUIRE(d->n > 0 && d->m > 0, MJRL_E_ARG, "%s: bad obs/act dims %d/%d", who, d->n, d->m);
+  MJRL_REQUIRE((d->h1 > 0 && d->h2 > 0) || (d->h1 == 0 && d->h2 == 0), MJRL_E_SHAPE,
+               "%s: hidden sizes (%d,%d): exactly two hidden layers, or none", who, d->h1, d->h2);
+  return 0;
+}
+
+extern "C" {
+
+int64_t mjrl_policy_param_count(const mjrl_policy_desc* d) {
+  if (!d || d->n <= 0 || d->m <= 0 || d->h1 < 0 || d->h2 < 0) return -1;
+  return Flat(d->n, d->m, d->h1, d->h2).d;
+}
+
+int mjrl_policy_clamp_log_std(mjrl_ctx* ctx, const mjrl_policy_desc* desc, float* params,
+                              float min_log_std, void* stream) {
+  int rc = check_desc(desc, "clamp_log_std");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params, MJRL_E_ARG, "clamp_log_std: null pointer");
+  MJRL_REQUIRE(desc->m <= 1024, MJRL_E_SHAPE, "clamp_log_std: act_dim %d > 1024", desc->m);
+  const Flat F(desc->n, desc->m, desc->h1, desc->h2);
+  clamp_log_std_kernel<<<1, ((desc->m + 31) / 32) * 32, 0, (cudaStream_t)stream>>>(params, F.ols, desc->m, min_log_std);
+  return mjrl_check_launch("clamp_log_std");
+}
+
+int mjrl_policy_forward(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                        const float* obs, const float* act, int64_t N, float* mean_out,
+                        float* ll_out, void* stream) {
+  int rc = check_desc(desc, "policy_forward");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params && N >= 0, MJRL_E_ARG, "policy_forward: bad argument");
+  if (N == 0) return 0;
+  MJRL_REQUIRE(obs && (mean_out || ll_out), MJRL_E_ARG, "policy_forward: null pointer");
+  MJRL_REQUIRE(!ll_out || act, MJRL_E_ARG, "policy_forward: ll_out needs act");
+  Args a = {};
+  fill_desc(a, desc);
+  a.params = params; a.obs = obs; a.act = ll_out ? act : nullptr; a.N = N;
+  a.mean_out = mean_out; a.ll_out = ll_out;
+  int grid;
+  return launch_any<M_FWD>(ctx, a, &grid, (cudaStream_t)stream);
+}
+
+int mjrl_policy_eval(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                     const float* obs, const float* act, const float* w, const float* old_ll,
+                     const float* old_mean, const float* old_log_std, int64_t N, double* sums2,
+                     void* stream) {
+  int rc = check_desc(desc, "policy_eval");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params && obs && act && old_ll && old_mean && old_log_std && sums2 && N > 0,
+               MJRL_E_ARG, "policy_eval: bad argument");
+  Args a = {};
+  fill_desc(a, desc);
+  a.params = params; a.obs = obs; a.act = act; a.w = w; a.old_ll = old_ll; a.old_mean = old_mean;
+  a.old_log_std = old_log_std; a.N = N;
+  int grid;
+  cudaStream_t s = (cudaStream_t)stream;
+  rc = launch_any<M_EVAL>(ctx, a, &grid, s);
+  if (rc) return rc;
+  reduce_scalars_kernel<<<1, 32, 0, s>>>(a.spartials, grid, sums2, 3, nullptr);
+  return mjrl_check_launch("policy_eval reduce");
+}
+
+int mjrl_policy_grad(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                     const float* obs, const float* act, const float* w, const float* old_ll,
+                     int64_t N, double* grad_sum, double* surr_sum, float* ll_out, float* mean_out,
+                     void* stream) {
+  int rc = check_desc(desc, "policy_grad");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params && obs && act && w && grad_sum && N > 0, MJRL_E_ARG,
+               "policy_grad: bad argument");
+  Args a = {};
+  fill_desc(a, desc);
+  a.params = params; a.obs = obs; a.act = act; a.w = w; a.old_ll = old_ll; a.N = N;
+  a.ll_out = ll_out; a.mean_out = mean_out;
+  int grid;
+  cudaStream_t s = (cudaStream_t)stream;
+  rc = launch_any<M_GRAD>(ctx, a, &grid, s);
+  if (rc) return rc;
+  const Flat F(desc->n, desc->m, desc->h1, desc->h2);
+  reduce_partials_kernel<<<(F.d + 127) / 128, 128, 0, s>>>(a.partials, grid, a.dstride, F.d, grad_sum,
+                                                            F.ols, 0.0, nullptr, nullptr, nullptr);
+  if (surr_sum) reduce_scalars_kernel<<<1, 32, 0, s>>>(a.spartials, grid, surr_sum, 1, nullptr);
+  return mjrl_check_launch("policy_grad reduce");
+}
+
+int mjrl_policy_fvp(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                    const float* obs, int64_t N, const float* vec, double* fvp_sum,
+                    const int32_t* stop_flag, void* stream) {
+  int rc = check_desc(desc, "policy_fvp");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params && obs && vec && fvp_sum && N > 0, MJRL_E_ARG, "policy_fvp: bad argument");
+  Args a = {};
+  fill_desc(a, desc);
+  a.params = params; a.obs = obs; a.vec = vec; a.N = N; a.stop_flag = stop_flag;
+  int grid;
+  cudaStream_t s = (cudaStream_t)stream;
+  rc = launch_any<M_FVP>(ctx, a, &grid, s);
+  if (rc) return rc;
+  const Flat F(desc->n, desc->m, desc->h1, desc->h2);
+  reduce_partials_kernel<<<(F.d + 127) / 128, 128, 0, s>>>(a.partials, grid, a.dstride, F.d, fvp_sum,
+                                                            F.ols, (double)N, params, vec, stop_flag);
+  return mjrl_check_launch("policy_fvp reduce");
+}
+
+int mjrl_cg_init(mjrl_ctx* ctx, const mjrl_cg_state* st, int64_t d, const double* b, double b_scale,
+                 void* stream) {
+  MJRL_REQUIRE(ctx && st && b && d > 0, MJRL_E_ARG, "cg_init: bad argument");
+  MJRL_REQUIRE(st->x && st->r && st->p && st->z && st->scal && st->p32 && st->flags, MJRL_E_ARG,
+               "cg_init: null state array");
+  cg_init_kernel<<<1, CG_THREADS, 0, (cudaStream_t)stream>>>(*st, d, b, b_scale);
+  return mjrl_check_launch("cg_init");
+}
+
+int mjrl_cg_update(mjrl_ctx* ctx, const mjrl_cg_state* st, int64_t d, double inv_count, double damping,
+                   double residual_tol, void* stream) {
+  MJRL_REQUIRE(ctx && st && d > 0, MJRL_E_ARG, "cg_update: bad argument");
+  cg_update_kernel<<<1, CG_THREADS, 0, (cudaStream_t)stream>>>(*st, d, inv_count, damping, residual_tol);
+  return mjrl_check_launch("cg_update");
+}
+
+int mjrl_npg_step(mjrl_ctx* ctx, int64_t d, int32_t m, const double* g, double g_scale,
+                  const double* x, const float* curr, double delta, double const_alpha,
+                  double alpha_scale, float min_log_std, float* new_params, double* scal4,
+                  void* stream) {
+  MJRL_REQUIRE(ctx && g && x && curr && new_params && scal4 && d > 0 && m > 0 && m <= d, MJRL_E_ARG,
+               "npg_step: bad argument");
+  npg_step_kernel<<<1, CG_THREADS, 0, (cudaStream_t)stream>>>(d, m, g, g_scale, x, curr, delta, const_alpha,
+                                                               alpha_scale, min_log_std, new_params, scal4);
+  return mjrl_check_launch("npg_step");
+}
+
+int mjrl_policy_act(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                    const float* obs, int64_t B, uint64_t seed, uint64_t offset, float* act_out,
+                    float* mean_out, void* stream) {
+  int rc = check_desc(desc, "policy_act");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params && obs && act_out && mean_out && B > 0, MJRL_E_ARG, "policy_act: bad argument");
+  rc = mjrl_policy_forward(ctx, desc, params, obs, nullptr, B, mean_out, nullptr, stream);
+  if (rc) return rc;
+  const Flat F(desc->n, desc->m, desc->h1, desc->h2);
+  const long long total = B * ((desc->m + 3) / 4);
+  int grid = (int)((total + 255) / 256);
+  if (grid > ctx->sm_count * 8) grid = ctx->sm_count * 8;
+  act_noise_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(mean_out, params, F.ols, desc->m, B, seed, offset, act_out);
+  return mjrl_check_launch("policy_act");
+}
+
+}  // extern "C"

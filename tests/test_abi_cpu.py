@@ -42,3 +42,24 @@ def test_product_package_never_imports_oracle():
             if f.endswith(".py"):
                 src = open(os.path.join(dp, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, os.path.join(dp, f)
+
+
+def test_policy_init_matches_reference_rng_order(golden):
+    """Seed-for-seed identical initial parameters (gaussian_mlp.py:27-57); host only."""
+    import numpy as np
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.policies.gaussian_linear import LinearPolicy
+    from mjrl_b200.utils.gym_env import EnvSpec
+    g = golden
+    spec = EnvSpec(g["n"], g["m"], g["horizon"], 1)
+    pol = MLP(spec, hidden_sizes=g["hidden"], seed=123) if g["hidden"] else LinearPolicy(spec, seed=123)
+    np.testing.assert_array_equal(pol.get_param_values(), g["init_params"])
+    assert pol.d == g["init_params"].size
+    # clamp semantics of set_param_values (gaussian_mlp.py:75-76) and pickling without handles
+    import pickle, copy
+    p = pol.get_param_values(); p[-1] = -7.0
+    pol.set_param_values(p)
+    assert pol.get_param_values()[-1] == -3.0 and pol.get_old_param_values()[-1] == -3.0
+    q = pickle.loads(pickle.dumps(pol)); c = copy.deepcopy(pol)
+    np.testing.assert_array_equal(q.get_param_values(), pol.get_param_values())
+    np.testing.assert_array_equal(c.get_param_values(), pol.get_param_values())

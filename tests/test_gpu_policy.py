@@ -1,0 +1,174 @@
+"""GPU parity of the fused Gaussian-policy passes and the NPG/TRPO/DAPG updates against the
+reference's outputs (tests/golden) and the oracle.
+
+Tolerances (north_star): policy gradient, FVP and step direction within 1e-4 relative (fp32);
+identical line-search decisions.  The 10-iteration CG direction follows the protocol of
+SURVEY.md H1: it must be no further from the fp64 truth than max(1e-4, the reference's own
+distance)."""
+import numpy as np
+import pytest
+
+from conftest import batch_of, rel_l2
+from mjrl_b200.utils import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def make_policy(g, params=None):
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.policies.gaussian_linear import LinearPolicy
+    from mjrl_b200.utils.gym_env import EnvSpec
+    spec = EnvSpec(g["n"], g["m"], g["horizon"], 1)
+    pol = MLP(spec, hidden_sizes=g["hidden"], seed=123) if g["hidden"] else LinearPolicy(spec, seed=123)
+    np.testing.assert_array_equal(pol.get_param_values(), g["init_params"])
+    if g["transforms"]:
+        pol.model.set_transformations(**g["transforms"])
+        pol.old_model.set_transformations(**g["transforms"])
+    pol.set_param_values((g["params"] if params is None else params).copy(), True, True)
+    return pol
+
+
+def prepared_paths(g):
+    p1 = syn.flat_to_paths(batch_of(g, "b1_"))
+    off = g["b1_path_offsets"]
+    for i, p in enumerate(p1):
+        p["advantages"] = g["b1_adv"][off[i]:off[i + 1]]
+        p["returns"] = g["b1_returns"][off[i]:off[i + 1]]
+    return p1
+
+
+def agent(cls, g, pol, **kw):
+    from mjrl_b200.baselines.linear_baseline import LinearBaseline
+    from mjrl_b200.utils.gym_env import EnvSpec
+    return cls(None, pol, LinearBaseline(EnvSpec(g["n"], g["m"], g["horizon"], 1)), **kw)
+
+
+def test_forward_surrogate_gradient_fvp(golden):
+    from mjrl_b200.algos.npg_cg import NPG
+    g = golden
+    b1 = batch_of(g, "b1_")
+    obs, act, adv = b1["observations"], b1["actions"], g["b1_adv_white"]
+    pol = make_policy(g)
+    ag = agent(NPG, g, pol)
+    LL = pol.log_likelihood(obs, act)
+    assert rel_l2(LL, g["LL"]) < 1e-5
+    assert rel_l2(pol.new_dist_info(obs, act)[1].numpy(), g["mean"]) < 1e-5
+    assert abs(float(ag.CPI_surrogate(obs, act, adv)) - g["surr_before"]) < 1e-6
+    assert abs(float(ag.kl_old_new(obs, act))) < 1e-7
+    grad = ag.flat_vpg(obs, act, adv)
+    assert grad.dtype == np.float32 and grad.shape == g["vpg_grad"].shape
+    assert rel_l2(grad, g["vpg_grad"]) < TOL
+    hv = ag.HVP(obs, act, g["vpg_grad"], 1e-4)
+    assert rel_l2(hv, g["hvp_of_grad"]) < TOL
+    assert rel_l2(ag.HVP(obs, act, g["vpg_grad"], 0.0), g["hvp_of_grad_nodamp"]) < TOL
+    # new != old: likelihood ratio, KL and the LR-weighted gradient
+    pol.set_param_values(g["pert_params"].copy(), set_new=True, set_old=False)
+    assert abs(float(ag.CPI_surrogate(obs, act, adv)) - g["pert_surr"]) < 1e-5 * max(1, abs(g["pert_surr"]))
+    assert abs(float(ag.kl_old_new(obs, act)) - g["pert_kl"]) < 1e-4 * g["pert_kl"] + 1e-8
+    assert rel_l2(ag.flat_vpg(obs, act, adv), g["pert_vpg"]) < TOL
+    assert rel_l2(pol.log_likelihood(obs, act), g["pert_LL"]) < 1e-5
+
+
+def test_npg_update_and_cg_protocol(golden):
+    from mjrl_b200.algos.npg_cg import NPG
+    from oracle import mjrl_oracle as O
+    g = golden
+    p1 = prepared_paths(g)
+    pol = make_policy(g)
+    ag = agent(NPG, g, pol, normalized_step_size=0.01)
+    trace = []
+    stats = ag.train_from_paths(p1, cg_trace=trace)
+    R = [sum(p["rewards"]) for p in p1]
+    np.testing.assert_allclose(stats, [np.mean(R), np.std(R), np.amin(R), np.amax(R)], rtol=1e-10)
+    # (ii) CG iterates k = 1..5 within 1e-4 of the reference
+    for k in (1, 2, 3, 5):
+        if k <= len(trace):
+            assert rel_l2(trace[k - 1], g["cg_k%d" % k]) < TOL, k
+    # (iii) k = 10: no further from the fp64 truth than the reference (or 1e-4)
+    b1 = batch_of(g, "b1_")
+    opol = O.GaussianPolicy(g["n"], g["m"], g["hidden"], g["params"], **(g["transforms"] or {}))
+    tp = O.TruthPolicy(opol)
+    xs = O.truth_cg(tp, b1["observations"], tp.vpg(b1["observations"], b1["actions"], g["b1_adv_white"]))
+    d_ref = rel_l2(g["cg_k10"], xs)
+    d_new = rel_l2(trace[-1], xs)
+    assert d_new <= max(TOL, 1.05 * d_ref), (d_new, d_ref)
+    # committed parameters: the step must agree with the reference's to the same floor
+    step_ref = g["npg_new_params"].astype(np.float64) - g["params"]
+    step_new = pol.get_param_values().astype(np.float64) - g["params"]
+    assert rel_l2(step_new, step_ref) < max(TOL, 2.5 * d_ref) + 1e-6
+    np.testing.assert_array_equal(pol.get_param_values(), pol.get_old_param_values())
+    assert abs(ag.last_update["kl_dist"] - 0.005) < 0.004
+
+
+def test_trpo_line_search_decisions(golden):
+    from mjrl_b200.algos.trpo import TRPO
+    g = golden
+    p1 = prepared_paths(g)
+    # stage 1: the reference's own direction through OUR step rule + line search
+    pol = make_policy(g)
+    ag = agent(TRPO, g, pol, kl_dist=0.01)
+    ag.train_from_paths(p1, direction_override=g["cg_k10"], verbose=False)
+    trials = ag.last_update["trials"]
+    margin = min(abs(t[0] - 0.01) / 0.01 for t in trials)
+    if margin > 1e-3:   # decisions are only meaningful away from the threshold
+        assert sum(1 for t in trials if not t[2]) == int(g["trpo_backtracks"])
+        step_ref = g["trpo_new_params"].astype(np.float64) - g["params"]
+        step_new = pol.get_param_values().astype(np.float64) - g["params"]
+        assert rel_l2(step_new, step_ref) < TOL
+    # stage 2: end to end
+    pol = make_policy(g)
+    ag = agent(TRPO, g, pol, kl_dist=0.01)
+    ag.train_from_paths(p1, verbose=False)
+    assert ag.last_update["kl_dist"] < 0.01
+    assert len(ag.last_update["trials"]) <= 100
+
+
+def test_dapg_and_reinforce_updates(golden):
+    from mjrl_b200.algos.dapg import DAPG
+    from mjrl_b200.algos.batch_reinforce import BatchREINFORCE
+    from oracle import mjrl_oracle as O
+    g = golden
+    p1 = prepared_paths(g)
+    pol = make_policy(g)
+    ag = agent(BatchREINFORCE, g, pol, learn_rate=0.01)
+    ag.train_from_paths(p1)
+    step_ref = g["reinforce_new_params"].astype(np.float64) - g["params"]
+    assert rel_l2(pol.get_param_values().astype(np.float64) - g["params"], step_ref) < TOL
+
+    pol = make_policy(g)
+    demo = syn.flat_to_paths(batch_of(g, "demo_"))
+    ag = agent(DAPG, g, pol, demo_paths=demo, kl_dist=0.01)
+    ag.train_from_paths(p1)
+    assert ag.iter_count == 1.0
+    # noise floor of the reference's own CG on this gradient (oracle fp32 vs fp64 truth)
+    opol = O.GaussianPolicy(g["n"], g["m"], g["hidden"], g["params"], **(g["transforms"] or {}))
+    oo = O.dapg_update(opol, prepared_paths(g), demo, kl_dist=0.01)
+    tp = O.TruthPolicy(O.GaussianPolicy(g["n"], g["m"], g["hidden"], g["params"], **(g["transforms"] or {})))
+    b1 = batch_of(g, "b1_")
+    xs = O.truth_cg(tp, b1["observations"], oo["vpg_grad"].astype(np.float64))
+    d_ref = rel_l2(oo["npg_grad"], xs)
+    step_ref = g["dapg_new_params"].astype(np.float64) - g["params"]
+    step_new = pol.get_param_values().astype(np.float64) - g["params"]
+    assert rel_l2(step_new, step_ref) < max(TOL, 2.5 * d_ref) + 1e-6
+
+
+def test_batched_actions_philox():
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.utils.gym_env import EnvSpec
+    pol = MLP(EnvSpec(11, 3, 1000, 1), hidden_sizes=(64, 64), seed=7)
+    pol.set_param_values(np.concatenate([pol.get_param_values()[:-3], [-0.3, 0.1, 0.4]]).astype(np.float32))
+    rng = np.random.default_rng(0)
+    obs = rng.standard_normal((20000, 11)).astype(np.float32)
+    a1, m1 = pol.get_action_batch(obs, seed=5, offset=0)
+    a2, m2 = pol.get_action_batch(obs, seed=5, offset=0)
+    a3, _ = pol.get_action_batch(obs, seed=6, offset=0)
+    a1, m1, a2, a3 = a1.cpu().numpy(), m1.cpu().numpy(), a2.cpu().numpy(), a3.cpu().numpy()
+    np.testing.assert_array_equal(a1, a2)               # counter-based: reproducible
+    assert np.abs(a1 - a3).max() > 0.1                   # keyed by seed
+    eps = (a1 - m1) / np.exp([-0.3, 0.1, 0.4])
+    assert abs(eps.mean()) < 0.02 and abs(eps.std() - 1) < 0.02
+    assert abs(np.corrcoef(eps[:, 0], eps[:, 1])[0, 1]) < 0.03
+    # exact parity on the mean with the single-observation API (gaussian_mlp.py:92-98)
+    act, info = pol.get_action(obs[3].astype(np.float64))
+    np.testing.assert_allclose(info["mean"], m1[3], rtol=1e-6, atol=1e-7)
