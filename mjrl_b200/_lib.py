@@ -75,6 +75,7 @@ class Context:
         self.h = h
         self.device = int(device)
         self.sm_count = self.lib.mjrl_ctx_sm_count(self.h)
+        self.launches = 0   # kernels launched through this context (bench.py's gpu_launches)
 
     def close(self):
         if getattr(self, "h", None):
@@ -89,7 +90,13 @@ class Context:
 
     def call(self, name, *args):
         check(getattr(self.lib, name)(self.h, *args), name)
+        self.launches += KERNELS_PER_CALL.get(name, 1)
 
+
+# kernels each entry point launches (csrc/*.cu), for the launch count bench.py reports
+KERNELS_PER_CALL = {"mjrl_moments": 4, "mjrl_path_return_stats": 2, "mjrl_linbase_gram": 2,
+                    "mjrl_policy_eval": 2, "mjrl_policy_grad": 3, "mjrl_policy_fvp": 2,
+                    "mjrl_policy_act": 2}
 
 _ctx = {}
 

@@ -92,11 +92,11 @@ class BatchREINFORCE:
             self.logger.log_kv('time_sampling', timer.time() - ts)
         self.seed = self.seed + N if self.seed is not None else self.seed
 
-        batch = batch_for(paths)
+        batch = paths if isinstance(paths, PathBatch) else batch_for(paths)
         process_samples.returns_on_device(batch, gamma)
         b = process_samples.baseline_values_on_device(batch, self.baseline)
         process_samples.advantages_on_device(batch, b, gamma, gae_lambda)
-        eval_statistics = self.train_from_paths(paths)
+        eval_statistics = self.train_from_paths(batch)
         eval_statistics.append(N)
         if self.save_logs:
             ts = timer.time()
@@ -113,7 +113,7 @@ class BatchREINFORCE:
             ar = self._engine().dist.allreduce if self._engine().dist.world > 1 else None
             return self.baseline.fit_batch(batch, return_errors=return_errors, allreduce=ar)
         batch.scatter("returns", batch.returns)
-        return self.baseline.fit(paths, return_errors=return_errors)
+        return self.baseline.fit(batch.paths, return_errors=return_errors)
 
     # ---- shared front half of every train_from_paths -----------------------------------------
     def _prepare(self, paths):
@@ -175,6 +175,7 @@ class BatchREINFORCE:
         return base_stats
 
     def _log_success(self, paths):
+        if isinstance(paths, PathBatch): paths = paths.paths
         try:
             self.env.env.env.evaluate_success(paths, self.logger)
         except Exception:

@@ -729,7 +729,7 @@ int launch_linear(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
   size_t fl = (size_t)LIN_TS * ns + 2 * (size_t)LIN_TS * ms + 2 * (size_t)a.m * a.n + F.d + 8 * a.m +
               2 * a.n + 8;
   size_t smem = sizeof(float) * fl + sizeof(double) * 40;
-  MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE, "linear policy: n=%d m=%d too large", a.n, a.m);
+  MJRL_REQUIRE(smem + 1024 <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE, "linear policy: n=%d m=%d too large", a.n, a.m);
   const long long ntiles = (a.N + LIN_TS - 1) / LIN_TS;
   int grid = (int)(ntiles < ctx->sm_count * 2 ? ntiles : ctx->sm_count * 2);
   if (grid < 1) grid = 1;
@@ -744,8 +744,10 @@ int launch_linear(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
     if (!a.spartials) return MJRL_E_STATE;
   }
   auto kern = linpol_kernel<MODE>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
-  if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+  }
   kern<<<grid, LIN_TS, smem, s>>>(a);
   return mjrl_check_launch("linpol_kernel");
 }
