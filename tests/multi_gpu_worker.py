@@ -1,0 +1,55 @@
+"""Run under torchrun (one rank per GPU): sharded NPG update must equal the single-GPU update.
+Used by tests/test_gpu_multi.py; rank 0 prints 'MULTI_OK <rel>'."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from conftest import load_golden, batch_of, rel_l2  # noqa: E402
+from mjrl_b200.sharding import init_distributed, shard_paths  # noqa: E402
+from mjrl_b200.utils import synthetic as syn  # noqa: E402
+from mjrl_b200.utils.gym_env import EnvSpec  # noqa: E402
+from mjrl_b200.policies.gaussian_mlp import MLP  # noqa: E402
+from mjrl_b200.baselines.linear_baseline import LinearBaseline  # noqa: E402
+from mjrl_b200.algos.npg_cg import NPG  # noqa: E402
+from mjrl_b200.algos.engine import Dist  # noqa: E402
+from mjrl_b200.batch import drop_cache  # noqa: E402
+
+
+def run(world_mode):
+    g = load_golden("c3_hopper_mid")
+    spec = EnvSpec(g["n"], g["m"], g["horizon"], 1)
+    pol = MLP(spec, hidden_sizes=g["hidden"], seed=123)
+    pol.model.set_transformations(**g["transforms"]); pol.old_model.set_transformations(**g["transforms"])
+    pol.set_param_values(g["params"].copy())
+    base = LinearBaseline(spec)
+    base._coeffs = g["fit0_coeffs"].copy()
+    paths = syn.flat_to_paths(batch_of(g, "b1_"))
+    ag = NPG(None, pol, base, normalized_step_size=0.01)
+    if world_mode:
+        ag.dist = Dist()
+        paths = shard_paths(paths, ag.dist.rank, ag.dist.world)
+    else:
+        ag.dist = Dist.__new__(Dist); ag.dist.td = None; ag.dist.world = 1; ag.dist.rank = 0; ag.dist.calls = 0
+        ag.dist.group = None
+    drop_cache()
+    ag.train_step(len(paths), gamma=g["gamma"], gae_lambda=g["gae_lambda"], paths=paths)
+    return pol.get_param_values().astype(np.float64) - g["params"], np.asarray(base._coeffs), g
+
+
+if __name__ == "__main__":
+    rank, world, local = init_distributed("nccl")
+    torch.cuda.set_device(local)
+    step_multi, coef_multi, g = run(True)
+    if rank == 0:
+        step_one, coef_one, _ = run(False)
+        r_step, r_coef = rel_l2(step_multi, step_one), rel_l2(coef_multi, coef_one)
+        ok = r_step < 1e-4 and r_coef < 1e-6
+        print("MULTI_%s world=%d step_rel=%.3e coef_rel=%.3e" % ("OK" if ok else "FAIL", world, r_step, r_coef))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
