@@ -12,6 +12,8 @@
 // intermediate stays in shared memory / registers, and nothing but per-CTA partial sums is
 // written back: algorithmic bytes 4n (FVP), 4n+8m+12 (grad), 4n+8m+12 (eval) per timestep.
 // These passes are fp32-FMA bound, not HBM bound.
+#include <stdlib.h>
+
 #include "policy_tile.cuh"
 
 namespace pol {
@@ -42,14 +44,17 @@ struct Args {
 
 // Shared-memory carve-up (offsets in floats), identical on host and device.
 struct Layout {
-  int TS, LDH, NP, LDX, MP, LDM;
+  int TS, LDH, LDW, NP, LDX, MP, LDM;
   int X, H1, H2, B1, B2, U, E, ACT, S0, S1;
   int W0t, b0, W1t, b1, W2t, b2, W1, W2, V0t, vb0, V1t, vb1, V2t, vb2;
   int ishift, iden, oscale, oshift, sig, ls, ols_, fisher;
   int total;
-  __host__ __device__ Layout(int HP, int n, int m, int mode) {
+  // mma: tensor-core path.  obs width padded to 8 (k-steps of the m16n8k8 MMA), k-major weight
+  // stride HP+8 (= 8 mod 32) so B-fragment loads are conflict free; activations keep HP+4 (= 4 mod 8).
+  __host__ __device__ Layout(int HP, int n, int m, int mode, bool mma) {
     const int NF = HP / 4, NT = NTHREADS / NF;
-    TS = RT * NT; LDH = HP + 4; NP = round4(n); LDX = NP + 4; MP = round4(m); LDM = MP + 4;
+    TS = RT * NT; LDH = HP + 4; LDW = mma ? HP + 8 : HP + 4;
+    NP = mma ? ((n + 7) & ~7) : round4(n); LDX = NP + 4; MP = round4(m); LDM = MP + 4;
     int o = 0;
     auto take = [&](int cnt) { int r = o; o += (cnt + 3) & ~3; return r; };
     X = take(TS * LDX);
@@ -60,11 +65,11 @@ struct Layout {
     E = mode == M_GRAD ? take(TS * LDM) : 0;
     ACT = mode != M_FVP ? take(TS * LDM) : 0;
     S0 = take(TS); S1 = take(TS);
-    W0t = take(NP * LDH); b0 = take(HP); W1t = take(HP * LDH); b1 = take(HP);
+    W0t = take(NP * LDW); b0 = take(HP); W1t = take(HP * LDW); b1 = take(HP);
     W2t = take(HP * LDM); b2 = take(MP);
-    W1 = bwd ? take(HP * LDH) : 0; W2 = bwd ? take(MP * LDH) : 0;
+    W1 = bwd ? take(HP * LDW) : 0; W2 = bwd ? take(MP * LDH) : 0;
     const bool fvp = mode == M_FVP;
-    V0t = fvp ? take(NP * LDH) : 0; vb0 = fvp ? take(HP) : 0; V1t = fvp ? take(HP * LDH) : 0;
+    V0t = fvp ? take(NP * LDW) : 0; vb0 = fvp ? take(HP) : 0; V1t = fvp ? take(HP * LDW) : 0;
     vb1 = fvp ? take(HP) : 0; V2t = fvp ? take(HP * LDM) : 0; vb2 = fvp ? take(MP) : 0;
     ishift = take(NP); iden = take(NP); oscale = take(MP); oshift = take(MP); sig = take(MP);
     ls = take(MP); ols_ = take(MP); fisher = take(MP);
@@ -94,17 +99,55 @@ __device__ __forceinline__ void load_v(float* dst, int pad, const float* src, in
   for (int i = threadIdx.x; i < pad; i += NTHREADS) dst[i] = (src && i < cnt) ? __ldg(src + i) : fill;
 }
 
-template <int HP, int MODE, int W0SLOTS>
+// Tensor-core forward layer on the warp's 32 x 16 tile: z = bias + A Wt (tangent dz = vbias + A Vt
+// [+ D Wt]), h = tanh(z), dh = (1 - h^2) dz, written to Hout / Dout ([t][ldo]).
+template <bool DUAL, bool HAS_D>
+__device__ __forceinline__ void mma_fwd_layer(const float* __restrict__ A, const float* __restrict__ D, int lda,
+                                              const float* __restrict__ Wt, const float* __restrict__ Vt, int ldw,
+                                              int K, const float* __restrict__ bias, const float* __restrict__ vbias,
+                                              float* __restrict__ Hout, float* __restrict__ Dout, int ldo,
+                                              int mrow0, int ncol0, int g, int c) {
+  float z[2][2][4], dz[2][2][4];
+#pragma unroll
+  for (int ni = 0; ni < 2; ++ni) {
+    const int col = ncol0 + ni * 8 + 2 * c;
+    const float b0 = bias[col], b1 = bias[col + 1];
+    const float v0 = DUAL ? vbias[col] : 0.f, v1 = DUAL ? vbias[col + 1] : 0.f;
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi) {
+      z[mi][ni][0] = b0; z[mi][ni][1] = b1; z[mi][ni][2] = b0; z[mi][ni][3] = b1;
+      dz[mi][ni][0] = v0; dz[mi][ni][1] = v1; dz[mi][ni][2] = v0; dz[mi][ni][3] = v1;
+    }
+  }
+  mma_layer<DUAL, HAS_D>(z, dz, A + mrow0 * lda, HAS_D ? D + mrow0 * lda : nullptr, lda, Wt + ncol0,
+                         DUAL ? Vt + ncol0 : nullptr, ldw, K, g, c);
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+    for (int ni = 0; ni < 2; ++ni)
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int row = mrow0 + mi * 16 + g + half * 8, col = ncol0 + ni * 8 + 2 * c;
+        const float h0 = tanhf(z[mi][ni][2 * half]), h1 = tanhf(z[mi][ni][2 * half + 1]);
+        *reinterpret_cast<float2*>(Hout + row * ldo + col) = make_float2(h0, h1);
+        if (DUAL)
+          *reinterpret_cast<float2*>(Dout + row * ldo + col) =
+              make_float2((1.f - h0 * h0) * dz[mi][ni][2 * half], (1.f - h1 * h1) * dz[mi][ni][2 * half + 1]);
+      }
+}
+
+template <int HP, int MODE, int W0SLOTS, bool MMA>
 __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
   constexpr int NF = HP / 4, NT = NTHREADS / NF, TS = RT * NT, LDH = HP + 4;
   constexpr bool BWD = MODE == M_GRAD || MODE == M_FVP;
   extern __shared__ __align__(16) float sm[];
   if (MODE == M_FVP && a.stop_flag && *a.stop_flag) return;
 
-  const Layout L(HP, a.n, a.m, MODE);
+  const Layout L(HP, a.n, a.m, MODE, MMA);
   const Flat F(a.n, a.m, a.h1, a.h2);
   const int tid = threadIdx.x;
   const int NP = L.NP, LDX = L.LDX, MP = L.MP, LDM = L.LDM;
+  constexpr int LDW = MMA ? HP + 8 : HP + 4;
   const int n = a.n, m = a.m;
 
   float* sX = sm + L.X; float* sH1 = sm + L.H1; float* sH2 = sm + L.H2;
@@ -114,21 +157,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
   // ---- one-time: zero activations (padding columns stay zero), stage weights -------------
   for (int i = tid; i < L.W0t; i += NTHREADS) sm[i] = 0.f;
   const float* P = a.params;
-  load_wt(sm + L.W0t, LDH, NP, HP, P + F.oW0, F.h1, n);
+  load_wt(sm + L.W0t, LDW, NP, HP, P + F.oW0, F.h1, n);
   load_v(sm + L.b0, HP, P + F.ob0, F.h1);
-  load_wt(sm + L.W1t, LDH, HP, HP, P + F.oW1, F.h2, F.h1);
+  load_wt(sm + L.W1t, LDW, HP, HP, P + F.oW1, F.h2, F.h1);
   load_v(sm + L.b1, HP, P + F.ob1, F.h2);
   load_wt(sm + L.W2t, LDM, HP, MP, P + F.oW2, m, F.h2);
   load_v(sm + L.b2, MP, P + F.ob2, m);
   if (BWD) {
-    load_w(sm + L.W1, LDH, HP, HP, P + F.oW1, F.h2, F.h1);
+    load_w(sm + L.W1, LDW, HP, HP, P + F.oW1, F.h2, F.h1);
     load_w(sm + L.W2, LDH, MP, HP, P + F.oW2, m, F.h2);
   }
   if (MODE == M_FVP) {
     const float* V = a.vec;
-    load_wt(sm + L.V0t, LDH, NP, HP, V + F.oW0, F.h1, n);
+    load_wt(sm + L.V0t, LDW, NP, HP, V + F.oW0, F.h1, n);
     load_v(sm + L.vb0, HP, V + F.ob0, F.h1);
-    load_wt(sm + L.V1t, LDH, HP, HP, V + F.oW1, F.h2, F.h1);
+    load_wt(sm + L.V1t, LDW, HP, HP, V + F.oW1, F.h2, F.h1);
     load_v(sm + L.vb1, HP, V + F.ob1, F.h2);
     load_wt(sm + L.V2t, LDM, HP, MP, V + F.oW2, m, F.h2);
     load_v(sm + L.vb2, MP, V + F.ob2, m);
@@ -152,13 +195,29 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
   const int tf = tid % NF, tt = tid / NF;  // feature tile / timestep group of the layer products
   const int row0 = tt * RT, col0 = tf * 4;
 
+  // tensor-core path: warp (wm, wn) owns a 32(t) x 16(f) tile of every layer output
+  constexpr int WN = HP / 16, WM = 8 / WN;
+  static_assert(!MMA || 32 * WM == TS, "MMA warp tiling must cover the timestep tile");
+  const int lane = tid & 31, warp = tid >> 5, fg = lane >> 2, fc = lane & 3;
+  const int wm = warp % WM, wn = warp / WM;
+  const int mrow0 = wm * 32, ncol0 = wn * 16;
+  // weight-gradient fragments (16 x 8): gW1 has (HP/16)*(HP/8) of them, NW1 per warp, all in one
+  // 16-row band; gW0 has (HP/16)*(NP/8), dealt round-robin to warps (slot = frag / 8)
+  constexpr int NW1 = (HP / 16) * (HP / 8) / 8;
+  float macc1[MMA ? NW1 : 1][4], macc0[MMA ? W0SLOTS : 1][4], mcb0[4];
+
   // persistent register accumulators
-  float acc0[W0SLOTS][16], acc1[16], acc2[16], cb0[4], cb1[4];
+  float acc0[MMA ? 1 : W0SLOTS][16], acc1[16], acc2[16], cb0[4], cb1[4];
   float gb2acc = 0.f, glsacc = 0.f;
   double surr_acc = 0.0, kl_acc = 0.0;
   if (BWD) {
 #pragma unroll
-    for (int s = 0; s < W0SLOTS; ++s)
+    for (int s = 0; s < (MMA ? NW1 : 1); ++s) macc1[s][0] = macc1[s][1] = macc1[s][2] = macc1[s][3] = 0.f;
+#pragma unroll
+    for (int s = 0; s < (MMA ? W0SLOTS : 1); ++s) macc0[s][0] = macc0[s][1] = macc0[s][2] = macc0[s][3] = 0.f;
+    mcb0[0] = mcb0[1] = mcb0[2] = mcb0[3] = 0.f;
+#pragma unroll
+    for (int s = 0; s < (MMA ? 1 : W0SLOTS); ++s)
 #pragma unroll
       for (int e = 0; e < 16; ++e) acc0[s][e] = 0.f;
 #pragma unroll
@@ -197,7 +256,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
     }
     __syncthreads();
     // ---- P1: layer 0 ----------------------------------------------------------------------
-    {
+    if constexpr (MMA) {
+      mma_fwd_layer<MODE == M_FVP, false>(sX, nullptr, LDX, sm + L.W0t, sm + L.V0t, LDW, NP, sm + L.b0,
+                                          sm + L.vb0, sH1, sB1, LDH, mrow0, ncol0, fg, fc);
+    } else {
       float z[RT][4], dz[RT][4];
       const float4 bias = *reinterpret_cast<const float4*>(sm + L.b0 + col0);
 #pragma unroll
@@ -207,9 +269,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
 #pragma unroll
         for (int r = 0; r < RT; ++r) { dz[r][0] = vb.x; dz[r][1] = vb.y; dz[r][2] = vb.z; dz[r][3] = vb.w; }
         mm_acc_dual<RT, false>(z, dz, sX + row0 * LDX, nullptr, LDX, sm + L.W0t + col0,
-                               sm + L.V0t + col0, LDH, NP);
+                               sm + L.V0t + col0, LDW, NP);
       } else {
-        mm_acc<RT>(z, sX + row0 * LDX, LDX, sm + L.W0t + col0, LDH, NP);
+        mm_acc<RT>(z, sX + row0 * LDX, LDX, sm + L.W0t + col0, LDW, NP);
       }
 #pragma unroll
       for (int r = 0; r < RT; ++r) {
@@ -224,7 +286,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
     }
     __syncthreads();
     // ---- P2: layer 1 ----------------------------------------------------------------------
-    {
+    if constexpr (MMA) {
+      mma_fwd_layer<MODE == M_FVP, MODE == M_FVP>(sH1, sB1, LDH, sm + L.W1t, sm + L.V1t, LDW, HP,
+                                                  sm + L.b1, sm + L.vb1, sH2, sB2, LDH, mrow0, ncol0, fg, fc);
+    } else {
       float z[RT][4], dz[RT][4];
       const float4 bias = *reinterpret_cast<const float4*>(sm + L.b1 + col0);
 #pragma unroll
@@ -234,9 +299,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
 #pragma unroll
         for (int r = 0; r < RT; ++r) { dz[r][0] = vb.x; dz[r][1] = vb.y; dz[r][2] = vb.z; dz[r][3] = vb.w; }
         mm_acc_dual<RT, true>(z, dz, sH1 + row0 * LDH, sB1 + row0 * LDH, LDH, sm + L.W1t + col0,
-                              sm + L.V1t + col0, LDH, HP);
+                              sm + L.V1t + col0, LDW, HP);
       } else {
-        mm_acc<RT>(z, sH1 + row0 * LDH, LDH, sm + L.W1t + col0, LDH, HP);
+        mm_acc<RT>(z, sH1 + row0 * LDH, LDH, sm + L.W1t + col0, LDW, HP);
       }
 #pragma unroll
       for (int r = 0; r < RT; ++r) {
@@ -382,11 +447,36 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
       __syncthreads();
       // ---- P5: gz1 = (GZ2 W1) * (1 - h1^2); gW1 += GZ2^T H1 -----------------------------------
-      {
+      if constexpr (MMA) {
+        float gh[2][2][4], unused[2][2][4];
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+          for (int ni = 0; ni < 2; ++ni) gh[mi][ni][0] = gh[mi][ni][1] = gh[mi][ni][2] = gh[mi][ni][3] = 0.f;
+        mma_layer<false, false>(gh, unused, sB2 + mrow0 * LDH, nullptr, LDH, sm + L.W1 + ncol0, nullptr, LDW,
+                                HP, fg, fc);
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+          for (int ni = 0; ni < 2; ++ni)
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              const int row = mrow0 + mi * 16 + fg + half * 8, col = ncol0 + ni * 8 + 2 * fc;
+              const float2 h = *reinterpret_cast<const float2*>(sH1 + row * LDH + col);
+              const float o0 = gh[mi][ni][2 * half] * (1.f - h.x * h.x);
+              const float o1 = gh[mi][ni][2 * half + 1] * (1.f - h.y * h.y);
+              *reinterpret_cast<float2*>(sB1 + row * LDH + col) = make_float2(o0, o1);
+              mcb0[ni * 2] += o0; mcb0[ni * 2 + 1] += o1;
+            }
+        {
+          const int f = warp * NW1;  // NW1 consecutive fragments share one 16-row band
+          mma_wgrad<NW1>(macc1, sB2, LDH, sH1, LDH, (f / (HP / 8)) * 16, (f % (HP / 8)) * 8, NW1, TS, fg, fc);
+        }
+      } else {
         float g[RT][4];
 #pragma unroll
         for (int r = 0; r < RT; ++r) { g[r][0] = g[r][1] = g[r][2] = g[r][3] = 0.f; }
-        mm_acc<RT>(g, sB2 + row0 * LDH, LDH, sm + L.W1 + col0, LDH, HP);
+        mm_acc<RT>(g, sB2 + row0 * LDH, LDH, sm + L.W1 + col0, LDW, HP);
 #pragma unroll
         for (int r = 0; r < RT; ++r) {
           const float4 h = *reinterpret_cast<const float4*>(sH1 + (row0 + r) * LDH + col0);
@@ -401,12 +491,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
       __syncthreads();
       // ---- P6: gW0 += GZ1^T X -----------------------------------------------------------------
+      if constexpr (MMA) {
+        const int nfn = NP / 8, nf0 = (HP / 16) * nfn;
 #pragma unroll
-      for (int s = 0; s < W0SLOTS; ++s) {
-        const TileOwner own0(nt0, tid, s);
-        if (own0.active)
-          wgrad_acc(acc0[s], sB1, LDH, sX, LDX, 4 * (own0.tile / (NP / 4)), 4 * (own0.tile % (NP / 4)),
-                    own0.grp, own0.G, TS);
+        for (int s = 0; s < W0SLOTS; ++s) {
+          const int f = warp + 8 * s;
+          if (f < nf0) {
+            float (&acc)[1][4] = *reinterpret_cast<float (*)[1][4]>(&macc0[s]);
+            mma_wgrad<1>(acc, sB1, LDH, sX, LDX, (f / nfn) * 16, (f % nfn) * 8, 1, TS, fg, fc);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int s = 0; s < W0SLOTS; ++s) {
+          const TileOwner own0(nt0, tid, s);
+          if (own0.active)
+            wgrad_acc(acc0[s], sB1, LDH, sX, LDX, 4 * (own0.tile / (NP / 4)), 4 * (own0.tile % (NP / 4)),
+                      own0.grp, own0.G, TS);
+        }
       }
     }
   }
@@ -425,13 +527,49 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
     __syncthreads();
     const int h1 = F.h1, h2 = F.h2;
     int gmax = NT;
-    {
+    if constexpr (MMA) {
+      gmax = max(gmax, max(own2.G, WM * 8));
+      // tensor-core fragments: every element has exactly one owner thread
+#pragma unroll
+      for (int j = 0; j < NW1; ++j) {
+        const int f = warp * NW1 + j, o0 = (f / (HP / 8)) * 16 + fg, i0 = (f % (HP / 8)) * 8 + 2 * fc;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int o = o0 + (e >> 1) * 8, i = i0 + (e & 1);
+          if (o < h2 && i < h1) sG[F.oW1 + o * h1 + i] = macc1[j][e];
+        }
+      }
+      const int nfn = NP / 8, nf0 = (HP / 16) * nfn;
+#pragma unroll
+      for (int sl = 0; sl < W0SLOTS; ++sl) {
+        const int f = warp + 8 * sl;
+        if (f < nf0) {
+          const int o0 = (f / nfn) * 16 + fg, i0 = (f % nfn) * 8 + 2 * fc;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int o = o0 + (e >> 1) * 8, i = i0 + (e & 1);
+            if (o < h1 && i < n) sG[F.oW0 + o * n + i] = macc0[sl][e];
+          }
+        }
+      }
+      __syncthreads();
+    } else {
       const TileOwner o0(nt0, tid, 0);
       gmax = max(gmax, max(o0.G, max(own1.G, own2.G)));
     }
     for (int g = 0; g < gmax; ++g) {
+      if constexpr (MMA) {
+        // fc0 bias gradient: column sums held per (warp row band, fragment row group)
+        if (wm * 8 + fg == g) {
 #pragma unroll
-      for (int s = 0; s < W0SLOTS; ++s) {
+          for (int q = 0; q < 4; ++q) {
+            const int f = ncol0 + (q >> 1) * 8 + 2 * fc + (q & 1);
+            if (f < h1) sG[F.ob0 + f] += mcb0[q];
+          }
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < (MMA ? 0 : W0SLOTS); ++s) {
         const TileOwner own0(nt0, tid, s);
         if (own0.active && own0.grp == g) {
           const int o0 = 4 * (own0.tile / (NP / 4)), i0 = 4 * (own0.tile % (NP / 4));
@@ -442,7 +580,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
           }
         }
       }
-      if (own1.active && own1.grp == g) {
+      if (!MMA && own1.active && own1.grp == g) {
         const int o0 = 4 * (own1.tile / NF), i0 = 4 * (own1.tile % NF);
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
@@ -462,7 +600,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           const int f = col0 + c;
-          if (f < h1) sG[F.ob0 + f] += cb0[c];
+          if (!MMA && f < h1) sG[F.ob0 + f] += cb0[c];
           if (f < h2) sG[F.ob1 + f] += cb1[c];
         }
       }
@@ -523,9 +661,9 @@ __global__ void clamp_log_std_kernel(float* p, int ols, int m, float lo) {
   if (j < m) p[ols + j] = fmaxf(p[ols + j], lo);
 }
 
-template <int HP, int MODE, int W0SLOTS>
+template <int HP, int MODE, int W0SLOTS, bool MMA>
 int launch_one(mjrl_ctx* ctx, const Args& a, int grid, size_t smem, cudaStream_t s) {
-  auto kern = mlp_kernel<HP, MODE, W0SLOTS>;
+  auto kern = mlp_kernel<HP, MODE, W0SLOTS, MMA>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -537,6 +675,33 @@ int launch_one(mjrl_ctx* ctx, const Args& a, int grid, size_t smem, cudaStream_t
   return mjrl_check_launch("mlp_kernel");
 }
 
+// Kernel variant: tensor cores (3xTF32 mma.sync) unless MJRL_B200_POLICY_PATH=fma or the shape does
+// not fit the tensor-core shared-memory plan (then the fp32-FMA variant, same results to ~1e-6).
+inline bool want_mma() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("MJRL_B200_POLICY_PATH");
+    v = (e && e[0] == 'f') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+template <int HP, int MODE, bool MMA>
+int launch_slots(mjrl_ctx* ctx, const Args& a, int slots, int grid, size_t smem, cudaStream_t s) {
+  constexpr bool BWD = MODE == M_GRAD || MODE == M_FVP;
+  if constexpr (!BWD) {
+    return launch_one<HP, MODE, 1, MMA>(ctx, a, grid, smem, s);
+  } else if constexpr (MMA) {
+    if (slots <= 1) return launch_one<HP, MODE, 1, true>(ctx, a, grid, smem, s);
+    if (slots <= 2) return launch_one<HP, MODE, 2, true>(ctx, a, grid, smem, s);
+    if (slots <= 4) return launch_one<HP, MODE, 4, true>(ctx, a, grid, smem, s);
+    return launch_one<HP, MODE, 8, true>(ctx, a, grid, smem, s);
+  } else {
+    return slots <= 1 ? launch_one<HP, MODE, 1, false>(ctx, a, grid, smem, s)
+                      : launch_one<HP, MODE, 2, false>(ctx, a, grid, smem, s);
+  }
+}
+
 template <int MODE>
 int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
   const int hmax = a.h1 > a.h2 ? a.h1 : a.h2;
@@ -544,18 +709,28 @@ int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
   MJRL_REQUIRE(hmax <= 64, MJRL_E_SHAPE, "policy: hidden sizes (%d,%d) > 64 are not supported yet",
                a.h1, a.h2);
   const int HP = hmax <= 32 ? 32 : 64;
-  const Layout L(HP, a.n, a.m, MODE);
+  const Flat F(a.n, a.m, a.h1, a.h2);
+  const bool bwd = MODE == M_GRAD || MODE == M_FVP;
+  bool mma = want_mma();
+  int slots = 1;
+  if (mma) {
+    const Layout Lm(HP, a.n, a.m, MODE, true);
+    const int nf0 = (HP / 16) * (Lm.NP / 8);
+    slots = bwd ? (nf0 + 7) / 8 : 1;
+    if (sizeof(float) * (size_t)Lm.total > (size_t)ctx->max_smem_optin || slots > 8) mma = false;
+  }
+  const Layout L(HP, a.n, a.m, MODE, mma);
   const size_t smem = sizeof(float) * (size_t)L.total;
   MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE,
                "policy: obs_dim=%d act_dim=%d hidden=%d needs %zu B of shared memory (max %d)", a.n,
                a.m, HP, smem, ctx->max_smem_optin);
-  const Flat F(a.n, a.m, a.h1, a.h2);
-  const bool bwd = MODE == M_GRAD || MODE == M_FVP;
   if (bwd)
     MJRL_REQUIRE(F.d <= 4 * L.TS * L.LDH, MJRL_E_SHAPE, "policy: d=%d exceeds the staging area", F.d);
-  const int nt0 = (HP / 4) * (L.NP / 4);
-  MJRL_REQUIRE(nt0 <= 2 * NTHREADS, MJRL_E_SHAPE, "policy: obs_dim=%d too large (fc0 tiles %d)", a.n, nt0);
-  const int slots = (bwd && nt0 > NTHREADS) ? 2 : 1;
+  if (!mma) {
+    const int nt0 = (HP / 4) * (L.NP / 4);
+    MJRL_REQUIRE(nt0 <= 2 * NTHREADS, MJRL_E_SHAPE, "policy: obs_dim=%d too large (fc0 tiles %d)", a.n, nt0);
+    slots = (bwd && nt0 > NTHREADS) ? 2 : 1;
+  }
   const long long ntiles = (a.N + L.TS - 1) / L.TS;
   int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
   if (grid < 1) grid = 1;
@@ -569,10 +744,11 @@ int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
     a.spartials = (double*)mjrl_scratch2(ctx, sizeof(double) * 2 * grid);
     if (!a.spartials) return MJRL_E_STATE;
   }
-  if (HP == 32) return slots == 1 ? launch_one<32, MODE, 1>(ctx, a, grid, smem, s)
-                                  : launch_one<32, MODE, 2>(ctx, a, grid, smem, s);
-  return slots == 1 ? launch_one<64, MODE, 1>(ctx, a, grid, smem, s)
-                    : launch_one<64, MODE, 2>(ctx, a, grid, smem, s);
+  if (HP == 32)
+    return mma ? launch_slots<32, MODE, true>(ctx, a, slots, grid, smem, s)
+               : launch_slots<32, MODE, false>(ctx, a, slots, grid, smem, s);
+  return mma ? launch_slots<64, MODE, true>(ctx, a, slots, grid, smem, s)
+             : launch_slots<64, MODE, false>(ctx, a, slots, grid, smem, s);
 }
 
 inline void fill_desc(Args& a, const mjrl_policy_desc* d) {

@@ -133,3 +133,114 @@ struct TileOwner {
 };
 
 }  // namespace pol
+
+// =========================================================================================
+// Tensor-core path: error-compensated 3xTF32 on mma.sync.m16n8k8 (fp32 accumulate).
+//   a*b ~= a_lo*b_hi + a_hi*b_lo + a_hi*b_hi,  x_hi = tf32(x), x_lo = tf32(x - x_hi)
+// keeps ~2^-21 relative error per product (plain TF32 is 2^-11 and breaks the 1e-4 parity gate).
+// Measured on B200 (profiles/probes/mma_probe.cu): 279 TFLOP/s TF32 mma.sync vs 72 TFLOP/s FFMA.
+//
+// Fragment ownership (PTX ISA, m16n8k8 .tf32):  g = lane>>2, c = lane&3
+//   A (16x8 row):  a0 (g, c)   a1 (g+8, c)   a2 (g, c+4)   a3 (g+8, c+4)
+//   B (8x8  col):  b0 (k=c, n=g)   b1 (k=c+4, n=g)
+//   C (16x8):      c0 (g, 2c)  c1 (g, 2c+1)  c2 (g+8, 2c)  c3 (g+8, 2c+1)
+// Shared-memory strides are chosen so every fragment load is bank-conflict free:
+// activations [t][lda] with lda = 4 (mod 8) words, k-major weights [k][ldw] with ldw = 8 (mod 32).
+// =========================================================================================
+namespace pol {
+
+struct Frag4 { uint32_t hi[4], lo[4]; };
+struct Frag2 { uint32_t hi[2], lo[2]; };
+
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+  const float r = x - __uint_as_float(hi);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+}
+
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+__device__ __forceinline__ void mma3(float (&d)[4], const Frag4& a, const Frag2& b) {
+  mma_tf32(d, a.lo, b.hi);  // small terms first
+  mma_tf32(d, a.hi, b.lo);
+  mma_tf32(d, a.hi, b.hi);
+}
+
+// A[m][k] = S[m][k], S row-major with stride ld; p = &S[m0][k0]
+__device__ __forceinline__ void load_a(Frag4& f, const float* __restrict__ p, int ld, int g, int c) {
+  split_tf32(p[g * ld + c], f.hi[0], f.lo[0]);
+  split_tf32(p[(g + 8) * ld + c], f.hi[1], f.lo[1]);
+  split_tf32(p[g * ld + c + 4], f.hi[2], f.lo[2]);
+  split_tf32(p[(g + 8) * ld + c + 4], f.hi[3], f.lo[3]);
+}
+// A[m][k] = S[k][m] (the k index walks rows of S); p = &S[k0][m0]
+__device__ __forceinline__ void load_a_t(Frag4& f, const float* __restrict__ p, int ld, int g, int c) {
+  split_tf32(p[c * ld + g], f.hi[0], f.lo[0]);
+  split_tf32(p[c * ld + g + 8], f.hi[1], f.lo[1]);
+  split_tf32(p[(c + 4) * ld + g], f.hi[2], f.lo[2]);
+  split_tf32(p[(c + 4) * ld + g + 8], f.hi[3], f.lo[3]);
+}
+// B[k][n] = S[k][n]; p = &S[k0][n0]
+__device__ __forceinline__ void load_b(Frag2& f, const float* __restrict__ p, int ld, int g, int c) {
+  split_tf32(p[c * ld + g], f.hi[0], f.lo[0]);
+  split_tf32(p[(c + 4) * ld + g], f.hi[1], f.lo[1]);
+}
+
+// Layer product on a 32(t) x 16(f) warp tile:  z += A Wt ;  dz += A Vt (+ D Wt)
+//   A, D: smem activations, pointers at the warp's first row; Wt, Vt: k-major weights at the warp's
+//   first column.  K multiple of 8.
+template <bool DUAL, bool HAS_D>
+__device__ __forceinline__ void mma_layer(float (&z)[2][2][4], float (&dz)[2][2][4],
+                                          const float* __restrict__ A, const float* __restrict__ D, int lda,
+                                          const float* __restrict__ Wt, const float* __restrict__ Vt, int ldw,
+                                          int K, int g, int c) {
+  for (int k0 = 0; k0 < K; k0 += 8) {
+    Frag4 a[2], d[2];
+    Frag2 w[2], v[2];
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi) {
+      load_a(a[mi], A + mi * 16 * lda + k0, lda, g, c);
+      if (HAS_D) load_a(d[mi], D + mi * 16 * lda + k0, lda, g, c);
+    }
+#pragma unroll
+    for (int ni = 0; ni < 2; ++ni) {
+      load_b(w[ni], Wt + k0 * ldw + ni * 8, ldw, g, c);
+      if (DUAL) load_b(v[ni], Vt + k0 * ldw + ni * 8, ldw, g, c);
+    }
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+      for (int ni = 0; ni < 2; ++ni) {
+        mma3(z[mi][ni], a[mi], w[ni]);
+        if (DUAL) mma3(dz[mi][ni], a[mi], v[ni]);
+        if (HAS_D) mma3(dz[mi][ni], d[mi], w[ni]);
+      }
+  }
+}
+
+// Weight-gradient fragments: acc[j] (16 x 8 each, rows = A columns m0.., cols = B columns n0 + 8j..)
+//   += sum_t A_s[t][m0 + .] * B_s[t][n0 + 8j + .]   over t in [0, TS), TS multiple of 8
+template <int NFR>
+__device__ __forceinline__ void mma_wgrad(float (&acc)[NFR][4], const float* __restrict__ A_s, int lda,
+                                          const float* __restrict__ B_s, int ldb, int m0, int n0, int nvalid,
+                                          int TS, int g, int c) {
+  for (int t0 = 0; t0 < TS; t0 += 8) {
+    Frag4 a;
+    load_a_t(a, A_s + t0 * lda + m0, lda, g, c);
+#pragma unroll
+    for (int j = 0; j < NFR; ++j) {
+      if (j < nvalid) {
+        Frag2 b;
+        load_b(b, B_s + t0 * ldb + n0 + 8 * j, ldb, g, c);
+        mma3(acc[j], a, b);
+      }
+    }
+  }
+}
+
+}  // namespace pol
