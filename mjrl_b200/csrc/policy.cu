@@ -38,6 +38,7 @@ struct Args {
   float* partials;    // [grid][dstride]
   double* spartials;  // [grid][2]
   const int32_t* stop_flag;
+  long long* phase_cycles;  // debug: [grid][8] cycles per phase (P0,P1,P2,P3a,P3b,P4,P5,P6+loop)
   long long N;
   int n, m, h1, h2, dstride;
 };
@@ -228,11 +229,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
   const int nt0 = NF * (NP / 4), nt1 = NF * NF, nt2 = (MP / 4) * NF;
   const TileOwner own1(nt1, tid, 0), own2(nt2, tid, 0);
 
+  // optional per-phase cycle counters (debug: MJRL_B200_PHASE_CYCLES=1), thread 0 of each CTA
+  long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long tprev = 0;
+#define PHASE_STAMP(q)                                   \
+  if (a.phase_cycles && tid == 0) {                      \
+    const long long now = clock64();                     \
+    ph[q] += now - tprev;                                \
+    tprev = now;                                         \
+  }
+  if (a.phase_cycles && tid == 0) tprev = clock64();
   const long long ntiles = (a.N + TS - 1) / TS;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long long t0 = tile * TS;
     const int rows = (int)min((long long)TS, a.N - t0);
     __syncthreads();  // previous tile fully consumed
+    PHASE_STAMP(7);
     // ---- P0: obs tile (+ actions) -> smem, input transform --------------------------------
     {
       const float* src = a.obs + t0 * n;
@@ -255,6 +267,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
     }
     __syncthreads();
+    PHASE_STAMP(0);
     // ---- P1: layer 0 ----------------------------------------------------------------------
     if constexpr (MMA) {
       mma_fwd_layer<MODE == M_FVP, false>(sX, nullptr, LDX, sm + L.W0t, sm + L.V0t, LDW, NP, sm + L.b0,
@@ -285,6 +298,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
     }
     __syncthreads();
+    PHASE_STAMP(1);
     // ---- P2: layer 1 ----------------------------------------------------------------------
     if constexpr (MMA) {
       mma_fwd_layer<MODE == M_FVP, MODE == M_FVP>(sH1, sB1, LDH, sm + L.W1t, sm + L.V1t, LDW, HP,
@@ -315,6 +329,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
     }
     __syncthreads();
+    PHASE_STAMP(2);
     // ---- P3a: head.  4 lanes split K for one timestep, shuffle-reduce -----------------------
     {
       const int q = tid & 3;
@@ -363,6 +378,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
     }
     __syncthreads();
+    PHASE_STAMP(3);
     // ---- P3b: Gaussian head, one thread per timestep ----------------------------------------
     if (MODE != M_FVP) {
       for (int t = tid; t < TS; t += NTHREADS) {
@@ -411,6 +427,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
         }
       }
       __syncthreads();
+    PHASE_STAMP(4);
       if (MODE == M_EVAL || MODE == M_GRAD) {
         if (tid < 32) {  // fixed-order fp64 sums of the tile's per-timestep terms
           double s0 = 0.0, s1 = 0.0;
@@ -446,6 +463,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
         }
       }
       __syncthreads();
+    PHASE_STAMP(5);
       // ---- P5: gz1 = (GZ2 W1) * (1 - h1^2); gW1 += GZ2^T H1 -----------------------------------
       if constexpr (MMA) {
         float gh[2][2][4], unused[2][2][4];
@@ -490,6 +508,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
                     own1.G, TS);
       }
       __syncthreads();
+    PHASE_STAMP(6);
       // ---- P6: gW0 += GZ1^T X -----------------------------------------------------------------
       if constexpr (MMA) {
         const int nfn = NP / 8, nf0 = (HP / 16) * nfn;
@@ -514,6 +533,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
   }
 
   // ---- per-CTA results ------------------------------------------------------------------------
+  if (a.phase_cycles && tid == 0)
+    for (int q = 0; q < 8; ++q) a.phase_cycles[blockIdx.x * 8 + q] = ph[q];
   if ((MODE == M_EVAL || MODE == M_GRAD) && tid == 0) {
     a.spartials[2 * blockIdx.x + 0] = surr_acc;
     a.spartials[2 * blockIdx.x + 1] = kl_acc;
@@ -670,6 +691,23 @@ int launch_one(mjrl_ctx* ctx, const Args& a, int grid, size_t smem, cudaStream_t
                                          ctx->max_smem_optin);
     if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
     attr_set = true;
+  }
+  static const bool dbg = getenv("MJRL_B200_PHASE_CYCLES") != nullptr;
+  if (dbg) {
+    Args b = a;
+    long long* dev; cudaMalloc(&dev, sizeof(long long) * 8 * grid);
+    cudaMemset(dev, 0, sizeof(long long) * 8 * grid);
+    b.phase_cycles = dev;
+    kern<<<grid, NTHREADS, smem, s>>>(b);
+    cudaStreamSynchronize(s);
+    long long* h = new long long[8 * grid];
+    cudaMemcpy(h, dev, sizeof(long long) * 8 * grid, cudaMemcpyDeviceToHost);
+    double tot[8] = {0};
+    for (int c = 0; c < grid; ++c) for (int q = 0; q < 8; ++q) tot[q] += (double)h[c * 8 + q] / grid;
+    fprintf(stderr, "[phase cycles HP=%d mode=%d mma=%d] P0 %.0f P1 %.0f P2 %.0f P3a %.0f P3b %.0f P4 %.0f P5 %.0f P6 %.0f\n",
+            HP, MODE, (int)MMA, tot[0], tot[1], tot[2], tot[3], tot[4], tot[5], tot[6], tot[7]);
+    delete[] h; cudaFree(dev);
+    return mjrl_check_launch("mlp_kernel(dbg)");
   }
   kern<<<grid, NTHREADS, smem, s>>>(a);
   return mjrl_check_launch("mlp_kernel");
