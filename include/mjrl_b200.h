@@ -100,6 +100,37 @@ int mjrl_linbase_solve(mjrl_ctx* ctx, const double* gram, int32_t F, double reg_
                        const double* coeffs_prev, double* coeffs, double* info4,
                        void* stream);
 
+/* ---- (b) MLPBaseline: mjrl/baselines/mlp_baseline.py --------------------------------- */
+/* (n+4)-128-128-1 ReLU value net, fp32 (:24-28).  Flat parameter vector in torch
+ * `model.parameters()` order: fc_0.weight [128][n+4] | fc_0.bias | fc_1.weight [128][128] |
+ * fc_1.bias | fc_2.weight [1][128] | fc_2.bias; returns the count (<0 on a bad n). */
+int64_t mjrl_mlpbase_param_count(int32_t n);
+/* _features (:37-56): feat[t] = [clip(o,-10,10)/10, al, al^2, al^3, al^4], al = t_in_path/1000,
+ * fp64 arithmetic cast to fp32 [N, n+4] (:63).  If returns and y32 are non-NULL also
+ * y32 = (float)returns (:64). */
+int mjrl_mlpbase_features(mjrl_ctx* ctx, const float* obs, const double* returns,
+                          const int32_t* path_offsets, int32_t P, int64_t N, int32_t n, float* feat,
+                          float* y32, void* stream);
+/* predict (:107-115) over the whole flat buffer; features are rebuilt in-kernel.  pred is
+ * fp64 [N] holding the fp32 network output widened (the reference mixes the fp32 prediction
+ * with fp64 rewards, process_samples.py:25-29, which numpy widens the same way). */
+int mjrl_mlpbase_predict(mjrl_ctx* ctx, const float* obs, const int32_t* path_offsets, int32_t P,
+                         int64_t N, int32_t n, const float* params, double* pred, void* stream);
+/* sums2 = { sum ((float)ret - (float)pred)^2 , sum (float)ret^2 }: the two sums of the
+ * error ratio of :75-81,98-104 (the caller adds 1e-8 to the denominator). */
+int mjrl_mlpbase_sqerr(mjrl_ctx* ctx, const double* pred, const double* returns, int64_t N,
+                       double* sums2, void* stream);
+/* fit (:83-96): `nsteps` dependent Adam steps; step s trains on rows perm[s*batch .. (s+1)*batch)
+ * of (feat, y32).  The host builds `perm` exactly like the reference: per epoch one
+ * np.random.permutation(N), of which the first (int(N/batch)-1)*batch entries are used (:84-86).
+ * params / adam_m / adam_v are updated in place; step0 = optimiser steps taken before this call
+ * (torch.optim.Adam keeps its state across fit() calls).  MSE loss (mean), weight_decay is
+ * added to the gradient, bias-corrected Adam as torch.optim.Adam.  batch <= 64. */
+int mjrl_mlpbase_fit(mjrl_ctx* ctx, const float* feat, const float* y32, int64_t N, int32_t n,
+                     float* params, float* adam_m, float* adam_v, int64_t step0, const int32_t* perm,
+                     int64_t nsteps, int32_t batch, double lr, double beta1, double beta2, double eps,
+                     double weight_decay, void* stream);
+
 /* ---- (c)(d)(e) Gaussian policy: mjrl/policies/gaussian_mlp.py, gaussian_linear.py ---- */
 /* Network description.  h1 == h2 == 0 selects the affine policy (LinearModel.forward,
  * gaussian_linear.py:171-175); otherwise the two-hidden-layer tanh MuNet

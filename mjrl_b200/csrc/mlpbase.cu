@@ -1,0 +1,562 @@
+// (b) MLPBaseline: (n+4) -> 128 -> 128 -> 1 ReLU value network, fp32.
+//
+// Replaces (reference = bennevans/mjrl, mjrl/baselines/mlp_baseline.py):
+//   _features   :37-56   [clip(o,-10,10)/10, al, al^2, al^3, al^4], al = t_in_path/1000
+//   predict     :107-115 forward pass over a path's features
+//   fit         :59-105  epochs x (floor(N/bs) - 1) Adam steps on minibatches drawn from a
+//                        host permutation (np.random.permutation, :84); MSE loss; L2
+//                        weight_decay added to the gradient (torch.optim.Adam, :34)
+//
+// predict is a persistent tile kernel like the policy passes (fp32-FMA bound: 36.9 kflop per
+// 4n+8 B).  fit is a SERIAL chain of dependent steps: one persistent CTA keeps
+// the fp32 master weights in shared memory for the whole chain, the Adam moments in L2-resident
+// global memory, prefetches the next minibatch with cp.async while the current step computes,
+// and applies Adam directly from the register tiles that hold the weight gradients (the
+// gradient is never materialised).
+//
+// Flat parameter layout (torch `model.parameters()` order, row-major (out,in)):
+//   fc_0.weight [128][F] | fc_0.bias [128] | fc_1.weight [128][128] | fc_1.bias [128] |
+//   fc_2.weight [1][128] | fc_2.bias [1]          F = n + 4
+#include <algorithm>
+
+#include "policy_tile.cuh"
+
+namespace mlpb {
+
+constexpr int H = 128;         // hidden width (mlp_baseline.py:24-28)
+constexpr int LDH = H + 4;     // activation / fc_1 row stride: = 4 (mod 32) words
+constexpr int MAXB = 64;       // rows of the minibatch tile
+
+struct Offsets {
+  int F, oW0, ob0, oW1, ob1, oW2, ob2, D;
+  __host__ __device__ explicit Offsets(int n) {
+    F = n + 4;
+    oW0 = 0; ob0 = H * F; oW1 = ob0 + H; ob1 = oW1 + H * H; oW2 = ob1 + H; ob2 = oW2 + H; D = ob2 + 1;
+  }
+};
+
+// Padded feature width (k extent of fc_0) and fc_0 row stride.  The stride is = 4 (mod 8) words
+// so that the 8 lanes of a quarter warp reading float4s of 8 different weight rows hit 8
+// different bank groups.
+__host__ __device__ inline int feat_pad(int F) { return (F + 3) & ~3; }
+__host__ __device__ inline int w0_stride(int F) {
+  int s = feat_pad(F) + 4;
+  while ((s & 7) != 4) s += 4;
+  return s;
+}
+
+// One row of features (mlp_baseline.py:38-55), computed in fp64 like the reference, cast to fp32.
+__device__ __forceinline__ void time_feats(int t_in_path, float (&tf)[4]) {
+  const double al = (double)t_in_path / 1000.0;
+  tf[0] = (float)al;
+  tf[1] = (float)(al * al);
+  tf[2] = (float)pow(al, 3.0);
+  tf[3] = (float)pow(al, 4.0);
+}
+__device__ __forceinline__ float obs_feat(float o) {
+  double v = (double)o;
+  v = v < -10.0 ? -10.0 : (v > 10.0 ? 10.0 : v);
+  return (float)(v / 10.0);
+}
+
+__global__ void features_kernel(const float* __restrict__ obs, const int32_t* __restrict__ offsets, int P,
+                                long long N, int n, float* __restrict__ feat) {
+  const int F = n + 4;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < N;
+       t += (long long)gridDim.x * blockDim.x) {
+    const int p = find_path(offsets, P, t);
+    float tf[4];
+    time_feats((int)(t - offsets[p]), tf);
+    const float* o = obs + t * n;
+    float* f = feat + t * F;
+    for (int k = 0; k < n; ++k) f[k] = obs_feat(ld_stream(o + k));
+    f[n] = tf[0]; f[n + 1] = tf[1]; f[n + 2] = tf[2]; f[n + 3] = tf[3];
+  }
+}
+
+// out[r][c] for the thread's 4 rows x 4 INTERLEAVED output units o = lane + 32 c:
+//   acc[r][c] += sum_k A[row0 + r][k] * W[lane + 32 c][k]      (W natural (out,in), stride ldw)
+// k-vectorised dot products: A loads are warp broadcasts, W loads are conflict free because
+// ldw = 4 (mod 8) words.
+template <int R>
+__device__ __forceinline__ void dot_acc(float (&acc)[R][4], const float* __restrict__ A, int lda,
+                                        const float* __restrict__ W, int ldw, int K) {
+#pragma unroll 2
+  for (int k = 0; k < K; k += 4) {
+    float4 w[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) w[c] = *reinterpret_cast<const float4*>(W + (32 * c) * ldw + k);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float4 a = *reinterpret_cast<const float4*>(A + r * lda + k);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        acc[r][c] = fmaf(a.x, w[c].x, acc[r][c]);
+        acc[r][c] = fmaf(a.y, w[c].y, acc[r][c]);
+        acc[r][c] = fmaf(a.z, w[c].z, acc[r][c]);
+        acc[r][c] = fmaf(a.w, w[c].w, acc[r][c]);
+      }
+    }
+  }
+}
+
+// Stage fc_0 / fc_1 / fc_2 from the flat vector into padded shared-memory images.
+__device__ __forceinline__ void stage_weights(const float* __restrict__ P, const Offsets& O, int FP, int LD0,
+                                              float* sW0, float* sb0, float* sW1, float* sb1, float* sw2,
+                                              float* sb2, int nthreads) {
+  for (int i = threadIdx.x; i < H * LD0; i += nthreads) {
+    const int o = i / LD0, k = i - o * LD0;
+    sW0[i] = k < O.F ? P[O.oW0 + o * O.F + k] : 0.f;
+  }
+  for (int i = threadIdx.x; i < H * LDH; i += nthreads) {
+    const int o = i / LDH, k = i - o * LDH;
+    sW1[i] = k < H ? P[O.oW1 + o * H + k] : 0.f;
+  }
+  for (int i = threadIdx.x; i < H; i += nthreads) {
+    sb0[i] = P[O.ob0 + i]; sb1[i] = P[O.ob1 + i]; sw2[i] = P[O.oW2 + i];
+  }
+  if (threadIdx.x == 0) sb2[0] = P[O.ob2];
+  (void)FP;
+}
+
+}  // namespace mlpb
+
+// =========================================================================================
+// predict: persistent CTAs of 256 threads walk tiles of 64 timesteps.  Warp w owns rows
+// 8w..8w+7, lane l owns output units l, l+32, l+64, l+96 of each hidden layer.
+// =========================================================================================
+namespace mlpb {
+
+constexpr int PT = 256;   // threads
+constexpr int TS = 64;    // timesteps per tile
+constexpr int R = 8;      // rows per thread
+
+struct Smem {
+  int W0, W1, b0, b1, w2, b2, X, H0, H1, total;
+  __host__ __device__ Smem(int F, int xbufs) {
+    const int FP = feat_pad(F), LD0 = w0_stride(F);
+    int o = 0;
+    auto take = [&](int c) { int r = o; o += (c + 3) & ~3; return r; };
+    W0 = take(H * LD0); W1 = take(H * LDH); b0 = take(H); b1 = take(H); w2 = take(H); b2 = take(4);
+    X = take(xbufs * TS * FP); H0 = take(TS * LDH); H1 = take(TS * LDH);
+    total = o;
+  }
+};
+
+// hidden layer on the thread's 8 x 4 tile: out = relu(bias + A W^T)
+__device__ __forceinline__ void hidden_layer(const float* __restrict__ A, int lda, const float* __restrict__ W,
+                                             int ldw, int K, const float* __restrict__ bias,
+                                             float* __restrict__ out, int row0, int lane) {
+  float acc[R][4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const float b = bias[lane + 32 * c];
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r][c] = b;
+  }
+  dot_acc<R>(acc, A + row0 * lda, lda, W + lane * ldw, ldw, K);
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) out[(row0 + r) * LDH + lane + 32 * c] = fmaxf(acc[r][c], 0.f);
+}
+
+// y[b] = b2 + sum_o w2[o] h1[b][o] for the 64 rows: 4 lanes per row, units q, q+4, q+8, ...
+__device__ __forceinline__ float head_row(const float* __restrict__ sH1, const float* __restrict__ sw2, int tid) {
+  const int b = tid >> 2, q = tid & 3;
+  const float* h = sH1 + b * LDH;
+  float s = 0.f;
+#pragma unroll 8
+  for (int k = 0; k < H / 4; ++k) s = fmaf(h[q + 4 * k], sw2[q + 4 * k], s);
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  return s;
+}
+
+__global__ void __launch_bounds__(PT, 1)
+predict_kernel(const float* __restrict__ obs, const int32_t* __restrict__ offsets, int P, long long N, int n,
+               const float* __restrict__ params, double* __restrict__ pred) {
+  extern __shared__ __align__(16) float sm[];
+  const Offsets O(n);
+  const int F = O.F, FP = feat_pad(F), LD0 = w0_stride(F);
+  const Smem L(F, 1);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, row0 = warp * R;
+  float* sX = sm + L.X; float* sH0 = sm + L.H0; float* sH1 = sm + L.H1;
+  stage_weights(params, O, FP, LD0, sm + L.W0, sm + L.b0, sm + L.W1, sm + L.b1, sm + L.w2, sm + L.b2, PT);
+  for (int i = tid; i < TS * FP; i += PT) sX[i] = 0.f;
+  const long long ntiles = (N + TS - 1) / TS;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long t0 = tile * TS;
+    const int rows = (int)min((long long)TS, N - t0);
+    __syncthreads();
+    const float* src = obs + t0 * n;
+    for (int i = tid; i < rows * n; i += PT) {
+      const int r = i / n, c = i - r * n;
+      sX[r * FP + c] = obs_feat(ld_stream(src + i));
+    }
+    if (tid < rows) {
+      const int p = find_path(offsets, P, t0 + tid);
+      float tf[4];
+      time_feats((int)(t0 + tid - offsets[p]), tf);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sX[tid * FP + n + j] = tf[j];
+    }
+    __syncthreads();
+    hidden_layer(sX, FP, sm + L.W0, LD0, FP, sm + L.b0, sH0, row0, lane);
+    __syncthreads();
+    hidden_layer(sH0, LDH, sm + L.W1, LDH, H, sm + L.b1, sH1, row0, lane);
+    __syncthreads();
+    const float y = head_row(sH1, sm + L.w2, tid) + sm[L.b2];
+    if ((tid & 3) == 0 && (tid >> 2) < rows) pred[t0 + (tid >> 2)] = (double)y;
+  }
+}
+
+// sums2 = { sum (y32 - p32)^2 , sum y32^2 } with y32 = (float)returns, p32 = (float)pred
+// (mlp_baseline.py:75-81,98-104 work on fp32 arrays); fp64 accumulation, fixed order.
+__global__ void __launch_bounds__(256) sqerr_partial_kernel(const double* __restrict__ pred,
+                                                            const double* __restrict__ ret, long long N,
+                                                            double* __restrict__ partial) {
+  __shared__ double red[32];
+  double se = 0.0, sy = 0.0;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < N;
+       t += (long long)gridDim.x * blockDim.x) {
+    const float y = (float)ret[t], p = (float)pred[t];
+    const float e = y - p;
+    se += (double)(e * e); sy += (double)(y * y);
+  }
+  se = block_sum(se, red);
+  if (threadIdx.x == 0) partial[2 * blockIdx.x] = se;
+  sy = block_sum(sy, red);
+  if (threadIdx.x == 0) partial[2 * blockIdx.x + 1] = sy;
+}
+__global__ void sqerr_final_kernel(const double* __restrict__ partial, int nparts, double* __restrict__ sums2) {
+  double a = 0.0, b = 0.0;
+  for (int c = threadIdx.x; c < nparts; c += 32) { a += partial[2 * c]; b += partial[2 * c + 1]; }
+  a = warp_sum(a); b = warp_sum(b);
+  if (threadIdx.x == 0) { sums2[0] = a; sums2[1] = b; }
+}
+
+}  // namespace mlpb
+
+// =========================================================================================
+// fit: ONE persistent CTA runs the whole chain of Adam steps (mlp_baseline.py:83-96).
+// Per step (minibatch of <= 64 rows, 256 threads):
+//   wait(cp.async batch s) -> prefetch batch s+1 -> L0 -> L1 -> head/dy -> gw2,gb2 ->
+//   dz1 (in place of h1) -> gW1 tile in registers, gb1 -> dh0 = dz1 W1 -> dz0 (in place of h0)
+//   -> Adam(W1,b1,w2,b2) -> gW0,gb0 -> Adam(W0,b0)
+// =========================================================================================
+namespace mlpb {
+
+struct AdamC {
+  float lr_over_bc1;   // lr / (1 - beta1^t)            (torch: step_size)
+  float bc2_sqrt;      // sqrt(1 - beta2^t)
+  float one_m_b1, b2, one_m_b2, eps, wd;
+};
+
+// torch.optim.Adam single-tensor update (weight_decay added to the gradient; lerp for exp_avg;
+// denom = sqrt(v)/sqrt(bc2) + eps; p -= step_size * m/denom).
+__device__ __forceinline__ float adam(float w, float g, float& m, float& v, const AdamC& c) {
+  g = fmaf(c.wd, w, g);
+  m = m + c.one_m_b1 * (g - m);
+  v = fmaf(c.one_m_b2 * g, g, v * c.b2);
+  const float denom = sqrtf(v) / c.bc2_sqrt + c.eps;
+  return w - c.lr_over_bc1 * (m / denom);
+}
+
+__device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"((uint32_t)__cvta_generic_to_shared(dst_smem)),
+               "l"(src) : "memory");
+}
+
+struct FitArgs {
+  const float* feat;      // [N][F]
+  const float* y32;       // [N]
+  const int32_t* perm;    // [nsteps * bs]
+  float* params;          // [D] in/out
+  float* am;              // Adam exp_avg [D] in/out
+  float* av;              // Adam exp_avg_sq [D] in/out
+  long long nsteps, step0;
+  int n, bs;
+  double lr, beta1, beta2, eps, wd;
+};
+
+__global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  __shared__ AdamC s_adam;
+  __shared__ float s_dy[TS], s_y[2][TS];
+  const Offsets O(a.n);
+  const int F = O.F, FP = feat_pad(F), LD0 = w0_stride(F);
+  const Smem L(F, 2);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, row0 = warp * R;
+  const int bs = a.bs;
+  float* sW0 = sm + L.W0; float* sW1 = sm + L.W1; float* sb0 = sm + L.b0; float* sb1 = sm + L.b1;
+  float* sw2 = sm + L.w2; float* sb2 = sm + L.b2; float* sH0 = sm + L.H0; float* sH1 = sm + L.H1;
+  stage_weights(a.params, O, FP, LD0, sW0, sb0, sW1, sb1, sw2, sb2, PT);
+  for (int i = tid; i < 2 * TS * FP; i += PT) sm[L.X + i] = 0.f;
+  if (tid < TS) { s_y[0][tid] = 0.f; s_y[1][tid] = 0.f; }
+  __syncthreads();
+
+  auto prefetch = [&](long long s) {   // minibatch s -> buffer s & 1
+    float* X = sm + L.X + (int)(s & 1) * TS * FP;
+    const int32_t* idx = a.perm + s * bs;
+    for (int i = tid; i < bs * F; i += PT) {
+      const int b = i / F, k = i - b * F;
+      cp_async4(X + b * FP + k, a.feat + (long long)__ldg(idx + b) * F + k);
+    }
+    if (tid < bs) cp_async4(&s_y[s & 1][tid], a.y32 + __ldg(idx + tid));
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (a.nsteps > 0) prefetch(0);
+
+  // wgrad ownership: fc_1 tile rows o0..o0+7, cols [i0, i0+4) and [64+i0, 64+i0+4) (two float4
+  // columns 64 apart so the 16 lanes that differ in i0 read 256 contiguous bytes: conflict free)
+  const int o0 = 8 * (tid >> 4), i0 = 4 * (tid & 15);
+
+  for (long long s = 0; s < a.nsteps; ++s) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (tid == 0) {
+      const double t = (double)(a.step0 + s + 1);
+      AdamC c;
+      c.lr_over_bc1 = (float)(a.lr / (1.0 - pow(a.beta1, t)));
+      c.bc2_sqrt = (float)sqrt(1.0 - pow(a.beta2, t));
+      c.one_m_b1 = (float)(1.0 - a.beta1); c.b2 = (float)a.beta2; c.one_m_b2 = (float)(1.0 - a.beta2);
+      c.eps = (float)a.eps; c.wd = (float)a.wd;
+      s_adam = c;
+    }
+    __syncthreads();   // batch s landed; previous step's weight updates visible
+    if (s + 1 < a.nsteps) prefetch(s + 1);
+    const float* X = sm + L.X + (int)(s & 1) * TS * FP;
+    const AdamC c = s_adam;
+
+    // ---- forward ------------------------------------------------------------------------
+    hidden_layer(X, FP, sW0, LD0, FP, sb0, sH0, row0, lane);
+    __syncthreads();
+    hidden_layer(sH0, LDH, sW1, LDH, H, sb1, sH1, row0, lane);
+    __syncthreads();
+    {
+      const float y = head_row(sH1, sw2, tid) + sb2[0];
+      const int b = tid >> 2;
+      // MSELoss (mean over the bs x 1 outputs): dL/dyhat = 2 (yhat - y) / bs
+      if ((tid & 3) == 0) s_dy[b] = b < bs ? 2.f * (y - s_y[s & 1][b]) / (float)bs : 0.f;
+    }
+    __syncthreads();
+    // ---- head gradients (threads 0..127: unit o = tid; thread 128: bias) ------------------
+    float gw2 = 0.f, gb2 = 0.f;
+    if (tid < H) {
+#pragma unroll 8
+      for (int b = 0; b < TS; ++b) gw2 = fmaf(s_dy[b], sH1[b * LDH + tid], gw2);
+    } else if (tid == H) {
+      for (int b = 0; b < TS; ++b) gb2 += s_dy[b];
+    }
+    __syncthreads();
+    // ---- dz1 = dy w2^T * (h1 > 0), in place of h1 --------------------------------------------
+    for (int i = tid; i < TS * H; i += PT) {
+      const int b = i >> 7, o = i & (H - 1);
+      const float h = sH1[b * LDH + o];
+      sH1[b * LDH + o] = h > 0.f ? s_dy[b] * sw2[o] : 0.f;
+    }
+    __syncthreads();
+    // ---- gW1 tile (8 x (4+4)) = sum_b dz1[b][o] h0[b][i]; gb1 ------------------------------------
+    float g1[8][8];
+#pragma unroll
+    for (int x = 0; x < 8; ++x)
+#pragma unroll
+      for (int y = 0; y < 8; ++y) g1[x][y] = 0.f;
+#pragma unroll 2
+    for (int b = 0; b < TS; ++b) {
+      const float4 d0 = *reinterpret_cast<const float4*>(sH1 + b * LDH + o0);
+      const float4 d1 = *reinterpret_cast<const float4*>(sH1 + b * LDH + o0 + 4);
+      const float4 h0 = *reinterpret_cast<const float4*>(sH0 + b * LDH + i0);
+      const float4 h1 = *reinterpret_cast<const float4*>(sH0 + b * LDH + i0 + 64);
+      const float dz[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+      const float hh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+      for (int x = 0; x < 8; ++x)
+#pragma unroll
+        for (int y = 0; y < 8; ++y) g1[x][y] = fmaf(dz[x], hh[y], g1[x][y]);
+    }
+    float gb1 = 0.f;
+    if (tid < H) {
+#pragma unroll 8
+      for (int b = 0; b < TS; ++b) gb1 += sH1[b * LDH + tid];
+    }
+    __syncthreads();   // all reads of h0 done before dz0 overwrites it
+    // ---- dh0 = dz1 W1 (old weights), dz0 = dh0 * (h0 > 0) in place of h0 -------------------
+    {
+      float acc[R][4];
+#pragma unroll
+      for (int r = 0; r < R; ++r) acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f;
+      pol::mm_acc<R>(acc, sH1 + row0 * LDH, LDH, sW1 + 4 * lane, LDH, H);
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        float4* p = reinterpret_cast<float4*>(sH0 + (row0 + r) * LDH + 4 * lane);
+        const float4 h = *p;
+        *p = make_float4(h.x > 0.f ? acc[r][0] : 0.f, h.y > 0.f ? acc[r][1] : 0.f,
+                         h.z > 0.f ? acc[r][2] : 0.f, h.w > 0.f ? acc[r][3] : 0.f);
+      }
+    }
+    __syncthreads();   // old W1 fully consumed; dz0 complete
+    // ---- Adam: fc_1 (register tile), fc_1.bias, fc_2 ------------------------------------------
+#pragma unroll
+    for (int x = 0; x < 8; ++x) {
+      const int gi = O.oW1 + (o0 + x) * H + i0;
+      float4* pm = reinterpret_cast<float4*>(a.am + gi);
+      float4* pv = reinterpret_cast<float4*>(a.av + gi);
+      float* pw = sW1 + (o0 + x) * LDH + i0;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        float4 m4 = pm[16 * hh], v4 = pv[16 * hh], w4 = *reinterpret_cast<float4*>(pw + 64 * hh);
+        w4.x = adam(w4.x, g1[x][4 * hh + 0], m4.x, v4.x, c);
+        w4.y = adam(w4.y, g1[x][4 * hh + 1], m4.y, v4.y, c);
+        w4.z = adam(w4.z, g1[x][4 * hh + 2], m4.z, v4.z, c);
+        w4.w = adam(w4.w, g1[x][4 * hh + 3], m4.w, v4.w, c);
+        pm[16 * hh] = m4; pv[16 * hh] = v4; *reinterpret_cast<float4*>(pw + 64 * hh) = w4;
+      }
+    }
+    if (tid < H) {
+      sb1[tid] = adam(sb1[tid], gb1, a.am[O.ob1 + tid], a.av[O.ob1 + tid], c);
+      sw2[tid] = adam(sw2[tid], gw2, a.am[O.oW2 + tid], a.av[O.oW2 + tid], c);
+    } else if (tid == H) {
+      sb2[0] = adam(sb2[0], gb2, a.am[O.ob2], a.av[O.ob2], c);
+    }
+    // ---- gW0 = dz0^T X (float4 chunks of k), gb0; Adam ----------------------------------------
+    const int kchunks = FP / 4;
+    for (int ch = tid; ch < H * kchunks; ch += PT) {
+      const int o = ch / kchunks, k0 = 4 * (ch - o * kchunks);
+      float g[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+      for (int b = 0; b < TS; ++b) {
+        const float d = sH0[b * LDH + o];
+        const float4 x = *reinterpret_cast<const float4*>(X + b * FP + k0);
+        g[0] = fmaf(d, x.x, g[0]); g[1] = fmaf(d, x.y, g[1]); g[2] = fmaf(d, x.z, g[2]); g[3] = fmaf(d, x.w, g[3]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = k0 + j;
+        if (k < F) {
+          const int gi = O.oW0 + o * F + k;
+          sW0[o * LD0 + k] = adam(sW0[o * LD0 + k], g[j], a.am[gi], a.av[gi], c);
+        }
+      }
+    }
+    if (tid < H) {
+      float gb0 = 0.f;
+#pragma unroll 8
+      for (int b = 0; b < TS; ++b) gb0 += sH0[b * LDH + tid];
+      sb0[tid] = adam(sb0[tid], gb0, a.am[O.ob0 + tid], a.av[O.ob0 + tid], c);
+    }
+    // the __syncthreads at the top of the next step orders these writes before its reads
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  // ---- write the master weights back ---------------------------------------------------------
+  for (int i = tid; i < H * F; i += PT) a.params[O.oW0 + i] = sW0[(i / F) * LD0 + (i % F)];
+  for (int i = tid; i < H * H; i += PT) a.params[O.oW1 + i] = sW1[(i >> 7) * LDH + (i & (H - 1))];
+  for (int i = tid; i < H; i += PT) {
+    a.params[O.ob0 + i] = sb0[i]; a.params[O.ob1 + i] = sb1[i]; a.params[O.oW2 + i] = sw2[i];
+  }
+  if (tid == 0) a.params[O.ob2] = sb2[0];
+}
+
+__global__ void cast_y_kernel(const double* __restrict__ ret, long long N, float* __restrict__ y32) {
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < N;
+       t += (long long)gridDim.x * blockDim.x)
+    y32[t] = (float)ret[t];
+}
+
+}  // namespace mlpb
+
+// =========================================================================================
+// C-ABI
+// =========================================================================================
+extern "C" {
+
+int64_t mjrl_mlpbase_param_count(int32_t n) {
+  if (n < 1) return MJRL_E_ARG;
+  return mlpb::Offsets(n).D;
+}
+
+int mjrl_mlpbase_features(mjrl_ctx* ctx, const float* obs, const double* returns,
+                          const int32_t* path_offsets, int32_t P, int64_t N, int32_t n, float* feat,
+                          float* y32, void* stream) {
+  MJRL_REQUIRE(ctx && obs && path_offsets && feat, MJRL_E_ARG, "mlpbase_features: null argument");
+  MJRL_REQUIRE(P >= 0 && N >= 0 && n >= 1, MJRL_E_ARG, "mlpbase_features: bad sizes");
+  if (N == 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = (int)std::min<int64_t>((N + 255) / 256, (int64_t)ctx->sm_count * 8);
+  mlpb::features_kernel<<<grid, 256, 0, s>>>(obs, path_offsets, P, N, n, feat);
+  int rc = mjrl_check_launch("mlpbase_features_kernel");
+  if (rc) return rc;
+  if (returns && y32) {
+    mlpb::cast_y_kernel<<<grid, 256, 0, s>>>(returns, N, y32);
+    rc = mjrl_check_launch("mlpbase_cast_y_kernel");
+  }
+  return rc;
+}
+
+int mjrl_mlpbase_predict(mjrl_ctx* ctx, const float* obs, const int32_t* path_offsets, int32_t P,
+                         int64_t N, int32_t n, const float* params, double* pred, void* stream) {
+  MJRL_REQUIRE(ctx && obs && path_offsets && params && pred, MJRL_E_ARG, "mlpbase_predict: null argument");
+  MJRL_REQUIRE(P >= 0 && N >= 0 && n >= 1, MJRL_E_ARG, "mlpbase_predict: bad sizes");
+  if (N == 0) return 0;
+  const mlpb::Smem L(n + 4, 1);
+  const size_t smem = sizeof(float) * (size_t)L.total;
+  MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE,
+               "mlpbase_predict: obs_dim=%d needs %zu B of shared memory (max %d)", n, smem, ctx->max_smem_optin);
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(mlpb::predict_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         ctx->max_smem_optin);
+    if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    attr = true;
+  }
+  const int64_t ntiles = (N + mlpb::TS - 1) / mlpb::TS;
+  const int grid = (int)std::min<int64_t>(ntiles, ctx->sm_count);
+  mlpb::predict_kernel<<<grid, mlpb::PT, smem, (cudaStream_t)stream>>>(obs, path_offsets, P, N, n, params, pred);
+  return mjrl_check_launch("mlpbase_predict_kernel");
+}
+
+int mjrl_mlpbase_sqerr(mjrl_ctx* ctx, const double* pred, const double* returns, int64_t N,
+                       double* sums2, void* stream) {
+  MJRL_REQUIRE(ctx && pred && returns && sums2, MJRL_E_ARG, "mlpbase_sqerr: null argument");
+  MJRL_REQUIRE(N >= 0, MJRL_E_ARG, "mlpbase_sqerr: bad size");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((N + 255) / 256, (int64_t)ctx->sm_count * 4));
+  double* part = (double*)mjrl_scratch(ctx, sizeof(double) * 2 * grid);
+  if (!part) return MJRL_E_STATE;
+  mlpb::sqerr_partial_kernel<<<grid, 256, 0, s>>>(pred, returns, N, part);
+  int rc = mjrl_check_launch("mlpbase_sqerr_partial_kernel");
+  if (rc) return rc;
+  mlpb::sqerr_final_kernel<<<1, 32, 0, s>>>(part, grid, sums2);
+  return mjrl_check_launch("mlpbase_sqerr_final_kernel");
+}
+
+int mjrl_mlpbase_fit(mjrl_ctx* ctx, const float* feat, const float* y32, int64_t N, int32_t n,
+                     float* params, float* adam_m, float* adam_v, int64_t step0, const int32_t* perm,
+                     int64_t nsteps, int32_t batch, double lr, double beta1, double beta2, double eps,
+                     double weight_decay, void* stream) {
+  MJRL_REQUIRE(ctx && feat && y32 && params && adam_m && adam_v, MJRL_E_ARG, "mlpbase_fit: null argument");
+  MJRL_REQUIRE(N >= 0 && n >= 1 && nsteps >= 0 && step0 >= 0, MJRL_E_ARG, "mlpbase_fit: bad sizes");
+  MJRL_REQUIRE(batch >= 1 && batch <= mlpb::MAXB, MJRL_E_SHAPE,
+               "mlpbase_fit: batch_size=%d not supported (1..%d)", batch, mlpb::MAXB);
+  if (nsteps == 0) return 0;
+  MJRL_REQUIRE(perm, MJRL_E_ARG, "mlpbase_fit: null permutation");
+  const mlpb::Smem L(n + 4, 2);
+  const size_t smem = sizeof(float) * (size_t)L.total;
+  MJRL_REQUIRE(smem + 1024 <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE,
+               "mlpbase_fit: obs_dim=%d needs %zu B of shared memory (max %d)", n, smem, ctx->max_smem_optin);
+  static size_t attr = 0;   // fit_kernel also has ~1 KB of static shared memory
+  if (smem > attr) {
+    cudaError_t e = cudaFuncSetAttribute(mlpb::fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    attr = smem;
+  }
+  mlpb::FitArgs a;
+  a.feat = feat; a.y32 = y32; a.perm = perm; a.params = params; a.am = adam_m; a.av = adam_v;
+  a.nsteps = nsteps; a.step0 = step0; a.n = n; a.bs = batch;
+  a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.wd = weight_decay;
+  mlpb::fit_kernel<<<1, mlpb::PT, smem, (cudaStream_t)stream>>>(a);
+  return mjrl_check_launch("mlpbase_fit_kernel");
+}
+
+}  // extern "C"

@@ -176,8 +176,46 @@ def run_case(R, name, n, m, hidden, horizon, N, seed, mid, algo="npg"):
     print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
 
 
+def run_mlpbase_case(R, name, n, horizon, N, seed, epochs, reg_coef):
+    """MLPBaseline (mlp_baseline.py): seed-for-seed init, predictions, one full fit() with the
+    minibatch permutations it drew from numpy's global stream, errors, final weights."""
+    import torch
+    from mjrl_b200.utils import synthetic as syn
+    spec = R.EnvSpec(n, 3, horizon, 1)
+    zero = np.zeros(n * 4 + 4 + 4 * 4 + 4 + 4 * 3 + 3 + 3, dtype=np.float32)
+    b = syn.make_flat_batch(N, n, 3, horizon, seed, zero, (4, 4))
+    paths = syn.flat_to_paths(b)
+    R.ps.compute_returns(paths, 0.995)
+    torch.manual_seed(seed)
+    base = R.mb.MLPBaseline(spec, reg_coef=reg_coef, batch_size=64, epochs=epochs)
+    flat = lambda: np.concatenate([p.data.numpy().ravel() for p in base.model.parameters()]).astype(np.float32)
+    out = dict(n=n, horizon=horizon, N=N, seed=seed, epochs=epochs, reg_coef=reg_coef, batch_size=64,
+               numpy_version=np.__version__, torch_version=torch.__version__,
+               observations=b["observations"], rewards=b["rewards"], path_offsets=b["path_offsets"],
+               terminated=b["terminated"], returns=np.concatenate([p["returns"] for p in paths]),
+               init_params=flat(), features=base._features(paths).astype(np.float32))
+    out["pred_before"] = np.concatenate([base.predict(p) for p in paths])
+    np.random.seed(seed + 1)
+    eb, ea = base.fit(paths, return_errors=True)
+    np.random.seed(seed + 1)
+    out["perms"] = np.stack([np.random.permutation(N) for _ in range(epochs)])
+    out["errors"] = np.asarray([eb, ea], dtype=np.float64)
+    out["fit_params"] = flat()
+    out["pred_after"] = np.concatenate([base.predict(p) for p in paths])
+    # the optimiser state persists across fit() calls: a second fit continues the Adam chain
+    base.fit(paths)
+    out["fit2_params"] = flat()
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
+
+
 if __name__ == "__main__":
     R = import_reference()
+    if "--mlpbase-only" in sys.argv:
+        run_mlpbase_case(R, "mlpbase_1step", 11, 60, 150, 7000, 1, 0.0)
+        run_mlpbase_case(R, "mlpbase_hopper", 11, 200, 1500, 7001, 2, 1e-3)
+        sys.exit(0)
     #            name            n   m  hidden    hor   N     seed  mid
     run_case(R, "c1_linear",     6,  2, (),        25, 1000, 1000, False)
     run_case(R, "c2_swimmer",   12,  4, (32, 32), 500, 4000, 2000, False)
@@ -185,3 +223,5 @@ if __name__ == "__main__":
     run_case(R, "c3_hopper_mid", 11, 3, (64, 64), 200, 3000, 3001, True)
     run_case(R, "c5_adroit_mid", 45, 24, (32, 32), 100, 2000, 5000, True)
     run_case(R, "c1_linear_mid", 6,  2, (),        25, 1000, 1001, True)
+    run_mlpbase_case(R, "mlpbase_1step", 11, 60, 150, 7000, 1, 0.0)
+    run_mlpbase_case(R, "mlpbase_hopper", 11, 200, 1500, 7001, 2, 1e-3)
