@@ -18,6 +18,7 @@
 //   fc_0.weight [128][F] | fc_0.bias [128] | fc_1.weight [128][128] | fc_1.bias [128] |
 //   fc_2.weight [1][128] | fc_2.bias [1]          F = n + 4
 #include <algorithm>
+#include <stdlib.h>
 
 #include "policy_tile.cuh"
 
@@ -278,6 +279,7 @@ struct FitArgs {
   long long nsteps, step0;
   int n, bs;
   double lr, beta1, beta2, eps, wd;
+  long long* phase_cycles;   // debug (MJRL_B200_PHASE_CYCLES): 12 per-phase cycle sums of thread 0
 };
 
 __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
@@ -312,6 +314,8 @@ __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
   // columns 64 apart so the 16 lanes that differ in i0 read 256 contiguous bytes: conflict free)
   const int o0 = 8 * (tid >> 4), i0 = 4 * (tid & 15);
 
+  long long ph[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+#define FIT_STAMP(q) if (a.phase_cycles && tid == 0) { const long long now = clock64(); ph[q] += now - tprev; tprev = now; }
   for (long long s = 0; s < a.nsteps; ++s) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     if (tid == 0) {
@@ -324,15 +328,19 @@ __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
       s_adam = c;
     }
     __syncthreads();   // batch s landed; previous step's weight updates visible
+    FIT_STAMP(0);
     if (s + 1 < a.nsteps) prefetch(s + 1);
     const float* X = sm + L.X + (int)(s & 1) * TS * FP;
     const AdamC c = s_adam;
+    FIT_STAMP(1);
 
     // ---- forward ------------------------------------------------------------------------
     hidden_layer(X, FP, sW0, LD0, FP, sb0, sH0, row0, lane);
     __syncthreads();
+    FIT_STAMP(2);
     hidden_layer(sH0, LDH, sW1, LDH, H, sb1, sH1, row0, lane);
     __syncthreads();
+    FIT_STAMP(3);
     {
       const float y = head_row(sH1, sw2, tid) + sb2[0];
       const int b = tid >> 2;
@@ -349,6 +357,7 @@ __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
       for (int b = 0; b < TS; ++b) gb2 += s_dy[b];
     }
     __syncthreads();
+    FIT_STAMP(4);
     // ---- dz1 = dy w2^T * (h1 > 0), in place of h1 --------------------------------------------
     for (int i = tid; i < TS * H; i += PT) {
       const int b = i >> 7, o = i & (H - 1);
@@ -356,6 +365,7 @@ __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
       sH1[b * LDH + o] = h > 0.f ? s_dy[b] * sw2[o] : 0.f;
     }
     __syncthreads();
+    FIT_STAMP(5);
     // ---- gW1 tile (8 x (4+4)) = sum_b dz1[b][o] h0[b][i]; gb1 ------------------------------------
     float g1[8][8];
 #pragma unroll
@@ -381,6 +391,7 @@ __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
       for (int b = 0; b < TS; ++b) gb1 += sH1[b * LDH + tid];
     }
     __syncthreads();   // all reads of h0 done before dz0 overwrites it
+    FIT_STAMP(6);
     // ---- dh0 = dz1 W1 (old weights), dz0 = dh0 * (h0 > 0) in place of h0 -------------------
     {
       float acc[R][4];
@@ -396,6 +407,7 @@ __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
       }
     }
     __syncthreads();   // old W1 fully consumed; dz0 complete
+    FIT_STAMP(7);
     // ---- Adam: fc_1 (register tile), fc_1.bias, fc_2 ------------------------------------------
 #pragma unroll
     for (int x = 0; x < 8; ++x) {
@@ -419,6 +431,7 @@ __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
     } else if (tid == H) {
       sb2[0] = adam(sb2[0], gb2, a.am[O.ob2], a.av[O.ob2], c);
     }
+    FIT_STAMP(8);
     // ---- gW0 = dz0^T X (float4 chunks of k), gb0; Adam ----------------------------------------
     const int kchunks = FP / 4;
     for (int ch = tid; ch < H * kchunks; ch += PT) {
@@ -445,8 +458,11 @@ __global__ void __launch_bounds__(PT, 1) fit_kernel(const FitArgs a) {
       for (int b = 0; b < TS; ++b) gb0 += sH0[b * LDH + tid];
       sb0[tid] = adam(sb0[tid], gb0, a.am[O.ob0 + tid], a.av[O.ob0 + tid], c);
     }
+    FIT_STAMP(9);
     // the __syncthreads at the top of the next step orders these writes before its reads
   }
+  if (a.phase_cycles && tid == 0)
+    for (int q = 0; q < 12; ++q) a.phase_cycles[q] = ph[q];
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
   // ---- write the master weights back ---------------------------------------------------------
@@ -462,6 +478,360 @@ __global__ void cast_y_kernel(const double* __restrict__ ret, long long N, float
   for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < N;
        t += (long long)gridDim.x * blockDim.x)
     y32[t] = (float)ret[t];
+}
+
+}  // namespace mlpb
+
+
+// =========================================================================================
+// fit, cluster version: ONE thread-block cluster of 8 CTAs runs the serial Adam chain.
+//
+// The chain is latency bound (15,624 dependent steps at N = 1M, 3.4 Mflop each), so the step is
+// split MODEL-parallel over the cluster: CTA c owns hidden units U_c = [16c, 16c+16) of both
+// layers -- rows U_c of fc_0 / fc_1, entries U_c of the biases and of fc_2 -- with their Adam
+// moments, all resident in its shared memory for the whole chain.  Per step three small
+// exchanges go over distributed shared memory as bulk async copies (cp.async.bulk
+// shared::cta -> shared::cluster) that signal an mbarrier in the RECEIVING CTA:
+//   E1  all-gather  h0[:, U_c]           (4 KB to each peer)        before layer 1
+//   E2  all-gather  partial head output  (256 B to each peer)       before dy
+//   E3  reduce-scatter of dh0 partials   (4 KB to each peer)        before dz0
+// Exchange buffers are double buffered by step parity; because every CTA needs data from every
+// peer in every step, no CTA can run more than one step ahead, so no cluster barrier is needed
+// inside the loop.  Sums over peers are taken in rank order, so all CTAs compute bit-identical
+// dy and the result does not depend on timing.
+// =========================================================================================
+namespace mlpb {
+
+constexpr int CL = 8;            // CTAs per cluster
+constexpr int UC = H / CL;       // hidden units owned per CTA (16)
+constexpr int SS = TS * UC + 16; // slice stride (floats) of slice-major [CL][64][16] buffers: = 16 (mod 32)
+constexpr int LDU = UC + 4;      // row stride of the per-CTA [64][16] matrices
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_cta(const void* p, uint32_t rank) {
+  uint32_t a = (uint32_t)__cvta_generic_to_shared(p), r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_init1(uint64_t* b) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((uint32_t)__cvta_generic_to_shared(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_arm(uint64_t* b, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+               :: "r"((uint32_t)__cvta_generic_to_shared(b)), "r"(bytes) : "memory");
+}
+// bounded wait: a protocol bug traps instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait_parity(uint64_t* b, uint32_t parity) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(b);
+  uint32_t ok = 0;
+  for (long long it = 0; !ok; ++it) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "selp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    if (it > (1ll << 24)) __trap();
+  }
+}
+// local shared memory -> the same buffer of CTA `rank`, completing `bytes` on its mbarrier
+__device__ __forceinline__ void bulk_to_peer(void* dst_local_equiv, const void* src, uint32_t bytes,
+                                             uint64_t* bar_local_equiv, uint32_t rank) {
+  const uint32_t d = map_to_cta(dst_local_equiv, rank), m = map_to_cta(bar_local_equiv, rank);
+  const uint32_t s = (uint32_t)__cvta_generic_to_shared(src);
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(d), "r"(s), "r"(bytes), "r"(m) : "memory");
+}
+
+struct CSmem {   // offsets in floats
+  int W0, M0, V0, W1, M1, V1, vec, X, H0, H1, P, RECV, DZ0, YP, total;
+  __host__ __device__ explicit CSmem(int F) {
+    const int FP = feat_pad(F), LD0 = w0_stride(F);
+    int o = 0;
+    auto take = [&](int c) { int r = o; o += (c + 3) & ~3; return r; };
+    W0 = take(UC * LD0); M0 = take(UC * LD0); V0 = take(UC * LD0);
+    W1 = take(UC * LDH); M1 = take(UC * LDH); V1 = take(UC * LDH);
+    vec = take(16 * UC);           // b0,b1,w2 (+m,v each) , b2,m,v
+    X = take(2 * TS * FP);
+    H0 = take(2 * CL * SS);        // all-gathered h0, slice-major, double buffered
+    H1 = take(TS * LDU);           // own h1 slice, then dz1
+    P = take(CL * SS);             // dh0 partials for every destination slice
+    RECV = take(CL * SS);          // dh0 partials received from every source
+    DZ0 = take(TS * LDU);
+    YP = take(CL * TS);            // head partials from every source
+    total = o;
+  }
+};
+
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_kernel(const FitArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  __shared__ __align__(8) uint64_t barH[2], barY[2], barR[2];
+  __shared__ AdamC s_adam;
+  __shared__ float s_dy[TS], s_y[2][TS];
+  const Offsets O(a.n);
+  const int F = O.F, FP = feat_pad(F), LD0 = w0_stride(F);
+  const CSmem L(F);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int c = (int)cluster_rank();
+  const int u0 = c * UC;               // first owned unit
+  const int bs = a.bs;
+  float* sW0 = sm + L.W0; float* sM0 = sm + L.M0; float* sV0 = sm + L.V0;
+  float* sW1 = sm + L.W1; float* sM1 = sm + L.M1; float* sV1 = sm + L.V1;
+  float* sb0 = sm + L.vec;            float* sb0m = sb0 + UC; float* sb0v = sb0 + 2 * UC;
+  float* sb1 = sm + L.vec + 3 * UC;   float* sb1m = sb1 + UC; float* sb1v = sb1 + 2 * UC;
+  float* sw2 = sm + L.vec + 6 * UC;   float* sw2m = sw2 + UC; float* sw2v = sw2 + 2 * UC;
+  float* sb2 = sm + L.vec + 9 * UC;   // [0] b2, [1] m, [2] v  (replicated in every CTA)
+  float* sH1 = sm + L.H1; float* sP = sm + L.P; float* sDZ0 = sm + L.DZ0;
+
+  // ---- stage the owned rows and their Adam moments --------------------------------------------
+  for (int i = tid; i < UC * LD0; i += PT) {
+    const int u = i / LD0, k = i - u * LD0;
+    const int gi = O.oW0 + (u0 + u) * F + k;
+    const bool in = k < F;
+    sW0[i] = in ? a.params[gi] : 0.f; sM0[i] = in ? a.am[gi] : 0.f; sV0[i] = in ? a.av[gi] : 0.f;
+  }
+  for (int i = tid; i < UC * LDH; i += PT) {
+    const int u = i / LDH, k = i - u * LDH;
+    const int gi = O.oW1 + (u0 + u) * H + k;
+    const bool in = k < H;
+    sW1[i] = in ? a.params[gi] : 0.f; sM1[i] = in ? a.am[gi] : 0.f; sV1[i] = in ? a.av[gi] : 0.f;
+  }
+  if (tid < UC) {
+    sb0[tid] = a.params[O.ob0 + u0 + tid]; sb0m[tid] = a.am[O.ob0 + u0 + tid]; sb0v[tid] = a.av[O.ob0 + u0 + tid];
+    sb1[tid] = a.params[O.ob1 + u0 + tid]; sb1m[tid] = a.am[O.ob1 + u0 + tid]; sb1v[tid] = a.av[O.ob1 + u0 + tid];
+    sw2[tid] = a.params[O.oW2 + u0 + tid]; sw2m[tid] = a.am[O.oW2 + u0 + tid]; sw2v[tid] = a.av[O.oW2 + u0 + tid];
+  }
+  if (tid == 0) {
+    sb2[0] = a.params[O.ob2]; sb2[1] = a.am[O.ob2]; sb2[2] = a.av[O.ob2];
+    for (int p = 0; p < 2; ++p) { mbar_init1(&barH[p]); mbar_init1(&barY[p]); mbar_init1(&barR[p]); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int i = tid; i < 2 * TS * FP; i += PT) sm[L.X + i] = 0.f;
+  if (tid < TS) { s_y[0][tid] = 0.f; s_y[1][tid] = 0.f; }
+  __syncthreads();
+  cluster_sync_all();   // every CTA's barriers are initialised before any peer signals them
+
+  auto prefetch = [&](long long s) {   // minibatch s -> buffer s & 1 (every CTA loads the same rows)
+    float* X = sm + L.X + (int)(s & 1) * TS * FP;
+    const int32_t* idx = a.perm + s * bs;
+    const int cnt = bs * F;
+    for (int i0 = tid; i0 < cnt; i0 += 4 * PT) {
+      long long row[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int i = i0 + j * PT;
+        row[j] = i < cnt ? (long long)__ldg(idx + i / F) : 0;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int i = i0 + j * PT;
+        if (i < cnt) { const int b = i / F, k = i - b * F; cp_async4(X + b * FP + k, a.feat + row[j] * F + k); }
+      }
+    }
+    if (tid < bs) cp_async4(&s_y[s & 1][tid], a.y32 + __ldg(idx + tid));
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (a.nsteps > 0) prefetch(0);
+
+  const int u = tid & 15, r0 = 4 * (tid >> 4);        // (unit, 4 rows) tiling of the [64][16] products
+  const int gu = tid >> 4, gi0 = 4 * (tid & 15);      // fc_1 gradient: unit gu, inputs gi0..+3 and 64+gi0..+3
+
+  for (long long s = 0; s < a.nsteps; ++s) {
+    const int p = (int)(s & 1);
+    const uint32_t par = (uint32_t)((s >> 1) & 1);
+    float* sH0 = sm + L.H0 + p * CL * SS;
+    // Only h0 needs two buffers: a peer that has my E3 data can finish step s and send its next
+    // h0 slice while this CTA still reads h0 for the fc_1 gradient.  E2/E3 data of step s+1 can
+    // only be sent after this CTA's own step-(s+1) h0 went out, i.e. after it left step s.
+    float* sRECV = sm + L.RECV;
+    float* sYP = sm + L.YP;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (tid == 0) {
+      const double t = (double)(a.step0 + s + 1);
+      AdamC ac;
+      ac.lr_over_bc1 = (float)(a.lr / (1.0 - pow(a.beta1, t)));
+      ac.bc2_sqrt = (float)sqrt(1.0 - pow(a.beta2, t));
+      ac.one_m_b1 = (float)(1.0 - a.beta1); ac.b2 = (float)a.beta2; ac.one_m_b2 = (float)(1.0 - a.beta2);
+      ac.eps = (float)a.eps; ac.wd = (float)a.wd;
+      s_adam = ac;
+      mbar_arm(&barH[p], (CL - 1) * TS * UC * 4);
+      mbar_arm(&barY[p], (CL - 1) * TS * 4);
+      mbar_arm(&barR[p], (CL - 1) * TS * UC * 4);
+    }
+    __syncthreads();
+    if (s + 1 < a.nsteps) prefetch(s + 1);
+    const float* X = sm + L.X + p * TS * FP;
+    const AdamC ac = s_adam;
+
+    // ---- L0: own slice of h0 -> sH0[c], then all-gather (E1) ---------------------------------
+    {
+      float acc[4];
+      const float b = sb0[u];
+      acc[0] = acc[1] = acc[2] = acc[3] = b;
+      for (int k = 0; k < FP; k += 4) {
+        const float4 w = *reinterpret_cast<const float4*>(sW0 + u * LD0 + k);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float4 x = *reinterpret_cast<const float4*>(X + (r0 + r) * FP + k);
+          acc[r] = fmaf(x.x, w.x, acc[r]); acc[r] = fmaf(x.y, w.y, acc[r]);
+          acc[r] = fmaf(x.z, w.z, acc[r]); acc[r] = fmaf(x.w, w.w, acc[r]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) sH0[c * SS + (r0 + r) * UC + u] = fmaxf(acc[r], 0.f);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (tid < CL && tid != c) bulk_to_peer(sH0 + c * SS, sH0 + c * SS, TS * UC * 4, &barH[p], (uint32_t)tid);
+    mbar_wait_parity(&barH[p], par);
+
+    // ---- L1: own slice of h1; head partial -> E2 -----------------------------------------------
+    {
+      float acc[4];
+      const float b = sb1[u];
+      acc[0] = acc[1] = acc[2] = acc[3] = b;
+#pragma unroll 4
+      for (int k = 0; k < H; k += 4) {
+        const float4 w = *reinterpret_cast<const float4*>(sW1 + u * LDH + k);
+        const float* hs = sH0 + (k >> 4) * SS + (k & 15);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float4 x = *reinterpret_cast<const float4*>(hs + (r0 + r) * UC);
+          acc[r] = fmaf(x.x, w.x, acc[r]); acc[r] = fmaf(x.y, w.y, acc[r]);
+          acc[r] = fmaf(x.z, w.z, acc[r]); acc[r] = fmaf(x.w, w.w, acc[r]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) sH1[(r0 + r) * LDU + u] = fmaxf(acc[r], 0.f);
+    }
+    __syncthreads();
+    if (tid < TS) {
+      float y = 0.f;
+#pragma unroll
+      for (int k = 0; k < UC; ++k) y = fmaf(sH1[tid * LDU + k], sw2[k], y);
+      sYP[c * TS + tid] = y;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (tid < CL && tid != c) bulk_to_peer(sYP + c * TS, sYP + c * TS, TS * 4, &barY[p], (uint32_t)tid);
+    mbar_wait_parity(&barY[p], par);
+    if (tid < TS) {
+      float y = sb2[0];
+#pragma unroll
+      for (int q = 0; q < CL; ++q) y += sYP[q * TS + tid];     // rank order: identical in every CTA
+      s_dy[tid] = tid < bs ? 2.f * (y - s_y[p][tid]) / (float)bs : 0.f;
+    }
+    __syncthreads();
+    // ---- head gradients, dz1 in place of h1 ------------------------------------------------------
+    float gw2 = 0.f, gb2 = 0.f;
+    if (tid < UC) {
+      for (int b = 0; b < TS; ++b) gw2 = fmaf(s_dy[b], sH1[b * LDU + tid], gw2);
+    } else if (tid == 32) {
+      for (int b = 0; b < TS; ++b) gb2 += s_dy[b];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const float h = sH1[(r0 + r) * LDU + u];
+      sH1[(r0 + r) * LDU + u] = h > 0.f ? s_dy[r0 + r] * sw2[u] : 0.f;
+    }
+    __syncthreads();
+    // ---- dh0 partials over the owned units for ALL inputs -> sP (slice-major), E3 -------------
+    {
+      float acc[R][4];
+#pragma unroll
+      for (int r = 0; r < R; ++r) acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f;
+      pol::mm_acc<R>(acc, sH1 + (warp * R) * LDU, LDU, sW1 + 4 * lane, LDH, UC);
+      float* dst = sP + (lane >> 2) * SS + 4 * (lane & 3);
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        *reinterpret_cast<float4*>(dst + (warp * R + r) * UC) = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (tid < CL && tid != c) bulk_to_peer(sRECV + c * SS, sP + tid * SS, TS * UC * 4, &barR[p], (uint32_t)tid);
+    // ---- (overlaps E3) fc_1 gradient for the owned rows: 8 entries per thread; gb1 -------------
+    float g1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    {
+      const float* ha = sH0 + (gi0 >> 4) * SS + (gi0 & 15);
+      const float* hb = sH0 + ((gi0 + 64) >> 4) * SS + (gi0 & 15);
+#pragma unroll 4
+      for (int b = 0; b < TS; ++b) {
+        const float d = sH1[b * LDU + gu];
+        const float4 x = *reinterpret_cast<const float4*>(ha + b * UC);
+        const float4 y = *reinterpret_cast<const float4*>(hb + b * UC);
+        g1[0] = fmaf(d, x.x, g1[0]); g1[1] = fmaf(d, x.y, g1[1]); g1[2] = fmaf(d, x.z, g1[2]); g1[3] = fmaf(d, x.w, g1[3]);
+        g1[4] = fmaf(d, y.x, g1[4]); g1[5] = fmaf(d, y.y, g1[5]); g1[6] = fmaf(d, y.z, g1[6]); g1[7] = fmaf(d, y.w, g1[7]);
+      }
+    }
+    float gb1 = 0.f;
+    if (tid < UC)
+      for (int b = 0; b < TS; ++b) gb1 += sH1[b * LDU + tid];
+    // ---- Adam on fc_1 rows (old rows were last read by the dh0 partials above) -----------------
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int o = gu * LDH + gi0 + 64 * hh;
+      float4 w4 = *reinterpret_cast<float4*>(sW1 + o), m4 = *reinterpret_cast<float4*>(sM1 + o),
+             v4 = *reinterpret_cast<float4*>(sV1 + o);
+      w4.x = adam(w4.x, g1[4 * hh + 0], m4.x, v4.x, ac); w4.y = adam(w4.y, g1[4 * hh + 1], m4.y, v4.y, ac);
+      w4.z = adam(w4.z, g1[4 * hh + 2], m4.z, v4.z, ac); w4.w = adam(w4.w, g1[4 * hh + 3], m4.w, v4.w, ac);
+      *reinterpret_cast<float4*>(sW1 + o) = w4; *reinterpret_cast<float4*>(sM1 + o) = m4;
+      *reinterpret_cast<float4*>(sV1 + o) = v4;
+    }
+    if (tid < UC) {
+      sb1[tid] = adam(sb1[tid], gb1, sb1m[tid], sb1v[tid], ac);
+      sw2[tid] = adam(sw2[tid], gw2, sw2m[tid], sw2v[tid], ac);
+    } else if (tid == 32) {
+      sb2[0] = adam(sb2[0], gb2, sb2[1], sb2[2], ac);
+    }
+    // ---- reduce the received dh0 partials (rank order), dz0 = dh0 * (h0 > 0) -----------------
+    mbar_wait_parity(&barR[p], par);
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int e = (r0 + r) * UC + u;
+      float dsum = 0.f;
+#pragma unroll
+      for (int q = 0; q < CL; ++q) dsum += (q == c) ? sP[c * SS + e] : sRECV[q * SS + e];
+      sDZ0[(r0 + r) * LDU + u] = sH0[c * SS + e] > 0.f ? dsum : 0.f;
+    }
+    __syncthreads();
+    // ---- fc_0 gradient for the owned rows + Adam ------------------------------------------------
+    for (int e = tid; e < UC * FP; e += PT) {
+      const int uu = e / FP, k = e - uu * FP;
+      if (k < F) {
+        float g = 0.f;
+#pragma unroll 8
+        for (int b = 0; b < TS; ++b) g = fmaf(sDZ0[b * LDU + uu], X[b * FP + k], g);
+        const int o = uu * LD0 + k;
+        sW0[o] = adam(sW0[o], g, sM0[o], sV0[o], ac);
+      }
+    }
+    if (tid < UC) {
+      float gb0 = 0.f;
+      for (int b = 0; b < TS; ++b) gb0 += sDZ0[b * LDU + tid];
+      sb0[tid] = adam(sb0[tid], gb0, sb0m[tid], sb0v[tid], ac);
+    }
+    // the __syncthreads at the top of the next step orders these writes before its reads
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  // ---- write back the owned rows and moments -----------------------------------------------------
+  for (int i = tid; i < UC * F; i += PT) {
+    const int uu = i / F, k = i - uu * F, gi = O.oW0 + (u0 + uu) * F + k, o = uu * LD0 + k;
+    a.params[gi] = sW0[o]; a.am[gi] = sM0[o]; a.av[gi] = sV0[o];
+  }
+  for (int i = tid; i < UC * H; i += PT) {
+    const int uu = i >> 7, k = i & (H - 1), gi = O.oW1 + (u0 + uu) * H + k, o = uu * LDH + k;
+    a.params[gi] = sW1[o]; a.am[gi] = sM1[o]; a.av[gi] = sV1[o];
+  }
+  if (tid < UC) {
+    a.params[O.ob0 + u0 + tid] = sb0[tid]; a.am[O.ob0 + u0 + tid] = sb0m[tid]; a.av[O.ob0 + u0 + tid] = sb0v[tid];
+    a.params[O.ob1 + u0 + tid] = sb1[tid]; a.am[O.ob1 + u0 + tid] = sb1m[tid]; a.av[O.ob1 + u0 + tid] = sb1v[tid];
+    a.params[O.oW2 + u0 + tid] = sw2[tid]; a.am[O.oW2 + u0 + tid] = sw2m[tid]; a.av[O.oW2 + u0 + tid] = sw2v[tid];
+  }
+  if (c == 0 && tid == 0) { a.params[O.ob2] = sb2[0]; a.am[O.ob2] = sb2[1]; a.av[O.ob2] = sb2[2]; }
+  cluster_sync_all();   // no CTA exits while a peer may still address its shared memory
 }
 
 }  // namespace mlpb
@@ -555,6 +925,36 @@ int mjrl_mlpbase_fit(mjrl_ctx* ctx, const float* feat, const float* y32, int64_t
   a.feat = feat; a.y32 = y32; a.perm = perm; a.params = params; a.am = adam_m; a.av = adam_v;
   a.nsteps = nsteps; a.step0 = step0; a.n = n; a.bs = batch;
   a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.wd = weight_decay;
+  a.phase_cycles = nullptr;
+  // Cluster kernel (8 CTAs, model parallel over hidden units) unless it does not fit or
+  // MJRL_B200_MLPFIT=single asks for the one-CTA chain.
+  {
+    const mlpb::CSmem LC(n + 4);
+    const size_t csmem = sizeof(float) * (size_t)LC.total;
+    static const char* mode = getenv("MJRL_B200_MLPFIT");
+    if (!(mode && mode[0] == 's') && csmem + 1024 <= (size_t)ctx->max_smem_optin) {
+      static size_t cattr = 0;
+      if (csmem > cattr) {
+        cudaError_t e = cudaFuncSetAttribute(mlpb::fit_cluster_kernel,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem);
+        if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+        cattr = csmem;
+      }
+      mlpb::fit_cluster_kernel<<<mlpb::CL, mlpb::PT, csmem, (cudaStream_t)stream>>>(a);
+      return mjrl_check_launch("mlpbase_fit_cluster_kernel");
+    }
+  }
+  static const bool dbg = getenv("MJRL_B200_PHASE_CYCLES") != nullptr;
+  if (dbg) {
+    long long* dev; cudaMalloc(&dev, sizeof(long long) * 12);
+    a.phase_cycles = dev;
+    mlpb::fit_kernel<<<1, mlpb::PT, smem, (cudaStream_t)stream>>>(a);
+    cudaStreamSynchronize((cudaStream_t)stream);
+    long long h[12]; cudaMemcpy(h, dev, sizeof(h), cudaMemcpyDeviceToHost); cudaFree(dev);
+    const char* nm[10] = {"wait+sync", "prefetch", "L0", "L1", "head+gw2", "dz1", "gW1+gb1", "dgrad", "adam1", "gW0+adam0"};
+    for (int q = 0; q < 10; ++q) fprintf(stderr, "[fit phase] %-10s %8.0f cycles/step\n", nm[q], (double)h[q] / nsteps);
+    return mjrl_check_launch("mlpbase_fit_kernel(dbg)");
+  }
   mlpb::fit_kernel<<<1, mlpb::PT, smem, (cudaStream_t)stream>>>(a);
   return mjrl_check_launch("mlpbase_fit_kernel");
 }
