@@ -637,6 +637,10 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
   const int u = tid & 15, r0 = 4 * (tid >> 4);        // (unit, 4 rows) tiling of the [64][16] products
   const int gu = tid >> 4, gi0 = 4 * (tid & 15);      // fc_1 gradient: unit gu, inputs gi0..+3 and 64+gi0..+3
 
+  // beta^t by recurrence (thread 0): fp64 pow() every step would cost ~2k cycles of the chain
+  double b1t = pow(a.beta1, (double)a.step0), b2t = pow(a.beta2, (double)a.step0);
+  long long ph[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+#define CL_STAMP(q) if (a.phase_cycles && tid == 0 && c == 0) { const long long now = clock64(); ph[q] += now - tprev; tprev = now; }
   for (long long s = 0; s < a.nsteps; ++s) {
     const int p = (int)(s & 1);
     const uint32_t par = (uint32_t)((s >> 1) & 1);
@@ -648,10 +652,10 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
     float* sYP = sm + L.YP;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     if (tid == 0) {
-      const double t = (double)(a.step0 + s + 1);
+      b1t *= a.beta1; b2t *= a.beta2;
       AdamC ac;
-      ac.lr_over_bc1 = (float)(a.lr / (1.0 - pow(a.beta1, t)));
-      ac.bc2_sqrt = (float)sqrt(1.0 - pow(a.beta2, t));
+      ac.lr_over_bc1 = (float)(a.lr / (1.0 - b1t));
+      ac.bc2_sqrt = (float)sqrt(1.0 - b2t);
       ac.one_m_b1 = (float)(1.0 - a.beta1); ac.b2 = (float)a.beta2; ac.one_m_b2 = (float)(1.0 - a.beta2);
       ac.eps = (float)a.eps; ac.wd = (float)a.wd;
       s_adam = ac;
@@ -663,6 +667,7 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
     if (s + 1 < a.nsteps) prefetch(s + 1);
     const float* X = sm + L.X + p * TS * FP;
     const AdamC ac = s_adam;
+    CL_STAMP(0);
 
     // ---- L0: own slice of h0 -> sH0[c], then all-gather (E1) ---------------------------------
     {
@@ -684,7 +689,9 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     if (tid < CL && tid != c) bulk_to_peer(sH0 + c * SS, sH0 + c * SS, TS * UC * 4, &barH[p], (uint32_t)tid);
+    CL_STAMP(1);
     mbar_wait_parity(&barH[p], par);
+    CL_STAMP(2);
 
     // ---- L1: own slice of h1; head partial -> E2 -----------------------------------------------
     {
@@ -715,7 +722,9 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     if (tid < CL && tid != c) bulk_to_peer(sYP + c * TS, sYP + c * TS, TS * 4, &barY[p], (uint32_t)tid);
+    CL_STAMP(3);
     mbar_wait_parity(&barY[p], par);
+    CL_STAMP(4);
     if (tid < TS) {
       float y = sb2[0];
 #pragma unroll
@@ -751,6 +760,7 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     if (tid < CL && tid != c) bulk_to_peer(sRECV + c * SS, sP + tid * SS, TS * UC * 4, &barR[p], (uint32_t)tid);
+    CL_STAMP(5);
     // ---- (overlaps E3) fc_1 gradient for the owned rows: 8 entries per thread; gb1 -------------
     float g1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     {
@@ -786,7 +796,9 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
       sb2[0] = adam(sb2[0], gb2, sb2[1], sb2[2], ac);
     }
     // ---- reduce the received dh0 partials (rank order), dz0 = dh0 * (h0 > 0) -----------------
+    CL_STAMP(6);
     mbar_wait_parity(&barR[p], par);
+    CL_STAMP(7);
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
       const int e = (r0 + r) * UC + u;
@@ -796,6 +808,7 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
       sDZ0[(r0 + r) * LDU + u] = sH0[c * SS + e] > 0.f ? dsum : 0.f;
     }
     __syncthreads();
+    CL_STAMP(9);
     // ---- fc_0 gradient for the owned rows + Adam ------------------------------------------------
     for (int e = tid; e < UC * FP; e += PT) {
       const int uu = e / FP, k = e - uu * FP;
@@ -807,13 +820,17 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
         sW0[o] = adam(sW0[o], g, sM0[o], sV0[o], ac);
       }
     }
+    CL_STAMP(10);
     if (tid < UC) {
       float gb0 = 0.f;
       for (int b = 0; b < TS; ++b) gb0 += sDZ0[b * LDU + tid];
       sb0[tid] = adam(sb0[tid], gb0, sb0m[tid], sb0v[tid], ac);
     }
+    CL_STAMP(8);
     // the __syncthreads at the top of the next step orders these writes before its reads
   }
+  if (a.phase_cycles && tid == 0 && c == 0)
+    for (int q = 0; q < 12; ++q) a.phase_cycles[q] = ph[q];
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
   // ---- write back the owned rows and moments -----------------------------------------------------
@@ -939,6 +956,18 @@ int mjrl_mlpbase_fit(mjrl_ctx* ctx, const float* feat, const float* y32, int64_t
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem);
         if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
         cattr = csmem;
+      }
+      static const bool cdbg = getenv("MJRL_B200_PHASE_CYCLES") != nullptr;
+      if (cdbg) {
+        long long* dev; cudaMalloc(&dev, sizeof(long long) * 12);
+        a.phase_cycles = dev;
+        mlpb::fit_cluster_kernel<<<mlpb::CL, mlpb::PT, csmem, (cudaStream_t)stream>>>(a);
+        cudaStreamSynchronize((cudaStream_t)stream);
+        long long h[12]; cudaMemcpy(h, dev, sizeof(h), cudaMemcpyDeviceToHost); cudaFree(dev);
+        const char* nm[11] = {"top(wait,sync,prefetch)", "L0+E1 issue", "E1 wait", "L1+head+E2 issue", "E2 wait",
+                              "dy,gw2,dz1,dgrad,E3 issue", "gW1+adam1", "E3 wait", "gb0+adam (tail)", "dz0 reduce+sync", "gW0+adam0"};
+        for (int q = 0; q < 11; ++q) fprintf(stderr, "[cluster fit] %-28s %8.0f cycles/step\n", nm[q], (double)h[q] / nsteps);
+        return mjrl_check_launch("mlpbase_fit_cluster_kernel(dbg)");
       }
       mlpb::fit_cluster_kernel<<<mlpb::CL, mlpb::PT, csmem, (cudaStream_t)stream>>>(a);
       return mjrl_check_launch("mlpbase_fit_cluster_kernel");
