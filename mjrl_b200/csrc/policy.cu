@@ -41,18 +41,21 @@ struct Args {
   long long* phase_cycles;  // debug: [grid][8] cycles per phase (P0,P1,P2,P3a,P3b,P4,P5,P6+loop)
   long long N;
   int n, m, h1, h2, dstride;
+  int prefetch;   // 1: double-buffered obs/act staging (Layout::XR/AR present)
 };
 
 // Shared-memory carve-up (offsets in floats), identical on host and device.
 struct Layout {
   int TS, LDH, LDW, NP, LDX, MP, LDM;
-  int X, H1, H2, B1, B2, U, E, ACT, S0, S1;
+  int X, H1, H2, B1, B2, U, E, ACT, S0, S1, XR, AR;
   int W0t, b0, W1t, b1, W2t, b2, W1, W2, V0t, vb0, V1t, vb1, V2t, vb2;
   int ishift, iden, oscale, oshift, sig, ls, ols_, fisher;
   int total;
   // mma: tensor-core path.  obs width padded to 8 (k-steps of the m16n8k8 MMA), k-major weight
   // stride HP+8 (= 8 mod 32) so B-fragment loads are conflict free; activations keep HP+4 (= 4 mod 8).
-  __host__ __device__ Layout(int HP, int n, int m, int mode, bool mma) {
+  // prefetch: raw staging of the NEXT tile's obs (and actions), filled by cp.async while the
+  // current tile computes.
+  __host__ __device__ Layout(int HP, int n, int m, int mode, bool mma, bool prefetch = false) {
     const int NF = HP / 4, NT = NTHREADS / NF;
     TS = RT * NT; LDH = HP + 4; LDW = mma ? HP + 8 : HP + 4;
     NP = mma ? ((n + 7) & ~7) : round4(n); LDX = NP + 4; MP = round4(m); LDM = MP + 4;
@@ -66,6 +69,8 @@ struct Layout {
     E = mode == M_GRAD ? take(TS * LDM) : 0;
     ACT = mode != M_FVP ? take(TS * LDM) : 0;
     S0 = take(TS); S1 = take(TS);
+    XR = prefetch ? take(TS * n) : 0;
+    AR = (prefetch && mode != M_FVP) ? take(TS * m) : 0;
     W0t = take(NP * LDW); b0 = take(HP); W1t = take(HP * LDW); b1 = take(HP);
     W2t = take(HP * LDM); b2 = take(MP);
     W1 = bwd ? take(HP * LDW) : 0; W2 = bwd ? take(MP * LDH) : 0;
@@ -144,7 +149,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
   extern __shared__ __align__(16) float sm[];
   if (MODE == M_FVP && a.stop_flag && *a.stop_flag) return;
 
-  const Layout L(HP, a.n, a.m, MODE, MMA);
+  const Layout L(HP, a.n, a.m, MODE, MMA, a.prefetch != 0);
   const Flat F(a.n, a.m, a.h1, a.h2);
   const int tid = threadIdx.x;
   const int NP = L.NP, LDX = L.LDX, MP = L.MP, LDM = L.LDM;
@@ -209,7 +214,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
 
   // persistent register accumulators
   float acc0[MMA ? 1 : W0SLOTS][16], acc1[16], acc2[16], cb0[4], cb1[4];
-  float gb2acc = 0.f, glsacc = 0.f;
+  float gb2acc[4] = {0.f, 0.f, 0.f, 0.f}, glsacc[4] = {0.f, 0.f, 0.f, 0.f};  // warp w: dims w, w+8, ... (lane 0)
   double surr_acc = 0.0, kl_acc = 0.0;
   if (BWD) {
 #pragma unroll
@@ -240,13 +245,52 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
   }
   if (a.phase_cycles && tid == 0) tprev = clock64();
   const long long ntiles = (a.N + TS - 1) / TS;
+  // cp.async staging of a tile's raw obs (and action) rows: 16 B chunks when the source is
+  // 16 B aligned (TS*n*4 is a multiple of 16, so every tile start is), 4 B copies otherwise.
+  auto stage_rows = [&](float* dst, const float* src, int cnt) {
+    const bool al = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+    const int nvec = al ? (cnt >> 2) : 0;
+    for (int i = tid; i < nvec; i += NTHREADS)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                   :: "r"((uint32_t)__cvta_generic_to_shared(dst + 4 * i)), "l"(src + 4 * i) : "memory");
+    for (int i = 4 * nvec + tid; i < cnt; i += NTHREADS)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;"
+                   :: "r"((uint32_t)__cvta_generic_to_shared(dst + i)), "l"(src + i) : "memory");
+  };
+  auto stage_tile = [&](long long tile) {
+    const long long t0 = tile * TS;
+    const int rows = (int)min((long long)TS, a.N - t0);
+    stage_rows(sm + L.XR, a.obs + t0 * n, rows * n);
+    if (MODE != M_FVP && a.act) stage_rows(sm + L.AR, a.act + t0 * m, rows * m);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (a.prefetch && (long long)blockIdx.x < ntiles) stage_tile(blockIdx.x);
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const long long t0 = tile * TS;
     const int rows = (int)min((long long)TS, a.N - t0);
-    __syncthreads();  // previous tile fully consumed
+    if (a.prefetch) asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();  // previous tile fully consumed; staged rows of this tile visible
     PHASE_STAMP(7);
     // ---- P0: obs tile (+ actions) -> smem, input transform --------------------------------
-    {
+    if (a.prefetch) {
+      // this tile's raw rows were staged by cp.async during the previous tile
+      float* sXR = sm + L.XR; float* sAR = sm + L.AR;
+      const int cnt = rows * n;
+      for (int i = tid; i < cnt; i += NTHREADS) {
+        int r = i / n, c = i - r * n;
+        sX[r * LDX + c] = (sXR[i] - sm[L.ishift + c]) / sm[L.iden + c];
+      }
+      if (rows < TS)
+        for (int i = tid; i < (TS - rows) * NP; i += NTHREADS) {
+          int r = rows + i / NP, c = i % NP;
+          sX[r * LDX + c] = 0.f;
+        }
+      if (MODE != M_FVP && a.act)
+        for (int i = tid; i < rows * m; i += NTHREADS) {
+          int r = i / m, c = i - r * m;
+          sAct[r * LDM + c] = sAR[i];
+        }
+    } else {
       const float* src = a.obs + t0 * n;
       const int cnt = rows * n;
       for (int i = tid; i < cnt; i += NTHREADS) {
@@ -267,6 +311,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
     }
     __syncthreads();
+    if (a.prefetch && tile + gridDim.x < ntiles) stage_tile(tile + gridDim.x);
     PHASE_STAMP(0);
     // ---- P1: layer 0 ----------------------------------------------------------------------
     if constexpr (MMA) {
@@ -330,22 +375,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
     }
     __syncthreads();
     PHASE_STAMP(2);
-    // ---- P3a: head.  4 lanes split K for one timestep, shuffle-reduce -----------------------
+    // ---- P3a: head.  4 lanes split K for one timestep (lane q takes k = q, q+4, ...: the
+    // activation reads of a warp then cover all 32 banks and the four weight rows of one step
+    // sit in four different bank groups), shuffle-reduce ------------------------------------
     {
       const int q = tid & 3;
       constexpr int KQ = HP / 4;
       for (int t = tid >> 2; t < TS; t += NTHREADS / 4) {
-        const float* h2 = sH2 + t * LDH + q * KQ;
-        const float* d2 = sB2 + t * LDH + q * KQ;
+        const float* h2 = sH2 + t * LDH + q;
+        const float* d2 = sB2 + t * LDH + q;
         for (int jt = 0; jt < MP; jt += 4) {
           float s[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 4
+#pragma unroll 8
           for (int k = 0; k < KQ; ++k) {
-            const float hv = h2[k];
-            const float4 wv = *reinterpret_cast<const float4*>(sm + L.W2t + (q * KQ + k) * LDM + jt);
+            const float hv = h2[4 * k];
+            const float4 wv = *reinterpret_cast<const float4*>(sm + L.W2t + (q + 4 * k) * LDM + jt);
             if (MODE == M_FVP) {
-              const float dv = d2[k];
-              const float4 vv = *reinterpret_cast<const float4*>(sm + L.V2t + (q * KQ + k) * LDM + jt);
+              const float dv = d2[4 * k];
+              const float4 vv = *reinterpret_cast<const float4*>(sm + L.V2t + (q + 4 * k) * LDM + jt);
               s[0] = fmaf(hv, vv.x, s[0]); s[1] = fmaf(hv, vv.y, s[1]);
               s[2] = fmaf(hv, vv.z, s[2]); s[3] = fmaf(hv, vv.w, s[3]);
               s[0] = fmaf(dv, wv.x, s[0]); s[1] = fmaf(dv, wv.y, s[1]);
@@ -456,10 +503,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
         if (own2.active)
           wgrad_acc(acc2, sU, LDM, sH2, LDH, 4 * (own2.tile / NF), 4 * (own2.tile % NF), own2.grp,
                     own2.G, TS);
-        if (tid < MP) {
-          float s = 0.f, e = 0.f;
-          for (int t = 0; t < TS; ++t) { s += sU[t * LDM + tid]; if (MODE == M_GRAD) e += sE[t * LDM + tid]; }
-          gb2acc += s; glsacc += e;
+        // fc2.bias / log_std gradients: column sums over the tile, one warp per action dimension
+        // (lanes over timesteps, fixed-order shuffle reduction)
+#pragma unroll
+        for (int ji = 0; ji < 4; ++ji) {
+          const int j = ji * 8 + warp;
+          if (j < MP) {
+            float sacc = 0.f, eacc = 0.f;
+            for (int t = lane; t < TS; t += 32) {
+              sacc += sU[t * LDM + j];
+              if (MODE == M_GRAD) eacc += sE[t * LDM + j];
+            }
+            sacc = warp_sum(sacc);
+            if (MODE == M_GRAD) eacc = warp_sum(eacc);
+            gb2acc[ji] += sacc; glsacc[ji] += eacc;
+          }
         }
       }
       __syncthreads();
@@ -627,9 +685,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
       __syncthreads();
     }
-    if (tid < m) {
-      sG[F.ob2 + tid] = gb2acc;
-      sG[F.ols + tid] = glsacc;  // FVP: 0 here, the log_std block is filled by the finalize kernel
+    if (lane == 0) {
+#pragma unroll
+      for (int ji = 0; ji < 4; ++ji) {
+        const int j = ji * 8 + warp;
+        if (j < m) {
+          sG[F.ob2 + j] = gb2acc[ji];
+          sG[F.ols + j] = glsacc[ji];  // FVP: 0 here, the log_std block is filled by the finalize kernel
+        }
+      }
     }
     __syncthreads();
     float* out = a.partials + (size_t)blockIdx.x * a.dstride;
@@ -757,7 +821,10 @@ int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
     slots = bwd ? (nf0 + 7) / 8 : 1;
     if (sizeof(float) * (size_t)Lm.total > (size_t)ctx->max_smem_optin || slots > 8) mma = false;
   }
-  const Layout L(HP, a.n, a.m, MODE, mma);
+  MJRL_REQUIRE(a.m <= 32, MJRL_E_SHAPE, "policy: act_dim %d > 32 is not supported by the MLP kernels", a.m);
+  // double-buffer the obs/act rows when the staging area fits next to everything else
+  a.prefetch = sizeof(float) * (size_t)Layout(HP, a.n, a.m, MODE, mma, true).total <= (size_t)ctx->max_smem_optin;
+  const Layout L(HP, a.n, a.m, MODE, mma, a.prefetch != 0);
   const size_t smem = sizeof(float) * (size_t)L.total;
   MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE,
                "policy: obs_dim=%d act_dim=%d hidden=%d needs %zu B of shared memory (max %d)", a.n,

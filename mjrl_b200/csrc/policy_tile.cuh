@@ -152,14 +152,17 @@ namespace pol {
 struct Frag4 { uint32_t hi[4], lo[4]; };
 struct Frag2 { uint32_t hi[2], lo[2]; };
 
+// Split with full-rate integer ALU ops instead of cvt.rna.tf32.f32 (a conversion-pipe instruction
+// whose throughput, not the tensor pipe, bounded the MMA loops): adding half a TF32 ulp to the bit
+// pattern and clearing the 13 low mantissa bits rounds to nearest (ties away); the tensor core
+// ignores the low 13 bits of a .tf32 operand, so `lo` only needs the half-ulp add.
 __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
-  const float r = x - __uint_as_float(hi);
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+  hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
+  lo = __float_as_uint(x - __uint_as_float(hi)) + 0x1000u;
 }
 
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
-  asm volatile(
+  asm(
       "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
       : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
@@ -212,14 +215,31 @@ __device__ __forceinline__ void mma_layer(float (&z)[2][2][4], float (&dz)[2][2]
       load_b(w[ni], Wt + k0 * ldw + ni * 8, ldw, g, c);
       if (DUAL) load_b(v[ni], Vt + k0 * ldw + ni * 8, ldw, g, c);
     }
+    // Issue order: one split term at a time across ALL accumulators, so that two MMAs on the same
+    // accumulator are 4-12 instructions apart (a warp issues in order; back-to-back dependent
+    // mma.sync stall for the full MMA latency and leave the tensor pipe half empty).
 #pragma unroll
-    for (int mi = 0; mi < 2; ++mi)
+    for (int term = 0; term < 3; ++term) {
 #pragma unroll
-      for (int ni = 0; ni < 2; ++ni) {
-        mma3(z[mi][ni], a[mi], w[ni]);
-        if (DUAL) mma3(dz[mi][ni], a[mi], v[ni]);
-        if (HAS_D) mma3(dz[mi][ni], d[mi], w[ni]);
+      for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 2; ++ni)
+          mma_tf32(z[mi][ni], term == 0 ? a[mi].lo : a[mi].hi, term == 1 ? w[ni].lo : w[ni].hi);
+      if (DUAL) {
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+          for (int ni = 0; ni < 2; ++ni)
+            mma_tf32(dz[mi][ni], term == 0 ? a[mi].lo : a[mi].hi, term == 1 ? v[ni].lo : v[ni].hi);
       }
+      if (HAS_D) {
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+          for (int ni = 0; ni < 2; ++ni)
+            mma_tf32(dz[mi][ni], term == 0 ? d[mi].lo : d[mi].hi, term == 1 ? w[ni].lo : w[ni].hi);
+      }
+    }
   }
 }
 
@@ -229,18 +249,36 @@ template <int NFR>
 __device__ __forceinline__ void mma_wgrad(float (&acc)[NFR][4], const float* __restrict__ A_s, int lda,
                                           const float* __restrict__ B_s, int ldb, int m0, int n0, int nvalid,
                                           int TS, int g, int c) {
-  for (int t0 = 0; t0 < TS; t0 += 8) {
-    Frag4 a;
-    load_a_t(a, A_s + t0 * lda + m0, lda, g, c);
+  // Two independent accumulator sets (even / odd timestep blocks) double the number of MMAs
+  // that can be in flight between two uses of the same accumulator; summed once per call.
+  float odd[NFR][4];
 #pragma unroll
-    for (int j = 0; j < NFR; ++j) {
+  for (int j = 0; j < NFR; ++j) odd[j][0] = odd[j][1] = odd[j][2] = odd[j][3] = 0.f;
+  for (int t0 = 0; t0 < TS; t0 += 16) {
+    Frag4 a0, a1;
+    Frag2 b0[NFR], b1[NFR];
+    load_a_t(a0, A_s + t0 * lda + m0, lda, g, c);
+    load_a_t(a1, A_s + (t0 + 8) * lda + m0, lda, g, c);
+#pragma unroll
+    for (int j = 0; j < NFR; ++j)
       if (j < nvalid) {
-        Frag2 b;
-        load_b(b, B_s + t0 * ldb + n0 + 8 * j, ldb, g, c);
-        mma3(acc[j], a, b);
+        load_b(b0[j], B_s + t0 * ldb + n0 + 8 * j, ldb, g, c);
+        load_b(b1[j], B_s + (t0 + 8) * ldb + n0 + 8 * j, ldb, g, c);
       }
+#pragma unroll
+    for (int term = 0; term < 3; ++term) {  // term-major order: see mma_layer
+#pragma unroll
+      for (int j = 0; j < NFR; ++j)
+        if (j < nvalid) mma_tf32(acc[j], term == 0 ? a0.lo : a0.hi, term == 1 ? b0[j].lo : b0[j].hi);
+#pragma unroll
+      for (int j = 0; j < NFR; ++j)
+        if (j < nvalid) mma_tf32(odd[j], term == 0 ? a1.lo : a1.hi, term == 1 ? b1[j].lo : b1[j].hi);
     }
   }
+#pragma unroll
+  for (int j = 0; j < NFR; ++j)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc[j][e] += odd[j][e];
 }
 
 }  // namespace pol
