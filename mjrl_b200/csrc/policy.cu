@@ -134,7 +134,7 @@ __device__ __forceinline__ void mma_fwd_layer(const float* __restrict__ A, const
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         const int row = mrow0 + mi * 16 + g + half * 8, col = ncol0 + ni * 8 + 2 * c;
-        const float h0 = tanhf(z[mi][ni][2 * half]), h1 = tanhf(z[mi][ni][2 * half + 1]);
+        const float h0 = tanh_fast(z[mi][ni][2 * half]), h1 = tanh_fast(z[mi][ni][2 * half + 1]);
         *reinterpret_cast<float2*>(Hout + row * ldo + col) = make_float2(h0, h1);
         if (DUAL)
           *reinterpret_cast<float2*>(Dout + row * ldo + col) =
@@ -333,7 +333,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
 #pragma unroll
       for (int r = 0; r < RT; ++r) {
-        float4 h = make_float4(tanhf(z[r][0]), tanhf(z[r][1]), tanhf(z[r][2]), tanhf(z[r][3]));
+        float4 h = make_float4(tanh_fast(z[r][0]), tanh_fast(z[r][1]), tanh_fast(z[r][2]), tanh_fast(z[r][3]));
         *reinterpret_cast<float4*>(sH1 + (row0 + r) * LDH + col0) = h;
         if (MODE == M_FVP) {
           float4 d = make_float4((1.f - h.x * h.x) * dz[r][0], (1.f - h.y * h.y) * dz[r][1],
@@ -364,7 +364,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
 #pragma unroll
       for (int r = 0; r < RT; ++r) {
-        float4 h = make_float4(tanhf(z[r][0]), tanhf(z[r][1]), tanhf(z[r][2]), tanhf(z[r][3]));
+        float4 h = make_float4(tanh_fast(z[r][0]), tanh_fast(z[r][1]), tanh_fast(z[r][2]), tanh_fast(z[r][3]));
         *reinterpret_cast<float4*>(sH2 + (row0 + r) * LDH + col0) = h;
         if (MODE == M_FVP) {
           float4 d = make_float4((1.f - h.x * h.x) * dz[r][0], (1.f - h.y * h.y) * dz[r][1],

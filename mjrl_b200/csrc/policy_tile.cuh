@@ -154,11 +154,30 @@ struct Frag2 { uint32_t hi[2], lo[2]; };
 
 // Split with full-rate integer ALU ops instead of cvt.rna.tf32.f32 (a conversion-pipe instruction
 // whose throughput, not the tensor pipe, bounded the MMA loops): adding half a TF32 ulp to the bit
-// pattern and clearing the 13 low mantissa bits rounds to nearest (ties away); the tensor core
-// ignores the low 13 bits of a .tf32 operand, so `lo` only needs the half-ulp add.
+// pattern and clearing the 13 low mantissa bits rounds to nearest (ties away).  lo = x - hi is
+// exact and has <= 12 significant bits; the tensor core ignores the low 13 bits of a .tf32
+// operand, i.e. truncates it to 11 (one bit, symmetric around zero: ~2^-23 |x|).
 __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
   hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
-  lo = __float_as_uint(x - __uint_as_float(hi)) + 0x1000u;
+  lo = __float_as_uint(x - __uint_as_float(hi));
+}
+
+// tanh to ~1.5 ulp without branches: odd minimax polynomial x + x^3 Q(x^2) on |x| < 0.6
+// (7.8e-8 relative, fitted offline), 1 - 2/(exp(2|x|) + 1) through ex2.approx / rcp.approx
+// beyond.  tanhf() costs ~2.5x the instructions here because both of its branches execute in
+// a warp whose lanes straddle its threshold.
+__device__ __forceinline__ float tanh_fast(float x) {
+  const float ax = fabsf(x), u = x * x;
+  float q = fmaf(u, -0.005909046623855829f, 0.02080880105495453f);
+  q = fmaf(q, u, -0.05378798395395279f);
+  q = fmaf(q, u, 0.13331978023052216f);
+  q = fmaf(q, u, -0.33333301544189453f);
+  const float p = fmaf(x * u, q, x);
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(ax * 2.8853900817779268f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.f));
+  const float t = copysignf(fmaf(-2.f, r, 1.f), x);
+  return ax < 0.6f ? p : t;
 }
 
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
@@ -181,12 +200,21 @@ __device__ __forceinline__ void load_a(Frag4& f, const float* __restrict__ p, in
   split_tf32(p[g * ld + c + 4], f.hi[2], f.lo[2]);
   split_tf32(p[(g + 8) * ld + c + 4], f.hi[3], f.lo[3]);
 }
-// A[m][k] = S[k][m] (the k index walks rows of S); p = &S[k0][m0]
+// Weight-gradient operands (k walks the rows = timesteps of an activation matrix whose row stride
+// is = 4 mod 8 words).  The MMA's k index j is mapped to row 2j (j < 4) / 2(j-4)+1 (j >= 4) of the
+// 8-row block -- any permutation of k is fine as long as A and B use the same one -- so that the
+// four k values a warp touches per load sit 8 banks apart: 8c + g covers all 32 banks.
+// A[m][k] = S[perm(k)][m]; p = &S[t0][m0]
 __device__ __forceinline__ void load_a_t(Frag4& f, const float* __restrict__ p, int ld, int g, int c) {
-  split_tf32(p[c * ld + g], f.hi[0], f.lo[0]);
-  split_tf32(p[c * ld + g + 8], f.hi[1], f.lo[1]);
-  split_tf32(p[(c + 4) * ld + g], f.hi[2], f.lo[2]);
-  split_tf32(p[(c + 4) * ld + g + 8], f.hi[3], f.lo[3]);
+  split_tf32(p[(2 * c) * ld + g], f.hi[0], f.lo[0]);
+  split_tf32(p[(2 * c) * ld + g + 8], f.hi[1], f.lo[1]);
+  split_tf32(p[(2 * c + 1) * ld + g], f.hi[2], f.lo[2]);
+  split_tf32(p[(2 * c + 1) * ld + g + 8], f.hi[3], f.lo[3]);
+}
+// B[k][n] = S[perm(k)][n]; p = &S[t0][n0]
+__device__ __forceinline__ void load_b_t(Frag2& f, const float* __restrict__ p, int ld, int g, int c) {
+  split_tf32(p[(2 * c) * ld + g], f.hi[0], f.lo[0]);
+  split_tf32(p[(2 * c + 1) * ld + g], f.hi[1], f.lo[1]);
 }
 // B[k][n] = S[k][n]; p = &S[k0][n0]
 __device__ __forceinline__ void load_b(Frag2& f, const float* __restrict__ p, int ld, int g, int c) {
@@ -202,6 +230,7 @@ __device__ __forceinline__ void mma_layer(float (&z)[2][2][4], float (&dz)[2][2]
                                           const float* __restrict__ A, const float* __restrict__ D, int lda,
                                           const float* __restrict__ Wt, const float* __restrict__ Vt, int ldw,
                                           int K, int g, int c) {
+#pragma unroll 2
   for (int k0 = 0; k0 < K; k0 += 8) {
     Frag4 a[2], d[2];
     Frag2 w[2], v[2];
@@ -262,8 +291,8 @@ __device__ __forceinline__ void mma_wgrad(float (&acc)[NFR][4], const float* __r
 #pragma unroll
     for (int j = 0; j < NFR; ++j)
       if (j < nvalid) {
-        load_b(b0[j], B_s + t0 * ldb + n0 + 8 * j, ldb, g, c);
-        load_b(b1[j], B_s + (t0 + 8) * ldb + n0 + 8 * j, ldb, g, c);
+        load_b_t(b0[j], B_s + t0 * ldb + n0 + 8 * j, ldb, g, c);
+        load_b_t(b1[j], B_s + (t0 + 8) * ldb + n0 + 8 * j, ldb, g, c);
       }
 #pragma unroll
     for (int term = 0; term < 3; ++term) {  // term-major order: see mma_layer
