@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--workload", default=WORKLOAD)
     ap.add_argument("--timesteps", type=int, default=0, help="override timesteps per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--baseline", default="linear", choices=["linear", "mlp"],
+                    help="value baseline inside the timed update: LinearBaseline (north_star (b), default) or "
+                         "MLPBaseline (BASELINE.json configs[2]; its fit is a serial chain of Adam steps)")
     ap.add_argument("--phases", action="store_true", help="also print a per-phase breakdown to stderr")
     return ap.parse_args()
 
@@ -201,7 +204,14 @@ def run_b200(args):
     spec = EnvSpec(n, m, horizon, 1)
     pol = MLP(spec, hidden_sizes=hidden, seed=123) if hidden else LinearPolicy(spec, seed=123)
     flat0 = pol.get_param_values()
-    base = LinearBaseline(spec)
+    use_mlp = args.baseline == "mlp"
+    if use_mlp:
+        from mjrl_b200.baselines.mlp_baseline import MLPBaseline
+        torch.manual_seed(7)
+        np.random.seed(7 + rank)
+        base = MLPBaseline(spec, epochs=1)
+    else:
+        base = LinearBaseline(spec)
     agent = NPG(None, pol, base, normalized_step_size=STEP,
                 FIM_invert_args={"iters": CG_ITERS, "damping": DAMPING})
 
@@ -221,14 +231,23 @@ def run_b200(args):
     warm = PathBatch(h_obs, h_act, h_rew, off, term, device=local)
     from mjrl_b200.utils import process_samples as ps
     ps.returns_on_device(warm, GAMMA)
-    ar = agent._engine().dist.allreduce if world > 1 else None
-    base.fit_batch(warm, allreduce=ar)
-    coeffs0 = np.asarray(base._coeffs).copy()
+    base.fit_batch(warm, dist=agent._engine().dist if world > 1 else None)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+    if use_mlp:
+        st0 = {k: v.clone() for k, v in base._state(dev).items()}
+        step0 = base.adam_step
 
-    def reset():
-        pol.set_param_values(flat0.copy(), True, True)
-        base._coeffs = coeffs0.copy()
+        def reset():
+            pol.set_param_values(flat0.copy(), True, True)
+            for k, v in base._state(dev).items():
+                v.copy_(st0[k])
+            base.adam_step = step0
+    else:
+        coeffs0 = np.asarray(base._coeffs).copy()
+
+        def reset():
+            pol.set_param_values(flat0.copy(), True, True)
+            base._coeffs = coeffs0.copy()
 
     resident = PathBatch(h_obs, h_act, h_rew, off, term, device=local)
 
@@ -284,7 +303,7 @@ def run_b200(args):
         td.all_reduce(te, op=td.ReduceOp.MAX)
     e2e_s = float(te.item()) / args.steps
     d = int(pol.d)
-    d2h = 4 * d + 8 * (2 + 1 + 4) + 8 * 4 + 8 * (n + 4)
+    d2h = 4 * d + 8 * (2 + 1 + 4) + 8 * 4 + (4 * 18689 if use_mlp else 8 * (n + 4))
     e2e = {"value": N * world / e2e_s, "unit": "timesteps/s", "ms_per_step": 1e3 * e2e_s,
            "h2d_bytes_per_step": int(b.h2d_bytes), "d2h_bytes_per_step": int(d2h)}
 
@@ -310,17 +329,32 @@ def run_b200(args):
     fvp_bytes = 4.0 * n                                   # FVP reads obs only
     ach = N * fvp_bytes / (fvp_ms * 1e-3) / 1e9
     fma_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12          # nominal fp32 FMA peak at max clock
+    bf16_peak = None
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        bf16_peak = float(json.load(open(pk)).get("bf16_tflops", 0.0)) or None
+    tensor_peak, tensor_src = (bf16_peak, peak_src) if bf16_peak else (1590.0, "fallback (B200_PROFILING.md)")
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "r01_fvp_traffic.json")
+    if os.path.exists(tp) and args.workload == "C3-hopper":
+        traffic = float(json.load(open(tp))["dram_bytes_per_timestep"]) * N
+    ach_tf = N * fvp_flop / (fvp_ms * 1e-3) / 1e12
     roofline = {
         "kernel": "mlp_kernel<FVP> (analytic Fisher-vector product, %d per update)" % CG_ITERS,
-        "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-        "peak_source": peak_src, "traffic": None, "ms_per_launch": fvp_ms,
+        "bound": "tensor", "achieved": ach_tf, "peak": tensor_peak, "unit": "TFLOP/s",
+        "frac": ach_tf / tensor_peak, "peak_source": tensor_src + ", dense bf16 burst",
+        "traffic": traffic, "traffic_source": "ncu dram bytes of one launch (profiles/r01_fvp_traffic.json) scaled by N",
+        "ms_per_launch": fvp_ms, "algorithmic_flop_per_timestep": fvp_flop,
         "algorithmic_bytes_per_timestep": fvp_bytes,
-        "note": "this pass is fp32-FMA bound, not HBM bound (SURVEY F13/H3: %.0f flop per byte); "
-                "see fp32_fma for the binding roofline" % (fvp_flop / fvp_bytes),
-        "fp32_fma": {"achieved_tflops": N * fvp_flop / (fvp_ms * 1e-3) / 1e12,
-                     "peak_tflops_nominal": fma_peak,
-                     "frac": N * fvp_flop / (fvp_ms * 1e-3) / 1e12 / fma_peak,
-                     "flop_per_timestep": fvp_flop},
+        "note": "compute bound (%.0f flop per byte, SURVEY F13/H3).  The pass must hold fp32 accuracy "
+                "(1e-4 parity gate, measured ~1e-6), so every algorithmic flop is 3 TF32 tensor flops "
+                "(a_hi*b_hi + a_hi*b_lo + a_lo*b_hi) on the mma.sync path; TF32 dense peak is half the "
+                "bf16 peak used as denominator here.  fp32_fma and hbm give the other two rooflines."
+                % (fvp_flop / fvp_bytes),
+        "tensor_flops_issued_tflops": 3.0 * ach_tf,
+        "fp32_fma": {"achieved_tflops": ach_tf, "peak_tflops_nominal": fma_peak,
+                     "frac": ach_tf / fma_peak, "flop_per_timestep": fvp_flop},
+        "hbm": {"achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak},
         "whole_update_hbm": {"bytes_per_timestep": 56 * n + 16 * m + 88,
                              "achieved": N * (56 * n + 16 * m + 88) / (ms_step * 1e-3) / 1e9,
                              "frac": N * (56 * n + 16 * m + 88) / (ms_step * 1e-3) / 1e9 / hbm_peak},
@@ -329,6 +363,9 @@ def run_b200(args):
     if args.phases and rank == 0:
         phase_breakdown(agent, resident, eng, N, n, m, hbm_peak)
 
+    mlp_extra = None
+    if rank == 0 and world == 1 and not use_mlp:
+        mlp_extra = mlpbase_timing(spec, resident, N)
     cb = None
     if rank == 0 and not args.no_cpu_baseline:
         cb = cpu_baseline(args.workload)
@@ -338,17 +375,43 @@ def run_b200(args):
             "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "%s: NPG + %s + LinearBaseline, obs %d act %d, %d timesteps per GPU "
+            "config": {"workload": "%s: NPG + %s + %s, obs %d act %d, %d timesteps per GPU "
                                    "(%d paths), gamma %.3f lambda %.2f, %d CG iters, damping %g"
-                                   % (args.workload, "MLP%s" % (hidden,) if hidden else "LinearPolicy", n, m,
+                                   % (args.workload, "MLP%s" % (hidden,) if hidden else "LinearPolicy",
+                                      "MLPBaseline(epochs=1, batch 64: %d serial Adam steps)" % base.last_fit_steps
+                                      if use_mlp else "LinearBaseline", n, m,
                                       N, len(off) - 1, GAMMA, LAM, CG_ITERS, DAMPING),
                        "parallelism": "dp%d (whole paths per GPU)" % world,
                        "l2": "256 MB buffer written between timed steps (outside the event brackets)",
                        "policy_reset_each_step": True},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
-            "cpu_baseline": cb}))
+            "cpu_baseline": cb, "mlp_baseline": mlp_extra}))
     if world > 1:
         td.destroy_process_group()
+
+
+def mlpbase_timing(spec, batch, N):
+    """MLPBaseline (BASELINE.json configs[2]) on the same batch: predict pass and one fit()
+    (epochs=1, batch 64), device times.  Reported beside the headline, not inside it: the fit
+    is a serial chain of int(N/64)-1 dependent Adam steps."""
+    import torch
+    from mjrl_b200.baselines.mlp_baseline import MLPBaseline
+    from mjrl_b200.utils import process_samples as ps
+    torch.manual_seed(7)
+    np.random.seed(7)
+    mb = MLPBaseline(spec, epochs=1)
+    if batch.returns is None:
+        ps.returns_on_device(batch, GAMMA)
+    mb.predict_batch(batch); mb.fit_batch(batch, sync=False)        # warm-up
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    ev[0].record(); mb.predict_batch(batch); ev[1].record(); mb.fit_batch(batch, sync=False); ev[2].record()
+    torch.cuda.synchronize()
+    p_ms, f_ms = ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2])
+    return {"predict_ms": p_ms, "predict_tflops_fp32": 2.0 * (15 * 128 + 128 * 128 + 128) * N / p_ms / 1e9
+            if spec.observation_dim == 11 else None,
+            "fit_ms": f_ms, "fit_steps": mb.last_fit_steps,
+            "fit_us_per_step": 1e3 * f_ms / max(mb.last_fit_steps, 1),
+            "kernel": "fit_cluster_kernel: one 8-CTA cluster, model parallel over hidden units, DSMEM exchanges"}
 
 
 def phase_breakdown(agent, batch, eng, N, n, m, hbm_peak):

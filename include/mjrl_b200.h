@@ -216,6 +216,21 @@ int mjrl_policy_act(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* pa
                     const float* obs, int64_t B, uint64_t seed, uint64_t offset, float* act_out,
                     float* mean_out, void* stream);
 
+/* ---- PPO minibatch epochs: mjrl/algos/ppo_clip.py:47-54,85-101 ------------------------- */
+/* dst[b] = src[idx[b]] for rows of `width` floats (a with-replacement minibatch, :89-92). */
+int mjrl_gather_rows_f32(mjrl_ctx* ctx, const float* src, const int32_t* idx, int32_t B, int32_t width,
+                         float* dst, void* stream);
+/* Gradient weights of PPO_surrogate (:47-54): w_t = adv_t where LR_t*adv_t <= clamp(LR_t)*adv_t,
+ * else 0, so that the gradient of mean(min(.,.)) is (1/B) sum_t w_t LR_t dLL_t, which
+ * mjrl_policy_grad computes from (w, old_ll).  surr_sum (fp64[1], may be NULL) = sum_t min(.,.). */
+int mjrl_ppo_clip_weights(mjrl_ctx* ctx, const float* ll_new, const float* ll_old, const float* adv,
+                          int32_t B, float clip_coef, float* w, double* surr_sum, void* stream);
+/* One torch.optim.Adam step (:34,96) on a flat fp32 vector from an fp64 gradient SUM:
+ * g = grad_scale*grad_sum (+ weight_decay*p); `step` counts from 1. */
+int mjrl_adam_step(mjrl_ctx* ctx, int64_t d, float* params, const double* grad_sum, double grad_scale,
+                   float* adam_m, float* adam_v, int64_t step, double lr, double beta1, double beta2,
+                   double eps, double weight_decay, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -110,8 +110,9 @@ class BatchREINFORCE:
 
     def _fit_baseline(self, batch, paths, return_errors):
         if hasattr(self.baseline, "fit_batch"):
-            ar = self._engine().dist.allreduce if self._engine().dist.world > 1 else None
-            return self.baseline.fit_batch(batch, return_errors=return_errors, allreduce=ar)
+            dist = self._engine().dist
+            return self.baseline.fit_batch(batch, return_errors=return_errors,
+                                           dist=dist if dist.world > 1 else None)
         batch.scatter("returns", batch.returns)
         return self.baseline.fit(batch.paths, return_errors=return_errors)
 

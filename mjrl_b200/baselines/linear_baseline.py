@@ -39,7 +39,7 @@ class LinearBaseline:
                        ptr(out), stream_ptr())
         return out
 
-    def fit_batch(self, batch: PathBatch, return_errors=False, sync=True, allreduce=None):
+    def fit_batch(self, batch: PathBatch, return_errors=False, sync=True, allreduce=None, dist=None):
         """Gram -> (optional all-reduce over ranks) -> Cholesky.  Returns (err_before, err_after)
         when asked.  With sync=False the coefficients stay on the device until `coeffs` is read."""
         if batch.returns is None:
@@ -48,6 +48,8 @@ class LinearBaseline:
         gram = torch.empty(F * (F + 1) + 1, dtype=torch.float64, device=batch.device)
         batch.ctx.call("mjrl_linbase_gram", ptr(batch.obs), ptr(batch.returns), ptr(batch.offsets),
                        c_int(batch.P), c_i64(batch.N), c_int(batch.n), ptr(gram), stream_ptr())
+        if allreduce is None and dist is not None and dist.world > 1:
+            allreduce = dist.allreduce
         if allreduce is not None:
             allreduce(gram)
         prev = self._coeffs_on(batch.device)

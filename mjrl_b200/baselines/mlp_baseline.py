@@ -21,6 +21,40 @@ from .._lib import c_double, c_i64, c_int, ptr, stream_ptr
 from ..batch import PathBatch, batch_for
 
 
+def _allgather_rows(dist, feat, y32):
+    """Concatenate every rank's (feat [N_r, F], y32 [N_r]) in rank order on every rank."""
+    td, dev = dist.td, feat.device
+    n_local = torch.tensor([feat.shape[0]], dtype=torch.int64, device=dev)
+    sizes = [torch.zeros_like(n_local) for _ in range(dist.world)]
+    td.all_gather(sizes, n_local, group=dist.group)
+    sizes = [int(s.item()) for s in sizes]
+    n_max, F = max(sizes), feat.shape[1]
+    packed = torch.zeros((n_max, F + 1), dtype=torch.float32, device=dev)
+    packed[:feat.shape[0], :F] = feat
+    packed[:feat.shape[0], F] = y32
+    parts = [torch.empty_like(packed) for _ in range(dist.world)]
+    td.all_gather(parts, packed, group=dist.group)
+    allrows = torch.cat([p[:k] for p, k in zip(parts, sizes)])
+    return allrows[:, :F].contiguous(), allrows[:, F].contiguous(), int(sum(sizes))
+
+
+def _broadcast_schedule(dist, base, n_rows, dev):
+    """Rank 0 draws the minibatch schedule from ITS numpy stream; everyone receives it."""
+    td = dist.td
+    per_epoch = int(n_rows / base.batch_size) - 1
+    nsteps = max(per_epoch, 0) * base.epochs
+    if nsteps == 0:
+        return np.zeros(0, dtype=np.int32), 0
+    if dist.rank == 0:
+        perm, _ = base.minibatch_schedule(n_rows)
+        d_perm = torch.from_numpy(perm).to(dev)
+    else:
+        d_perm = torch.empty(nsteps * base.batch_size, dtype=torch.int32, device=dev)
+    src = td.get_global_rank(dist.group, 0) if dist.group is not None else 0
+    td.broadcast(d_perm, src=src, group=dist.group)
+    return d_perm, nsteps
+
+
 class MLPBaseline:
     def __init__(self, env_spec, obs_dim=None, learn_rate=1e-3, reg_coef=0.0,
                  batch_size=64, epochs=1, use_gpu=False):
@@ -87,11 +121,13 @@ class MLPBaseline:
                        c_i64(batch.N), c_int(batch.n), ptr(st["params"]), ptr(out), stream_ptr())
         return out
 
-    def _rel_error(self, batch):
+    def _rel_error(self, batch, dist=None):
         pred = self.predict_batch(batch)
         sums = torch.empty(2, dtype=torch.float64, device=batch.device)
         batch.ctx.call("mjrl_mlpbase_sqerr", ptr(pred), ptr(batch.returns), c_i64(batch.N), ptr(sums),
                        stream_ptr())
+        if dist is not None and dist.world > 1:
+            dist.allreduce(sums)
         return sums
 
     def minibatch_schedule(self, num_samples):
@@ -107,7 +143,11 @@ class MLPBaseline:
             return np.zeros(0, dtype=np.int32), 0
         return np.concatenate(chunks).astype(np.int32), per_epoch * self.epochs
 
-    def fit_batch(self, batch: PathBatch, return_errors=False, perm=None, sync=True):
+    def fit_batch(self, batch: PathBatch, return_errors=False, perm=None, sync=True, dist=None):
+        """One `fit` on the flat buffer.  Multi-GPU (`dist.world > 1`): the chain of Adam steps
+        is serial and cannot be sharded, so this is REPLICAS ONLY -- every rank
+        all-gathers the (features, returns) rows of all ranks, rank 0 draws the permutation and
+        broadcasts it, and every rank runs the identical deterministic chain."""
         if batch.returns is None:
             batch.returns = batch.gather("returns")
         st = self._state(batch.device)
@@ -117,15 +157,22 @@ class MLPBaseline:
         y32 = torch.empty(batch.N, dtype=torch.float32, device=dev)
         batch.ctx.call("mjrl_mlpbase_features", ptr(batch.obs), ptr(batch.returns), ptr(batch.offsets),
                        c_int(batch.P), c_i64(batch.N), c_int(batch.n), ptr(feat), ptr(y32), stream_ptr())
-        before = self._rel_error(batch) if return_errors else None
+        multi = dist is not None and dist.world > 1
+        before = self._rel_error(batch, dist) if return_errors else None
+        n_rows = batch.N
+        if multi:
+            feat, y32, n_rows = _allgather_rows(dist, feat, y32)
         if perm is None:
-            perm, nsteps = self.minibatch_schedule(batch.N)
+            if multi:
+                perm, nsteps = _broadcast_schedule(dist, self, n_rows, dev)
+            else:
+                perm, nsteps = self.minibatch_schedule(n_rows)
         else:
             perm = np.ascontiguousarray(perm, dtype=np.int32).reshape(-1)
             nsteps = perm.size // self.batch_size
         if nsteps > 0:
-            d_perm = torch.from_numpy(perm).to(dev, non_blocking=True)
-            batch.ctx.call("mjrl_mlpbase_fit", ptr(feat), ptr(y32), c_i64(batch.N), c_int(batch.n),
+            d_perm = perm if torch.is_tensor(perm) else torch.from_numpy(perm).to(dev, non_blocking=True)
+            batch.ctx.call("mjrl_mlpbase_fit", ptr(feat), ptr(y32), c_i64(n_rows), c_int(batch.n),
                            ptr(st["params"]), ptr(st["m"]), ptr(st["v"]), c_i64(self.adam_step),
                            ptr(d_perm), c_i64(nsteps), c_int(self.batch_size),
                            c_double(self.learn_rate), c_double(self.adam_betas[0]),
@@ -135,7 +182,7 @@ class MLPBaseline:
         self.last_fit_steps = nsteps
         errs = None
         if return_errors:
-            after = self._rel_error(batch)
+            after = self._rel_error(batch, dist)
             b, a = before.cpu().numpy(), after.cpu().numpy()
             errs = (float(b[0] / (b[1] + 1e-8)), float(a[0] / (a[1] + 1e-8)))
         if sync:

@@ -66,6 +66,7 @@ class _GaussianPolicyBase:
         self.d = np.sum(self.param_sizes)
         self.obs_var = torch.randn(self.n)                  # RNG draw kept for seed parity, :57
         self._dev = None
+        self._old_aliases_new = False
 
     # ---- flat parameters --------------------------------------------------------------
     def get_param_values(self):
@@ -86,6 +87,15 @@ class _GaussianPolicyBase:
         params[-1].data = torch.clamp(params[-1].data, self.min_log_std)
 
     def set_param_values(self, new_params, set_new=True, set_old=True):
+        # Reference quirk kept as STATE, not as shared memory: gaussian_mlp.py:66-88 assigns
+        # `param.data = torch.from_numpy(vals).float()`, which does not copy a float32 array, so
+        # after set_new=set_old=True on float32 input the new and old NETWORK tensors share one
+        # buffer (log_std does not: the clamp re-creates it on both sides).  Only in-place
+        # optimisers see it (PPO, ppo_clip.py:96); algos/ppo_clip.py reads this flag.
+        if set_new and set_old:
+            self._old_aliases_new = np.asarray(new_params).dtype == np.float32
+        elif set_new or set_old:
+            self._old_aliases_new = False
         if set_new:
             self._assign(self.trainable_params, new_params)
             self.log_std_val = np.float64(self.log_std.data.numpy().ravel())

@@ -256,6 +256,7 @@ class GaussianPolicy:
         self.new = None
         self.old = None
         self.set_param_values(np.asarray(flat_params, dtype=np.float32))
+        self.aliased = False   # a freshly constructed reference policy clones old from new (:42-46)
 
     # gaussian_mlp.py:61-64
     def get_param_values(self):
@@ -263,6 +264,14 @@ class GaussianPolicy:
 
     # gaussian_mlp.py:66-88 -- fp32 cast, then clamp log_std at min_log_std
     def set_param_values(self, flat, set_new=True, set_old=True):
+        # Reference quirk (gaussian_mlp.py:66-88): `param.data = torch.from_numpy(vals).float()` does
+        # NOT copy when `new_params` is already float32, so after a call with set_new=set_old=True on
+        # a float32 array the new and old tensors share ONE buffer.  It only matters to optimisers
+        # that update the new parameters in place (PPO, ppo_clip.py:96): from then on old == new.
+        if set_new and set_old:
+            self.aliased = np.asarray(flat).dtype == np.float32
+        elif set_new or set_old:
+            self.aliased = False
         if set_new:
             self.new = unflatten(flat, self.shapes, requires_grad=True)
             self.new[-1] = torch.clamp(self.new[-1].detach(), self.min_log_std).requires_grad_(True)
@@ -270,6 +279,12 @@ class GaussianPolicy:
         if set_old:
             self.old = unflatten(flat, self.shapes)
             self.old[-1] = torch.clamp(self.old[-1], self.min_log_std)
+
+    def sync_aliased_old(self):
+        """What the shared buffer does in the reference once `aliased`: the old NETWORK tensors equal
+        the new ones.  log_std is excluded: the clamp at :75-76 / :87-88 re-assigns `.data` to a fresh
+        tensor on both sides, so old_log_std keeps the value it had when it was set."""
+        self.old = [t.detach().clone() for t in self.new[:-1]] + [self.old[-1]]
 
     def mean(self, obs, params):
         """MuNet.forward gaussian_mlp.py:176-182 / LinearModel.forward gaussian_linear.py:171-175."""
@@ -549,6 +564,64 @@ def dapg_update(pol, paths, demo_paths, kl_dist, lam_0=1.0, lam_1=0.95, iter_cou
     out["kl_dist"] = _scalar(kl_old_new(pol, obs, act))
     pol.set_param_values(new, set_new=True, set_old=True)
     out.update(alpha=alpha, delta=delta, new_params=new)
+    return out
+
+
+def ppo_surrogate(pol, obs, act, adv, clip_coef):
+    """mjrl/algos/ppo_clip.py:47-54."""
+    adv_var = torch.from_numpy(np.asarray(adv)).float()
+    old = pol.dist_info(obs, act, "old")
+    new = pol.dist_info(obs, act, "new")
+    LR = torch.exp(new[0] - old[0])
+    LR_clip = torch.clamp(LR, min=1 - clip_coef, max=1 + clip_coef)
+    return torch.mean(torch.min(LR * adv_var, LR_clip * adv_var))
+
+
+class PPOState:
+    """The optimizer the reference builds once in PPO.__init__ (ppo_clip.py:45): Adam over the
+    policy's trainable tensors, state kept across iterations."""
+
+    def __init__(self, pol, learn_rate=3e-4):
+        self.pol = pol
+        self.optimizer = torch.optim.Adam(pol.new, lr=learn_rate)
+
+
+def ppo_update(pol, paths, state=None, clip_coef=0.2, epochs=10, mb_size=64, learn_rate=3e-4,
+               choice_source=None):
+    """mjrl/algos/ppo_clip.py:57-120.  `choice_source(num_samples, mb_size)` lets a test inject the
+    minibatch indices; default np.random.choice on the global stream like :89."""
+    obs, act, adv = concat_paths(paths)
+    out = {"stats": path_return_stats(paths)}
+    out["surr_before"] = _scalar(cpi_surrogate(pol, obs, act, adv))
+    state = state or PPOState(pol, learn_rate)
+    # the optimizer must hold the CURRENT trainable tensors (set_param_values re-creates them here,
+    # the reference mutates .data in place); moments are carried over by position
+    if any(a is not b for a, b in zip(state.optimizer.param_groups[0]["params"], pol.new)):
+        old_params = state.optimizer.param_groups[0]["params"]
+        st = [state.optimizer.state.get(p, None) for p in old_params]
+        state.optimizer = torch.optim.Adam(pol.new, lr=state.optimizer.param_groups[0]["lr"])
+        for p, s_ in zip(pol.new, st):
+            if s_ is not None:
+                state.optimizer.state[p] = s_
+    choice = choice_source or (lambda n, k: np.random.choice(n, size=k))
+    num_samples = obs.shape[0]
+    for _ in range(epochs):
+        for _mb in range(int(num_samples / mb_size)):
+            idx = choice(num_samples, mb_size)
+            state.optimizer.zero_grad()
+            if pol.aliased:   # old network tensors share new's storage: they track every Adam step
+                pol.sync_aliased_old()
+            loss = -ppo_surrogate(pol, obs[idx], act[idx], adv[idx], clip_coef)
+            loss.backward()
+            state.optimizer.step()
+    params_after_opt = pol.get_param_values()
+    if pol.aliased:
+        pol.sync_aliased_old()
+    out["surr_after"] = _scalar(cpi_surrogate(pol, obs, act, adv))
+    out["kl_dist"] = _scalar(kl_old_new(pol, obs, act))
+    pol.set_param_values(params_after_opt, set_new=True, set_old=True)
+    out["new_params"] = pol.get_param_values()
+    out["state"] = state
     return out
 
 

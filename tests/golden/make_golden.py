@@ -210,8 +210,52 @@ def run_mlpbase_case(R, name, n, horizon, N, seed, epochs, reg_coef):
     print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
 
 
+def run_ppo_case(R, name, n, m, hidden, horizon, N, seed, mid, epochs):
+    """PPO (ppo_clip.py): full train_from_paths of the live reference, with the minibatch rows it
+    drew from numpy's global stream (np.random.choice, :89) recorded."""
+    import torch
+    from mjrl_b200.utils import synthetic as syn
+    import mjrl.algos.ppo_clip as ppo
+    spec = R.EnvSpec(n, m, horizon, 1)
+    pol, init = build_ref_policy(R, n, m, hidden, seed=123)
+    flat, tr = init, None
+    if mid:
+        flat, tr = syn.mid_training_variant(init, n, m, seed)
+        pol, _ = build_ref_policy(R, n, m, hidden, seed=123, flat=flat, transforms=tr)
+    b = syn.make_flat_batch(N, n, m, horizon, seed, flat, hidden, tr)
+    paths = syn.flat_to_paths(b)
+    rng = np.random.default_rng(seed + 5)
+    for p in paths:   # synthetic advantages: PPO only reads paths[...]["advantages"]
+        p["advantages"] = rng.standard_normal(len(p["rewards"]))
+    out = dict(n=n, m=m, hidden=np.asarray(hidden, dtype=np.int64), horizon=horizon, N=N, seed=seed,
+               epochs=epochs, params=flat, init_params=init, numpy_version=np.__version__,
+               torch_version=torch.__version__, advantages=np.concatenate([p["advantages"] for p in paths]))
+    out.update(b)
+    if tr is not None:
+        out.update({"tr_" + k: v for k, v in tr.items()})
+    agent = ppo.PPO(None, pol, R.lb.LinearBaseline(spec), clip_coef=0.2, epochs=epochs, mb_size=64,
+                    learn_rate=3e-4)
+    steps = epochs * int(N / 64)
+    np.random.seed(seed + 9)
+    out["minibatches"] = np.stack([np.random.choice(N, size=64) for _ in range(steps)])
+    np.random.seed(seed + 9)
+    stats = agent.train_from_paths(paths)
+    out["stats"] = np.asarray(stats)
+    out["ppo_new_params"] = pol.get_param_values()
+    # second iteration on the same paths: Adam state persists in agent.optimizer
+    agent.train_from_paths(paths)
+    out["ppo_new_params_2"] = pol.get_param_values()
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
+
+
 if __name__ == "__main__":
     R = import_reference()
+    if "--ppo-only" in sys.argv:
+        run_ppo_case(R, "ppo_hopper_mid", 11, 3, (64, 64), 100, 640, 8000, True, 2)
+        run_ppo_case(R, "ppo_linear", 6, 2, (), 25, 320, 8001, False, 3)
+        sys.exit(0)
     if "--mlpbase-only" in sys.argv:
         run_mlpbase_case(R, "mlpbase_1step", 11, 60, 150, 7000, 1, 0.0)
         run_mlpbase_case(R, "mlpbase_hopper", 11, 200, 1500, 7001, 2, 1e-3)
@@ -225,3 +269,5 @@ if __name__ == "__main__":
     run_case(R, "c1_linear_mid", 6,  2, (),        25, 1000, 1001, True)
     run_mlpbase_case(R, "mlpbase_1step", 11, 60, 150, 7000, 1, 0.0)
     run_mlpbase_case(R, "mlpbase_hopper", 11, 200, 1500, 7001, 2, 1e-3)
+    run_ppo_case(R, "ppo_hopper_mid", 11, 3, (64, 64), 100, 640, 8000, True, 2)
+    run_ppo_case(R, "ppo_linear", 6, 2, (), 25, 320, 8001, False, 3)
