@@ -74,7 +74,7 @@ class BatchREINFORCE:
             old_ll, _ = eng.old_cache(p_old, obs, act)
         g = eng.gradient(p_new, obs, act, w, old_ll)
         eng.dist.allreduce(g)
-        return (g[:eng.dv.d] / float(obs.shape[0] * eng.dist.world)).float().cpu().numpy()
+        return (g[:eng.dv.d] / eng.dist.global_count(obs.shape[0], eng.device)).float().cpu().numpy()
 
     # ---- one iteration -------------------------------------------------------------------
     def train_step(self, N, sample_mode='trajectories', env_name=None, T=1e6, gamma=0.995,
@@ -131,6 +131,14 @@ class BatchREINFORCE:
         eng.launches += 2
         return eng, batch, w, stats
 
+    @staticmethod
+    def _global_n(eng, batch):
+        """Global timestep count of a sharded batch (cached on the batch object)."""
+        n = getattr(batch, "_n_global", None)
+        if n is None:
+            n = batch._n_global = eng.dist.global_count(batch.N, eng.device)
+        return n
+
     def _finish_stats(self, stats, paths):
         base_stats = [float(v) for v in stats.cpu().numpy()]
         mean_return = base_stats[0]
@@ -142,7 +150,7 @@ class BatchREINFORCE:
     def train_from_paths(self, paths):
         """batch_reinforce.py:106-164: new = curr + learn_rate * vpg_grad."""
         eng, batch, w, stats = self._prepare(paths)
-        N_glob = float(batch.N * eng.dist.world)
+        N_glob = self._global_n(eng, batch)
         d, m = eng.dv.d, eng.dv.m
         ts = timer.time()
         p_old, curr = eng.dv.params("old"), eng.dv.params("new")

@@ -36,6 +36,16 @@ class Dist:
             self.calls += 1
         return t
 
+    def global_count(self, n_local, device=None):
+        """Sum of per-rank sample counts as a host float.  Shards are whole paths, so ranks
+        generally own DIFFERENT numbers of timesteps: every mean over the batch divides by this,
+        never by n_local * world.  One tiny all-reduce + host read; callers cache it per batch."""
+        if self.td is None or self.world == 1:
+            return float(n_local)
+        t = torch.tensor([float(n_local)], dtype=torch.float64, device=device)
+        self.allreduce(t)
+        return float(t.item())
+
 
 class UpdateEngine:
     def __init__(self, policy, dist=None):
@@ -118,7 +128,7 @@ class UpdateEngine:
         self.launches += 1
         for _ in range(iters):
             o = obs if subsample is None else subsample()
-            cnt = N_global if subsample is None else float(o.shape[0]) * self.dist.world
+            cnt = N_global if subsample is None else self.dist.global_count(o.shape[0], self.device)
             self.fvp(params, o, self.cg_p32, self.cg_z)
             self.dist.allreduce(self.cg_z)
             self.ctx.call("mjrl_cg_update", ctypes.byref(self.cg), c_i64(d), c_double(1.0 / cnt),

@@ -39,7 +39,7 @@ class NPG(BatchREINFORCE):
         out = torch.empty(eng.dv.d, dtype=torch.float64, device=eng.device)
         eng.fvp(params, obs, _dev32(vector, eng.device), out)
         eng.dist.allreduce(out)
-        hv = (out / float(obs.shape[0] * eng.dist.world)).float().cpu().numpy()
+        hv = (out / eng.dist.global_count(obs.shape[0], eng.device)).float().cpu().numpy()
         return hv + regu_coef * vector
 
     def build_Hvp_eval(self, inputs, regu_coef=None):
@@ -50,7 +50,7 @@ class NPG(BatchREINFORCE):
     # ---- shared body: gradient -> CG -> step size; returns everything still on device ----------
     def _npg_direction(self, eng, batch, w, g_scale_extra=1.0, demo=None, trace=None):
         d, m = eng.dv.d, eng.dv.m
-        N_glob = float(batch.N * eng.dist.world)
+        N_glob = self._global_n(eng, batch)
         p_old, curr = eng.dv.params("old"), eng.dv.params("new")
         old_ll = torch.empty(batch.N, dtype=torch.float32, device=eng.device)
         old_mean = torch.empty((batch.N, m), dtype=torch.float32, device=eng.device)

@@ -29,9 +29,9 @@ def run(world_mode):
     base = LinearBaseline(spec)
     base._coeffs = g["fit0_coeffs"].copy()
     paths = syn.flat_to_paths(batch_of(g, "b1_"))
-    # 3 CG iterations: beyond ~5 the direction is chaotic under ANY re-ordering of the fp32 sums,
-    # the reference's own included, so rank-count invariance is gated before that
-    ag = NPG(None, pol, base, normalized_step_size=0.01, FIM_invert_args={"iters": 3, "damping": 1e-4})
+    # the full 10 CG iterations: shards own whole paths and DIFFERENT timestep counts, every mean
+    # divides by the all-reduced global count, and only the fp32 summation order differs
+    ag = NPG(None, pol, base, normalized_step_size=0.01, FIM_invert_args={"iters": 10, "damping": 1e-4})
     if world_mode:
         ag.dist = Dist()
         paths = shard_paths(paths, ag.dist.rank, ag.dist.world)
@@ -43,15 +43,44 @@ def run(world_mode):
     return pol.get_param_values().astype(np.float64) - g["params"], np.asarray(base._coeffs), g
 
 
+def run_mlpbase(world_mode, rank, world):
+    """MLPBaseline.fit is replicas-only: every rank gathers all rows and runs the same chain, so the
+    result must equal (bit for bit) a single-GPU fit on the shards concatenated in rank order."""
+    from mjrl_b200.baselines.mlp_baseline import MLPBaseline
+    from mjrl_b200.utils import process_samples as ps
+    from mjrl_b200.batch import batch_for
+    g = load_golden("c3_hopper_mid")
+    spec = EnvSpec(g["n"], g["m"], g["horizon"], 1)
+    paths = syn.flat_to_paths(batch_of(g, "b1_"))
+    shards = [shard_paths(paths, r, world) for r in range(world)]
+    torch.manual_seed(5); np.random.seed(11)
+    mb = MLPBaseline(spec, epochs=1)
+    drop_cache()
+    if world_mode:
+        b = batch_for(shards[rank])
+        ps.returns_on_device(b, g["gamma"])
+        errs = mb.fit_batch(b, return_errors=True, dist=Dist())
+    else:
+        b = batch_for([p for sh in shards for p in sh])
+        ps.returns_on_device(b, g["gamma"])
+        errs = mb.fit_batch(b, return_errors=True)
+    return mb.get_param_values(), errs, mb.last_fit_steps
+
+
 if __name__ == "__main__":
     rank, world, local = init_distributed("nccl")
     torch.cuda.set_device(local)
     step_multi, coef_multi, g = run(True)
+    mlp_multi, errs_multi, steps_multi = run_mlpbase(True, rank, world)
     if rank == 0:
         step_one, coef_one, _ = run(False)
+        mlp_one, errs_one, steps_one = run_mlpbase(False, rank, world)
         r_step, r_coef = rel_l2(step_multi, step_one), rel_l2(coef_multi, coef_one)
-        ok = r_step < 1e-4 and r_coef < 1e-6
-        print("MULTI_%s world=%d step_rel=%.3e coef_rel=%.3e" % ("OK" if ok else "FAIL", world, r_step, r_coef))
+        mlp_same = steps_multi == steps_one and np.array_equal(mlp_multi, mlp_one)
+        errs_ok = all(abs(a - b) < 1e-9 * max(1.0, abs(b)) for a, b in zip(errs_multi, errs_one))
+        ok = r_step < 1e-4 and r_coef < 1e-6 and mlp_same and errs_ok
+        print("MULTI_%s world=%d step_rel=%.3e coef_rel=%.3e mlpbase_bitexact=%s (%d steps) errs_ok=%s"
+              % ("OK" if ok else "FAIL", world, r_step, r_coef, mlp_same, steps_multi, errs_ok))
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
