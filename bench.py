@@ -142,7 +142,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20",
                  "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -365,7 +365,10 @@ def run_b200(args):
 
     mlp_extra = None
     if rank == 0 and world == 1 and not use_mlp:
-        mlp_extra = mlpbase_timing(spec, resident, N)
+        try:
+            mlp_extra = mlpbase_timing(spec, resident, N)
+        except Exception as e:   # e.g. obs_dim too wide for the fit kernels' shared-memory plan
+            mlp_extra = {"unavailable": str(e)[:200]}
     cb = None
     if rank == 0 and not args.no_cpu_baseline:
         cb = cpu_baseline(args.workload)
