@@ -12,41 +12,108 @@
 namespace {
 
 // ------------------------------------------------------------------ predict
+// One thread per timestep, 256 timesteps per tile.  The obs slab of a tile is contiguous in HBM
+// (256*n floats): one thread issues a single bulk copy (TMA) into shared memory, double-buffered,
+// so the next tile streams in while this one is reduced and no thread spends instructions on
+// staging.  The path of the tile's first timestep is found once per warp (32-ary search).
 constexpr int PRED_TS = 256;  // timesteps per tile == threads per CTA
+
+// sum_k clip(row[k]) * sc[k] in ascending k for every vector width (identical rounding)
+__device__ __forceinline__ double clipd(float x) { return (double)fminf(fmaxf(x, -10.f), 10.f); }
+template <int VEC>
+__device__ __forceinline__ double pred_dot(const float* __restrict__ row, const double* __restrict__ sc,
+                                           int n) {
+  double acc = 0.0;
+  int k = 0;
+  for (; k + 4 <= n; k += 4) {
+    float x0, x1, x2, x3;
+    if (VEC == 4) {
+      const float4 v = *reinterpret_cast<const float4*>(row + k);
+      x0 = v.x; x1 = v.y; x2 = v.z; x3 = v.w;
+    } else if (VEC == 2) {
+      const float2 u = *reinterpret_cast<const float2*>(row + k);
+      const float2 v = *reinterpret_cast<const float2*>(row + k + 2);
+      x0 = u.x; x1 = u.y; x2 = v.x; x3 = v.y;
+    } else {
+      x0 = row[k]; x1 = row[k + 1]; x2 = row[k + 2]; x3 = row[k + 3];
+    }
+    const double2 c01 = *reinterpret_cast<const double2*>(sc + k);
+    const double2 c23 = *reinterpret_cast<const double2*>(sc + k + 2);
+    acc = fma(clipd(x0), c01.x, acc);
+    acc = fma(clipd(x1), c01.y, acc);
+    acc = fma(clipd(x2), c23.x, acc);
+    acc = fma(clipd(x3), c23.y, acc);
+  }
+  for (; k < n; ++k) acc = fma(clipd(row[k]), sc[k], acc);
+  return acc;
+}
 
 __global__ void __launch_bounds__(PRED_TS)
 linbase_predict_kernel(const float* __restrict__ obs, const int32_t* __restrict__ off, int P,
-                       int64_t N, int n, const double* __restrict__ coeffs,
+                       int64_t N, int n, int nbuf, const double* __restrict__ coeffs,
                        double* __restrict__ pred) {
-  extern __shared__ unsigned char smem_raw[];
-  const int ns = n | 1;  // odd row stride: thread-per-row reads are bank-conflict free
-  double* sc = reinterpret_cast<double*>(smem_raw);           // [n+4]
-  float* so = reinterpret_cast<float*>(sc + ((n + 4 + 1) & ~1));  // [PRED_TS][ns]
-  for (int k = threadIdx.x; k < n + 4; k += blockDim.x) sc[k] = coeffs[k];
-  const int64_t ntiles = (N + PRED_TS - 1) / PRED_TS;
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int64_t t0 = tile * PRED_TS;
-    const int rows = (int)min((int64_t)PRED_TS, N - t0);
-    __syncthreads();
-    // contiguous, coalesced copy of rows*n floats
-    const float* src = obs + t0 * n;
-    const int cnt = rows * n;
-    for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
-      int r = i / n, c = i - r * n;
-      so[r * ns + c] = ld_stream(src + i);
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint64_t bar[2];
+  __shared__ int sTP[2][4];
+  double* sc = reinterpret_cast<double*>(smem_raw);                  // [n+4]
+  float* tiles = reinterpret_cast<float*>(sc + ((n + 4 + 1) & ~1));  // [nbuf][PRED_TS*n], dense rows
+  const int tid = threadIdx.x;
+  const int ntiles = (int)((N + PRED_TS - 1) / PRED_TS);
+  const int tile_elems = PRED_TS * n;
+  const bool base_ok = (reinterpret_cast<uintptr_t>(obs) & 15) == 0;
+  // a tile goes through the bulk path iff its byte count is a multiple of 16 (all but maybe the last)
+  auto tile_rows = [&](int tile) { return tile + 1 < ntiles ? PRED_TS : (int)(N - (int64_t)tile * PRED_TS); };
+  auto bulk_ok = [&](int tile) { return base_ok && ((tile_rows(tile) * n) & 3) == 0; };
+  const double inv = (double)P / (double)N;
+  auto start_copy = [&](int tile, int buf) {  // one thread
+    if (bulk_ok(tile)) {
+      const uint32_t bytes = (uint32_t)(tile_rows(tile) * n) * 4u;
+      tma::mbar_expect(&bar[buf], bytes);
+      tma::bulk_g2s(tiles + (size_t)buf * tile_elems, obs + (int64_t)tile * tile_elems, bytes, &bar[buf]);
     }
-    __syncthreads();
-    const int r = threadIdx.x;
-    if (r < rows) {
-      const int64_t t = t0 + r;
-      const int p = find_path(off, P, t);
-      const double al = (double)(t - off[p]) / 1000.0;
-      double acc = 0.0;
-      const float* row = so + r * ns;
-      for (int k = 0; k < n; ++k) {
-        double o = (double)fminf(fmaxf(row[k], -10.f), 10.f);
-        acc = fma(o, sc[k], acc);
-      }
+  };
+  auto publish = [&](int slot, const TilePath& tp) {
+    sTP[slot][0] = tp.p0; sTP[slot][1] = tp.s0; sTP[slot][2] = tp.s1;
+  };
+  for (int k = tid; k < n + 4; k += PRED_TS) sc[k] = coeffs[k];
+  if (tid == 0) { tma::mbar_init(&bar[0], 1); tma::mbar_init(&bar[1], 1); tma::mbar_init_fence(); }
+  __syncthreads();
+  int tile = blockIdx.x;
+  if (tid < 32 && tile < ntiles) {
+    if (tid == 0 && nbuf == 2) start_copy(tile, 0);
+    const TilePath tp = tile_path(off, P, (int64_t)tile * PRED_TS, inv);
+    if (tid == 0) publish(0, tp);
+  }
+  __syncthreads();
+  for (int it = 0; tile < ntiles; tile += gridDim.x, ++it) {
+    const int slot = it & 1, buf = nbuf == 2 ? slot : 0;
+    // warp 0 looks one tile ahead: the copy starts now, the path lookup's loads are in flight while
+    // the warp reduces its own rows and are consumed just before the closing barrier
+    const int next = tile + gridDim.x;
+    const bool ahead = tid < 32 && next < ntiles;
+    TilePath tpn;
+    if (tid == 0) {
+      if (nbuf == 2) { if (next < ntiles) start_copy(next, buf ^ 1); }
+      else start_copy(tile, 0);
+    }
+    if (ahead) tpn = tile_path(off, P, (int64_t)next * PRED_TS, inv);
+    const int64_t t0 = (int64_t)tile * PRED_TS;
+    const int rows = tile_rows(tile);
+    TilePath tp;
+    tp.p0 = sTP[slot][0]; tp.s0 = sTP[slot][1]; tp.s1 = sTP[slot][2];
+    float* so = tiles + (size_t)buf * tile_elems;
+    if (bulk_ok(tile)) {
+      tma::mbar_wait(&bar[buf], nbuf == 2 ? ((it >> 1) & 1) : (it & 1));
+    } else {
+      stream_rows<PRED_TS>(obs + t0 * n, rows * n, n, tid, [&](int r, int c, float v) { so[r * n + c] = v; });
+      __syncthreads();
+    }
+    if (tid < rows) {
+      const int64_t t = t0 + tid;
+      const double al = (double)t_in_path(off, P, tp, t) / 1000.0;
+      const float* row = so + tid * n;
+      double acc = (n & 3) == 0 ? pred_dot<4>(row, sc, n)
+                 : (n & 1) == 0 ? pred_dot<2>(row, sc, n) : pred_dot<1>(row, sc, n);
       const double al2 = al * al;
       acc = fma(al, sc[n], acc);
       acc = fma(al2, sc[n + 1], acc);
@@ -54,6 +121,8 @@ linbase_predict_kernel(const float* __restrict__ obs, const int32_t* __restrict_
       acc += sc[n + 3];
       pred[t] = acc;
     }
+    if (ahead && tid == 0) publish(slot ^ 1, tpn);
+    __syncthreads();  // every thread is done with `so` and sTP[slot] before they are refilled
   }
 }
 
@@ -64,117 +133,241 @@ __global__ void fill_zero_kernel(double* __restrict__ x, int64_t N) {
 }
 
 // --------------------------------------------------------------------- Gram
-// Symmetric (F+1)x(F+1) matrix S = Z^T Z with Z = [X | y]; only 4x4 tiles with tj >= ti are
-// computed.  Each thread owns up to MAXT tiles (16 fp64 accumulators each) for the whole
-// persistent loop; when there are fewer tiles than threads the timesteps of a smem tile are
-// split over G thread groups.  Per-CTA partials go to scratch, a second kernel sums them in a
-// fixed order and mirrors the triangle.
+// Symmetric (F+1)x(F+1) matrix S = Z^T Z with Z = [X | y], on the fp64 tensor-core path
+// (mma.sync m8n8k4 f64: the only fp64 MMA sm_100a has; tcgen05 has no fp64 kind).  The matrix is
+// cut into 8x8 tiles, only tiles with tj >= ti are computed.  One MMA contracts 4 timesteps:
+//   A fragment (8 features x 4 timesteps, row-major):  lane holds Z[t0 + lane%4][8*ti + lane/4]
+//   B fragment (4 timesteps x 8 features, col-major):  lane holds Z[t0 + lane%4][8*tj + lane/4]
+// i.e. both come from the SAME shared-memory feature tile with the same index map, one 8-byte load
+// each.  Row stride FS = 4 mod 16 doubles makes those loads bank-conflict free.
+//   SPLIT (few tiles, small n): every warp owns all NS*(NS+1)/2 tiles and takes every 8th group
+//     of 4 timesteps; the 8 warp partials are summed in a fixed order at the end.
+//   otherwise: warp w owns a contiguous run of <= MAXT tiles and walks all timesteps.
+// Per-CTA partials go to scratch, a second kernel sums them in a fixed order and mirrors.
 constexpr int GRAM_THREADS = 256;
+constexpr int GRAM_WARPS = GRAM_THREADS / 32;
+
+__device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+      : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// fills feat[TS][FS] for the tile starting at timestep t0 (rows valid, the rest zero)
+__device__ __forceinline__ void gram_stage_tile(const float* __restrict__ obs,
+                                                const double* __restrict__ ret,
+                                                const int32_t* __restrict__ off, int P, double inv,
+                                                int64_t t0, int rows, int n, int TS, int FP8, int FS,
+                                                double* __restrict__ feat, int tid) {
+  const int F1 = n + 5;
+  const TilePath tp = tile_path(off, P, t0, inv);
+  // time features / target / padding first: the lookup latency overlaps the obs copy below
+  for (int r = tid; r < TS; r += GRAM_THREADS) {
+    double* row = feat + r * FS;
+    if (r < rows) {
+      const int64_t t = t0 + r;
+      const double y = ldg_stream(ret + t);
+      const double al = (double)t_in_path(off, P, tp, t) / 1000.0;
+      row[n] = al; row[n + 1] = al * al; row[n + 2] = al * al * al; row[n + 3] = 1.0;
+      row[n + 4] = y;
+      for (int c = F1; c < FP8; ++c) row[c] = 0.0;
+    } else {
+      for (int c = 0; c < FP8; ++c) row[c] = 0.0;  // zero rows contribute nothing
+    }
+  }
+  stream_rows<GRAM_THREADS>(obs + t0 * n, rows * n, n, tid, [&](int r, int c, float v) {
+    feat[r * FS + c] = (double)fminf(fmaxf(v, -10.f), 10.f);
+  });
+}
+
+// SPLIT variant (n <= 19).  The obs slab of a tile arrives by one bulk copy (TMA), double-buffered,
+// and stays fp32 in shared memory.  Columns are cut into 8-wide blocks: the first n/8 blocks are
+// pure obs columns (clipped + widened when a fragment is loaded); everything after them -- the
+// last n%8 obs columns, [al, al^2, al^3, 1, y] and the zero padding -- is written once per timestep
+// as fp64 into `ex` by one thread per timestep, so those fragments are a single 8-byte load.
+// Warp 0 looks one tile ahead (path lookup + bulk copy) while the others compute.
+template <int NS>
+__global__ void __launch_bounds__(GRAM_THREADS)
+linbase_gram_split_kernel(const float* __restrict__ obs, const double* __restrict__ ret,
+                          const int32_t* __restrict__ off, int P, int64_t N, int n, int TS, int EXS,
+                          double* __restrict__ partial) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint64_t bar[2];
+  __shared__ int sTP[2][4];
+  constexpr int FP8 = 8 * NS, NTRI = NS * (NS + 1) / 2;
+  const int tile_elems = TS * n;
+  float* tiles = reinterpret_cast<float*>(smem_raw);                               // [2][TS*n]
+  double* ex = reinterpret_cast<double*>(smem_raw + (size_t)2 * tile_elems * 4);   // [TS][EXS]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, q = lane & 3;
+  const int nb_obs = n >> 3, tail = n & 7;   // pure-obs blocks; obs columns that live in `ex`
+  const int exw = 8 * (NS - nb_obs);         // fp64 columns per timestep (8 or 16)
+  double acc[NTRI][2];
+#pragma unroll
+  for (int k = 0; k < NTRI; ++k) acc[k][0] = acc[k][1] = 0.0;
+
+  const int ntiles = (int)((N + TS - 1) / TS);
+  const int nq = TS >> 2;
+  const bool base_ok = (reinterpret_cast<uintptr_t>(obs) & 15) == 0;
+  auto tile_rows = [&](int tile) { return tile + 1 < ntiles ? TS : (int)(N - (int64_t)tile * TS); };
+  auto bulk_ok = [&](int tile) { return base_ok && ((tile_rows(tile) * n) & 3) == 0; };
+  const double inv = (double)P / (double)N;
+  auto start_copy = [&](int tile, int buf) {  // one thread
+    if (bulk_ok(tile)) {
+      const uint32_t bytes = (uint32_t)(tile_rows(tile) * n) * 4u;
+      tma::mbar_expect(&bar[buf], bytes);
+      tma::bulk_g2s(tiles + (size_t)buf * tile_elems, obs + (int64_t)tile * tile_elems, bytes, &bar[buf]);
+    }
+  };
+  auto publish = [&](int slot, const TilePath& tp) {
+    sTP[slot][0] = tp.p0; sTP[slot][1] = tp.s0; sTP[slot][2] = tp.s1;
+  };
+  if (tid == 0) { tma::mbar_init(&bar[0], 1); tma::mbar_init(&bar[1], 1); tma::mbar_init_fence(); }
+  __syncthreads();
+  int tile = blockIdx.x;
+  if (tid < 32 && tile < ntiles) {
+    if (tid == 0) start_copy(tile, 0);
+    const TilePath tp0 = tile_path(off, P, (int64_t)tile * TS, inv);
+    if (tid == 0) publish(0, tp0);
+  }
+  __syncthreads();
+  for (int it = 0; tile < ntiles; tile += gridDim.x, ++it) {
+    const int buf = it & 1;
+    // warp 0 looks one tile ahead: copy now, path lookup consumed just before the closing barrier
+    const int next = tile + gridDim.x;
+    const bool ahead = tid < 32 && next < ntiles;
+    TilePath tpn;
+    if (tid == 0 && next < ntiles) start_copy(next, buf ^ 1);
+    if (ahead) tpn = tile_path(off, P, (int64_t)next * TS, inv);
+    const int64_t t0 = (int64_t)tile * TS;
+    const int rows = tile_rows(tile);
+    TilePath tp;
+    tp.p0 = sTP[buf][0]; tp.s0 = sTP[buf][1]; tp.s1 = sTP[buf][2];
+    // per-timestep scalars first: their global loads overlap the wait for the tile
+    double y = 0.0, al = 0.0;
+    if (tid < rows) {  // TS <= GRAM_THREADS
+      y = ldg_stream(ret + t0 + tid);
+      al = (double)t_in_path(off, P, tp, t0 + tid) / 1000.0;
+    }
+    float* of = tiles + (size_t)buf * tile_elems;
+    if (bulk_ok(tile)) {
+      tma::mbar_wait(&bar[buf], (it >> 1) & 1);
+    } else {
+      stream_rows<GRAM_THREADS>(obs + t0 * n, rows * n, n, tid, [&](int r, int c, float v) { of[r * n + c] = v; });
+      __syncthreads();
+    }
+    if (rows < TS)  // last tile: rows past the end must read as zero
+      for (int i = rows * n + tid; i < tile_elems; i += GRAM_THREADS) of[i] = 0.f;
+    if (tid < TS) {
+      double* e = ex + tid * EXS;
+      if (tid < rows) {
+        const float* orow = of + tid * n + 8 * nb_obs;
+        for (int c = 0; c < tail; ++c) e[c] = (double)fminf(fmaxf(orow[c], -10.f), 10.f);
+        e[tail] = al; e[tail + 1] = al * al; e[tail + 2] = al * al * al; e[tail + 3] = 1.0; e[tail + 4] = y;
+        for (int c = tail + 5; c < exw; ++c) e[c] = 0.0;
+      } else {
+        for (int c = 0; c < exw; ++c) e[c] = 0.0;  // zero rows contribute nothing
+      }
+    }
+    __syncthreads();
+    const float* orow = of + (4 * warp + q) * n + g;
+    const double* erow = ex + (4 * warp + q) * EXS + g;
+#pragma unroll 2
+    for (int qd = warp; qd < nq; qd += GRAM_WARPS) {
+      double f[NS];
+#pragma unroll
+      for (int a = 0; a < NS; ++a) {
+        if (a < nb_obs) f[a] = (double)fminf(fmaxf(orow[8 * a], -10.f), 10.f);  // warp-uniform branch
+        else f[a] = erow[8 * (a - nb_obs)];
+      }
+      orow += 4 * GRAM_WARPS * n;
+      erow += 4 * GRAM_WARPS * EXS;
+      int k = 0;
+#pragma unroll
+      for (int a = 0; a < NS; ++a)
+#pragma unroll
+        for (int b = a; b < NS; ++b, ++k) dmma_m8n8k4(acc[k][0], acc[k][1], f[a], f[b]);
+    }
+    if (ahead && tid == 0) publish(buf ^ 1, tpn);
+    __syncthreads();  // tile, ex and sTP[buf] are free again
+  }
+  // ---- sum the 8 warp partials in a fixed order, write the CTA partial [FP8][FP8] ----
+  double* red = reinterpret_cast<double*>(smem_raw);  // [GRAM_WARPS][NTRI][64] (host sizes for both uses)
+#pragma unroll
+  for (int k = 0; k < NTRI; ++k) {
+    double* dst = red + ((size_t)warp * NTRI + k) * 64 + g * 8 + 2 * q;
+    dst[0] = acc[k][0]; dst[1] = acc[k][1];
+  }
+  __syncthreads();
+  double* out = partial + (size_t)blockIdx.x * FP8 * FP8;
+  for (int i = tid; i < NTRI * 64; i += GRAM_THREADS) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < GRAM_WARPS; ++w) s += red[(size_t)w * NTRI * 64 + i];
+    int slot = i >> 6, e = i & 63;
+    int a = 0, rem = slot, rowlen = NS;
+    while (rem >= rowlen) { rem -= rowlen; ++a; --rowlen; }
+    const int b = a + rem;
+    out[(8 * a + (e >> 3)) * FP8 + 8 * b + (e & 7)] = s;
+  }
+}
 
 template <int MAXT>
 __global__ void __launch_bounds__(GRAM_THREADS)
-linbase_gram_kernel(const float* __restrict__ obs, const double* __restrict__ ret,
-                    const int32_t* __restrict__ off, int P, int64_t N, int n, int TS, int G,
-                    int ntile_side, int ntiles_tri, double* __restrict__ partial) {
+linbase_gram_tiles_kernel(const float* __restrict__ obs, const double* __restrict__ ret,
+                          const int32_t* __restrict__ off, int P, int64_t N, int n, int TS, int FS,
+                          int nside, int ntri, double* __restrict__ partial) {
   extern __shared__ unsigned char smem_raw[];
-  const int F1 = n + 5;               // features + y
-  const int FP = (F1 + 3) & ~3;       // padded row length (multiple of 4)
-  double* feat = reinterpret_cast<double*>(smem_raw);  // [TS][FP]
-  const int tid = threadIdx.x;
-
-  // tile ownership: slot s = tid % ntiles_tri (+ k*GRAM_THREADS for MAXT>1), group = tid / ntiles_tri
+  const int FP8 = 8 * nside;
+  double* feat = reinterpret_cast<double*>(smem_raw);  // [TS][FS]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, q = lane & 3;
+  // tile ownership: contiguous row-major run of the upper triangle -> the A fragment is shared
+  const int per = (ntri + GRAM_WARPS - 1) / GRAM_WARPS;
+  const int s_begin = warp * per;
+  const int nown = max(0, min(per, ntri - s_begin));
   int ti[MAXT], tj[MAXT];
-  bool own[MAXT];
-  int grp = 0;
-#pragma unroll
-  for (int k = 0; k < MAXT; ++k) {
-    int s;
-    if (MAXT == 1) { s = tid % ntiles_tri; grp = tid / ntiles_tri; own[k] = grp < G; }
-    else { s = tid + k * GRAM_THREADS; grp = 0; own[k] = s < ntiles_tri; }
-    // decode s -> (ti, tj) with tj >= ti, row-major over the upper triangle
-    int a = 0, rem = own[k] ? s : 0, rowlen = ntile_side;
+  {
+    int a = 0, rem = nown > 0 ? s_begin : 0, rowlen = nside;
     while (rem >= rowlen) { rem -= rowlen; ++a; --rowlen; }
-    ti[k] = a; tj[k] = a + rem;
+    int b = a + rem;
+#pragma unroll
+    for (int k = 0; k < MAXT; ++k) {
+      ti[k] = a; tj[k] = b;
+      if (++b == nside) { ++a; b = a; }
+      if (a >= nside) { a = nside - 1; b = nside - 1; }  // past the end: never used (k >= nown)
+    }
   }
-  double acc[MAXT][16];
+  double acc[MAXT][2];
 #pragma unroll
-  for (int k = 0; k < MAXT; ++k)
-#pragma unroll
-    for (int e = 0; e < 16; ++e) acc[k][e] = 0.0;
+  for (int k = 0; k < MAXT; ++k) acc[k][0] = acc[k][1] = 0.0;
 
   const int64_t ntiles = (N + TS - 1) / TS;
+  const int nq = TS >> 2;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t t0 = tile * TS;
     const int rows = (int)min((int64_t)TS, N - t0);
     __syncthreads();
-    // obs block (coalesced) -> clipped fp64 features
-    const float* src = obs + t0 * n;
-    const int cnt = rows * n;
-    for (int i = tid; i < cnt; i += GRAM_THREADS) {
-      int r = i / n, c = i - r * n;
-      feat[r * FP + c] = (double)fminf(fmaxf(ld_stream(src + i), -10.f), 10.f);
-    }
-    for (int r = tid; r < TS; r += GRAM_THREADS) {
-      double* row = feat + r * FP;
-      if (r < rows) {
-        const int64_t t = t0 + r;
-        const int p = find_path(off, P, t);
-        const double al = (double)(t - off[p]) / 1000.0;
-        row[n] = al; row[n + 1] = al * al; row[n + 2] = al * al * al; row[n + 3] = 1.0;
-        row[n + 4] = ld_stream(ret + t);
-        for (int c = F1; c < FP; ++c) row[c] = 0.0;
-      } else {
-        for (int c = 0; c < FP; ++c) row[c] = 0.0;  // zero rows contribute nothing
-      }
-    }
+    gram_stage_tile(obs, ret, off, P, (double)P / (double)N, t0, rows, n, TS, FP8, FS, feat, tid);
     __syncthreads();
+    for (int qd = 0; qd < nq; ++qd) {
+      const double* fr = feat + (4 * qd + q) * FS + g;
+      double fa = 0.0;
 #pragma unroll
-    for (int k = 0; k < MAXT; ++k) {
-      if (!own[k]) continue;
-      const double* pa = feat + 4 * ti[k];
-      const double* pb = feat + 4 * tj[k];
-      for (int r = grp; r < TS; r += G) {
-        const double2 a01 = *reinterpret_cast<const double2*>(pa + r * FP);
-        const double2 a23 = *reinterpret_cast<const double2*>(pa + r * FP + 2);
-        const double2 b01 = *reinterpret_cast<const double2*>(pb + r * FP);
-        const double2 b23 = *reinterpret_cast<const double2*>(pb + r * FP + 2);
-        const double a[4] = {a01.x, a01.y, a23.x, a23.y};
-        const double b[4] = {b01.x, b01.y, b23.x, b23.y};
-#pragma unroll
-        for (int x = 0; x < 4; ++x)
-#pragma unroll
-          for (int y = 0; y < 4; ++y) acc[k][x * 4 + y] = fma(a[x], b[y], acc[k][x * 4 + y]);
+      for (int k = 0; k < MAXT; ++k) {
+        if (k < nown) {  // warp-uniform
+          if (k == 0 || ti[k] != ti[k - 1]) fa = fr[8 * ti[k]];
+          const double fb = fr[8 * tj[k]];
+          dmma_m8n8k4(acc[k][0], acc[k][1], fa, fb);
+        }
       }
     }
   }
-  // ---- reduce the G groups of this CTA in a fixed order, write the CTA partial ----
-  __syncthreads();
-  double* red = feat;  // reuse: [G][ntiles_tri][16] may exceed the feature tile -> sized by host
-  const int S1 = FP;   // partial layout: dense [FP][FP] upper-tile entries
-  double* out = partial + (size_t)blockIdx.x * S1 * S1;
-  if (MAXT == 1) {
-    if (own[0]) {
-      double* dst = red + ((size_t)grp * ntiles_tri + (tid % ntiles_tri)) * 16;
+  double* out = partial + (size_t)blockIdx.x * FP8 * FP8;
 #pragma unroll
-      for (int e = 0; e < 16; ++e) dst[e] = acc[0][e];
-    }
-    __syncthreads();
-    for (int i = tid; i < ntiles_tri * 16; i += GRAM_THREADS) {
-      double s = 0.0;
-      for (int g = 0; g < G; ++g) s += red[(size_t)g * ntiles_tri * 16 + i];
-      int slot = i >> 4, e = i & 15;
-      int a = 0, rem = slot, rowlen = ntile_side;
-      while (rem >= rowlen) { rem -= rowlen; ++a; --rowlen; }
-      int b = a + rem;
-      out[(4 * a + (e >> 2)) * S1 + 4 * b + (e & 3)] = s;
-    }
-  } else {
-#pragma unroll
-    for (int k = 0; k < MAXT; ++k) {
-      if (!own[k]) continue;
-#pragma unroll
-      for (int e = 0; e < 16; ++e)
-        out[(4 * ti[k] + (e >> 2)) * S1 + 4 * tj[k] + (e & 3)] = acc[k][e];
+  for (int k = 0; k < MAXT; ++k) {
+    if (k < nown) {
+      double* dst = out + (size_t)(8 * ti[k] + g) * FP8 + 8 * tj[k] + 2 * q;
+      dst[0] = acc[k][0]; dst[1] = acc[k][1];
     }
   }
 }
@@ -188,7 +381,7 @@ __global__ void linbase_gram_reduce_kernel(const double* __restrict__ partial, i
     int i, j;
     if (idx == F * F1) { i = F; j = F; } else { i = idx / F1; j = idx - i * F1; }
     int a = min(i, j), b = max(i, j);
-    // entry (a,b) lives in tile (a/4, b/4) which is stored iff b/4 >= a/4 -- always true
+    // entry (a,b) lives in tile (a/8, b/8) which is stored iff b/8 >= a/8 -- always true
     double s = 0.0;
     for (int c = 0; c < nparts; ++c) s += partial[(size_t)c * FP * FP + a * FP + b];
     gram[idx] = s;
@@ -302,13 +495,18 @@ int mjrl_linbase_predict(mjrl_ctx* ctx, const float* obs, const int32_t* off, in
     return mjrl_check_launch("linbase_predict(zero)");
   }
   MJRL_REQUIRE(obs && off, MJRL_E_ARG, "linbase_predict: null pointer");
-  size_t smem = sizeof(double) * ((n + 4 + 1) & ~1) + sizeof(float) * PRED_TS * (n | 1);
+  const size_t coef_b = sizeof(double) * ((n + 4 + 1) & ~1), tile_b = sizeof(float) * PRED_TS * (size_t)n;
+  const int nbuf = coef_b + 2 * tile_b <= (size_t)100 * 1024 ? 2 : 1;  // double-buffer while 2 CTAs/SM fit
+  size_t smem = coef_b + nbuf * tile_b;
   MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE, "linbase_predict: n=%d too large", n);
-  if (smem > 48 * 1024)
+  if (smem > 40 * 1024)
     cudaFuncSetAttribute(linbase_predict_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int per_sm = 1;  // persistent grid = exactly the resident CTAs (a larger grid leaves a half-empty second wave)
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, linbase_predict_kernel, PRED_TS, smem);
+  per_sm = per_sm < 1 ? 1 : per_sm;
   int64_t ntiles = (N + PRED_TS - 1) / PRED_TS;
-  int grid = (int)(ntiles < (int64_t)ctx->sm_count * 8 ? ntiles : (int64_t)ctx->sm_count * 8);
-  linbase_predict_kernel<<<grid, PRED_TS, smem, s>>>(obs, off, P, N, n, coeffs, pred);
+  int grid = (int)(ntiles < (int64_t)ctx->sm_count * per_sm ? ntiles : (int64_t)ctx->sm_count * per_sm);
+  linbase_predict_kernel<<<grid, PRED_TS, smem, s>>>(obs, off, P, N, n, nbuf, coeffs, pred);
   return mjrl_check_launch("linbase_predict");
 }
 
@@ -316,35 +514,69 @@ int mjrl_linbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, co
                       int32_t P, int64_t N, int32_t n, double* gram, void* stream) {
   MJRL_REQUIRE(ctx && obs && returns && off && gram && N > 0 && n > 0 && P > 0, MJRL_E_ARG,
                "linbase_gram: bad argument");
-  const int F = n + 4, F1 = F + 1, FP = (F1 + 3) & ~3;
-  const int side = FP / 4, ntri = side * (side + 1) / 2;
-  MJRL_REQUIRE(ntri <= 2 * GRAM_THREADS, MJRL_E_SHAPE,
-               "linbase_gram: n=%d gives %d Gram tiles (> %d)", n, ntri, 2 * GRAM_THREADS);
-  const int maxt = ntri <= GRAM_THREADS ? 1 : 2;
-  int TS = FP <= 32 ? 128 : 32;
-  int G = 1;
-  if (maxt == 1) { G = GRAM_THREADS / ntri; if (G > TS) G = TS; }
-  size_t smem_feat = sizeof(double) * (size_t)TS * FP;
-  size_t smem_red = maxt == 1 ? sizeof(double) * (size_t)G * ntri * 16 : 0;
-  size_t smem = smem_feat > smem_red ? smem_feat : smem_red;
+  const int F = n + 4, F1 = F + 1, FP = (F1 + 7) & ~7;
+  const int nside = FP / 8, ntri = nside * (nside + 1) / 2;
+  const int per = (ntri + GRAM_WARPS - 1) / GRAM_WARPS;
+  MJRL_REQUIRE(nside <= 3 || per <= 32, MJRL_E_SHAPE,
+               "linbase_gram: n=%d gives %d Gram tiles (> %d)", n, ntri, 32 * GRAM_WARPS);
+  int FS = FP;  // row stride in doubles, = 4 (mod 16): the fragment loads hit 16 distinct bank pairs
+  while ((FS & 15) != 4) ++FS;
+  const int TS = FS <= 24 ? 256 : (FS <= 52 ? 128 : 64);
+  size_t smem = sizeof(double) * (size_t)TS * FS;
+  // split variant: two fp32 obs tiles + the fp64 columns (row stride 9 doubles: the per-timestep
+  // writes and the fragment reads are both conflict-free; 18 when two 8-wide blocks live there:
+  // 2-way); reused for the warp partials
+  const int EXS = (nside - n / 8) == 1 ? 9 : 18;
+  if (nside <= 3) {
+    smem = (size_t)2 * TS * n * sizeof(float) + sizeof(double) * (size_t)TS * EXS;
+    size_t smem_red = sizeof(double) * (size_t)GRAM_WARPS * ntri * 64;
+    if (smem_red > smem) smem = smem_red;
+  }
   MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE, "linbase_gram: smem %zu", smem);
+  const void* kern = nullptr;
+  if (nside == 1) kern = (const void*)linbase_gram_split_kernel<1>;
+  else if (nside == 2) kern = (const void*)linbase_gram_split_kernel<2>;
+  else if (nside == 3) kern = (const void*)linbase_gram_split_kernel<3>;
+  else if (per <= 4) kern = (const void*)linbase_gram_tiles_kernel<4>;
+  else if (per <= 8) kern = (const void*)linbase_gram_tiles_kernel<8>;
+  else if (per <= 16) kern = (const void*)linbase_gram_tiles_kernel<16>;
+  else kern = (const void*)linbase_gram_tiles_kernel<32>;
+  if (smem > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int per_sm = 1;  // persistent grid = exactly the resident CTAs
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, GRAM_THREADS, smem);
+  per_sm = per_sm < 1 ? 1 : per_sm;
+  if (nside > 3 && per_sm > 2) per_sm = 2;  // bounds the scratch of the per-CTA partials
   int64_t ntiles = (N + TS - 1) / TS;
-  int grid = (int)(ntiles < (int64_t)ctx->sm_count * 2 ? ntiles : (int64_t)ctx->sm_count * 2);
+  int grid = (int)(ntiles < (int64_t)ctx->sm_count * per_sm ? ntiles : (int64_t)ctx->sm_count * per_sm);
   double* partial = (double*)mjrl_scratch2(ctx, sizeof(double) * (size_t)grid * FP * FP);
   if (!partial) return MJRL_E_STATE;
   cudaStream_t s = (cudaStream_t)stream;
   // partials are written sparsely (upper tiles only); entries never written are never read
-  if (maxt == 1) {
-    if (smem > 48 * 1024)
-      cudaFuncSetAttribute(linbase_gram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    linbase_gram_kernel<1><<<grid, GRAM_THREADS, smem, s>>>(obs, returns, off, P, N, n, TS, G, side,
-                                                            ntri, partial);
-  } else {
-    if (smem > 48 * 1024)
-      cudaFuncSetAttribute(linbase_gram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    linbase_gram_kernel<2><<<grid, GRAM_THREADS, smem, s>>>(obs, returns, off, P, N, n, TS, G, side,
-                                                            ntri, partial);
-  }
+#define GRAM_SPLIT(NS)                                                                              \
+  do {                                                                                              \
+    if (smem > 40 * 1024)                                                                           \
+      cudaFuncSetAttribute(linbase_gram_split_kernel<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                           (int)smem);                                                              \
+    linbase_gram_split_kernel<NS><<<grid, GRAM_THREADS, smem, s>>>(obs, returns, off, P, N, n, TS,  \
+                                                                   EXS, partial);                   \
+  } while (0)
+#define GRAM_TILES(MT)                                                                              \
+  do {                                                                                              \
+    if (smem > 40 * 1024)                                                                           \
+      cudaFuncSetAttribute(linbase_gram_tiles_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                           (int)smem);                                                              \
+    linbase_gram_tiles_kernel<MT><<<grid, GRAM_THREADS, smem, s>>>(obs, returns, off, P, N, n, TS, FS, \
+                                                                   nside, ntri, partial);           \
+  } while (0)
+  if (nside == 1) GRAM_SPLIT(1);
+  else if (nside == 2) GRAM_SPLIT(2);
+  else if (nside == 3) GRAM_SPLIT(3);
+  else if (per <= 4) GRAM_TILES(4);
+  else if (per <= 8) GRAM_TILES(8);
+  else if (per <= 16) GRAM_TILES(16);
+  else GRAM_TILES(32);
+#undef GRAM_SPLIT
+#undef GRAM_TILES
   int rc = mjrl_check_launch("linbase_gram");
   if (rc) return rc;
   int total = F * F1 + 1;
@@ -358,7 +590,7 @@ int mjrl_linbase_solve(mjrl_ctx* ctx, const double* gram, int32_t F, double reg_
   size_t smem = sizeof(double) * ((size_t)F * (F + 1) + F);
   MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE,
                "linbase_solve: F=%d needs %zu B of shared memory", F, smem);
-  if (smem > 48 * 1024)
+  if (smem > 40 * 1024)
     cudaFuncSetAttribute(linbase_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   linbase_solve_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(gram, F, reg_coeff, coeffs_prev, coeffs, info4);
   return mjrl_check_launch("linbase_solve");

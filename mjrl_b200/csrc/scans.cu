@@ -21,12 +21,11 @@ constexpr int SCAN_CHUNK = SCAN_THREADS * SCAN_E;  // 1024
 __device__ __forceinline__ int padi(int i) { return i + (i >> 3); }  // conflict-free blocked reads
 
 template <bool GAE>
-__global__ void __launch_bounds__(SCAN_THREADS)
+__global__ void __launch_bounds__(SCAN_THREADS, 8)
 segscan_kernel(const double* __restrict__ rew, const double* __restrict__ base,
                const int32_t* __restrict__ off, const uint8_t* __restrict__ term, int P,
                double g_td /*gamma*/, double g /*scan discount*/, double* __restrict__ out) {
   __shared__ double sx[SCAN_CHUNK + SCAN_CHUNK / 8 + 8];
-  __shared__ double sb[GAE ? SCAN_CHUNK + 8 : 1];
   __shared__ double swarp[SCAN_THREADS / 32];
   __shared__ double scarry;
 
@@ -56,39 +55,39 @@ segscan_kernel(const double* __restrict__ rew, const double* __restrict__ base,
     const int c0 = c * SCAN_CHUNK;
     const int L = min(SCAN_CHUNK, T - c0);
     const int64_t gbase = s0 + c0;
-    // ---- coalesced load ----------------------------------------------------
+    // ---- coalesced load: every request of the chunk is issued before the first use.  GAE forms
+    // the TD residual here, in the coalesced domain: b[t+1] is a second, one-element-shifted
+    // coalesced read of the same sectors (an L2 hit), so only the residual goes through smem.
+    {
+      double r[SCAN_E], b[GAE ? SCAN_E : 1], bn[GAE ? SCAN_E : 1];
 #pragma unroll
-    for (int k = 0; k < SCAN_E; ++k) {
-      int i = k * SCAN_THREADS + tid;
-      double r = 0.0;
-      if (i < L) r = ld_stream(rew + gbase + i);
-      if (GAE) {
-        double b = 0.0;
-        if (i < L) b = ld_stream(base + gbase + i);
-        else if (i == L) b = (c0 + L < T) ? ld_stream(base + gbase + L) : b_tail;  // halo b1[t+1]
-        sb[i] = b;
+      for (int k = 0; k < SCAN_E; ++k) {
+        const int i = k * SCAN_THREADS + tid;
+        r[k] = (i < L) ? ldg_stream(rew + gbase + i) : 0.0;
       }
-      sx[padi(i)] = r;
+      if (GAE) {
+#pragma unroll
+        for (int k = 0; k < SCAN_E; ++k) {
+          const int i = k * SCAN_THREADS + tid;
+          b[k] = (i < L) ? ldg_stream(base + gbase + i) : 0.0;
+          bn[k] = (i < L && c0 + i + 1 < T) ? __ldg(base + gbase + i + 1) : b_tail;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < SCAN_E; ++k) {
+        const int i = k * SCAN_THREADS + tid;
+        double x = r[k];
+        // (r + gamma*b[t+1]) - b[t], same association as process_samples.py:28
+        if (GAE) x = (i < L) ? __dsub_rn(__dadd_rn(x, __dmul_rn(g_td, bn[k])), b[k]) : 0.0;
+        sx[padi(i)] = x;
+      }
     }
-    if (GAE && L == SCAN_CHUNK && tid == 0)
-      sb[L] = (c0 + L < T) ? ld_stream(base + gbase + L) : b_tail;
     __syncthreads();
-    // ---- blocked read, TD residual, per-thread reverse scan ----------------
+    // ---- blocked read, per-thread reverse scan -------------------------------
     double y[SCAN_E];
     const int e0 = tid * SCAN_E;
 #pragma unroll
-    for (int j = 0; j < SCAN_E; ++j) {
-      int i = e0 + j;
-      double x = sx[padi(i)];
-      if (GAE) {
-        // (r + gamma*b[t+1]) - b[t], same association as process_samples.py:28
-        double bn = (i < L) ? sb[i + 1] : 0.0;
-        double bc = (i < L) ? sb[i] : 0.0;
-        x = __dsub_rn(__dadd_rn(x, __dmul_rn(g_td, bn)), bc);
-        if (i >= L) x = 0.0;
-      }
-      y[j] = x;
-    }
+    for (int j = 0; j < SCAN_E; ++j) y[j] = sx[padi(e0 + j)];
     // inject the carry of the later chunk as a virtual addend on the last valid element
     if (c != nchunks - 1 && tid == SCAN_THREADS - 1)  // L == SCAN_CHUNK here
       y[SCAN_E - 1] += g * carry;

@@ -131,3 +131,81 @@ def test_linbase_nan_retry_and_large_feature_count():
     gb2.fit(bad)
     assert np.all(np.isnan(np.asarray(gb2._coeffs)))
     assert gb2.last_fit_info["retries"] == 9
+
+
+@pytest.mark.parametrize("n,lens", [
+    (11, [1000] * 7 + [37]),          # Hopper: split variant, bulk tiles + ragged last tile (rows*n % 4 != 0)
+    (11, [25] * 90 + [3]),            # short paths: several boundaries inside every tile
+    (8, [300, 513, 2]),               # n % 4 == 0: 16-byte row reads, one 8x8 tile row + target column
+    (6, [257, 255]),                  # n % 2 == 0
+    (17, [700, 1, 1, 400]),           # 3x3 tiles split variant, single-timestep paths
+    (3, [5]),                         # fewer timesteps than one MMA group pair
+    (39, [400, 333]),                 # warp-owned tiles (MAXT = 4)
+    (61, [300, 211]),                 # MAXT = 8
+])
+def test_linbase_fit_predict_shapes_vs_oracle(n, lens):
+    """Gram (fp64 tensor-core tiles) + solve + predict vs the oracle on shapes that exercise every
+    staging variant.  1e-6 relative is the gate (north_star); measured ~1e-12."""
+    from oracle import mjrl_oracle as O
+    ps, LinearBaseline, EnvSpec, drop_cache = _mods()
+    drop_cache()
+    rng = np.random.default_rng(n * 1000 + len(lens))
+    paths = [dict(observations=(4 * rng.standard_normal((T, n))).astype(np.float32).astype(np.float64),
+                  actions=np.zeros((T, 2)), rewards=rng.standard_normal(T), terminated=False)
+             for T in lens]
+    ref = copy.deepcopy(paths)
+    O.compute_returns(ref, 0.98)
+    ps.compute_returns(paths, 0.98)
+    gb, ob = LinearBaseline(EnvSpec(n, 2, max(lens), 1)), O.LinearBaseline()
+    eg = gb.fit(paths, return_errors=True)
+    eo = ob.fit(ref, return_errors=True)
+    X = np.concatenate([O.linear_features(p) for p in ref])
+    want = X @ ob._coeffs
+    got_fit = X @ np.asarray(gb._coeffs)
+    scale = max(1.0, float(np.abs(want).max()))
+    if sum(lens) > n + 8:   # well-posed fits only: tiny batches are dominated by the ridge term
+        assert np.max(np.abs(got_fit - want)) / scale < 1e-6
+        assert abs(eg[1] - eo[1]) < 1e-6
+    # predict with the ORACLE's coefficients: isolates the predict kernel
+    gb._coeffs = ob._coeffs.copy()
+    drop_cache()
+    got = np.concatenate([gb.predict(p) for p in paths])
+    assert np.max(np.abs(got - want)) / scale < 1e-9
+
+
+def test_linbase_kernels_unaligned_obs_base():
+    """obs pointer not 16-byte aligned (a row slice of a larger buffer): the kernels must take the
+    plain-load staging path instead of bulk copies and give the same Gram / predictions."""
+    from mjrl_b200 import _lib
+    from mjrl_b200._lib import c_i64, c_int, ptr, stream_ptr
+    ctx = _lib.context()
+    dev = torch.device("cuda", ctx.device)
+    rng = np.random.default_rng(5)
+    n, lens = 11, [700, 450, 131]
+    N, F = sum(lens), n + 4
+    big = torch.from_numpy(rng.standard_normal((N + 1, n)).astype(np.float32) * 6).to(dev)
+    obs_u = big[1:]                                  # data_ptr offset 44 B
+    obs_a = obs_u.clone()
+    assert obs_u.data_ptr() % 16 != 0 and obs_a.data_ptr() % 16 == 0
+    ret = torch.from_numpy(rng.standard_normal(N)).to(dev)
+    off = torch.from_numpy(np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)).to(dev)
+    coef = torch.from_numpy(rng.standard_normal(F)).to(dev)
+    out = {}
+    for name, obs in (("u", obs_u), ("a", obs_a)):
+        gram = torch.empty(F * (F + 1) + 1, dtype=torch.float64, device=dev)
+        pred = torch.empty(N, dtype=torch.float64, device=dev)
+        ctx.call("mjrl_linbase_gram", ptr(obs), ptr(ret), ptr(off), c_int(len(lens)), c_i64(N), c_int(n),
+                 ptr(gram), stream_ptr())
+        ctx.call("mjrl_linbase_predict", ptr(obs), ptr(off), c_int(len(lens)), c_i64(N), c_int(n), ptr(coef),
+                 ptr(pred), stream_ptr())
+        out[name] = (gram.cpu().numpy(), pred.cpu().numpy())
+    np.testing.assert_array_equal(out["u"][1], out["a"][1])
+    np.testing.assert_allclose(out["u"][0], out["a"][0], rtol=1e-12, atol=1e-9)
+    # and against numpy
+    X = np.concatenate([obs_a.cpu().numpy().clip(-10, 10).astype(np.float64),
+                        np.concatenate([np.stack([(np.arange(T) / 1000.0) ** k for k in (1, 2, 3)] +
+                                                 [np.ones(T)], 1) for T in lens])], 1)
+    np.testing.assert_allclose(out["a"][1], X @ coef.cpu().numpy(), rtol=1e-10, atol=1e-10)
+    G = out["a"][0][:F * (F + 1)].reshape(F, F + 1)
+    np.testing.assert_allclose(G[:, :F], X.T @ X, rtol=1e-10, atol=1e-8)
+    np.testing.assert_allclose(G[:, F], X.T @ ret.cpu().numpy(), rtol=1e-10, atol=1e-8)
