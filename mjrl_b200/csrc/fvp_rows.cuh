@@ -1,0 +1,495 @@
+// Fisher-vector product, "rows in registers" variant (included by policy.cu, namespace pol).
+//
+// Same math as mlp_kernel<.., M_FVP, ..> (npg_cg.py:55-74 replaced by the analytic Gauss-Newton
+// product), different dataflow.  A CTA tile is 128 timesteps; warp w owns rows 16w..16w+15 and keeps
+// the WHOLE forward / tangent / backward chain of those rows in registers:
+//
+//   The C fragment of mma.m16n8k8 holds (row g, cols 2c,2c+1 | row g+8, cols 2c,2c+1).  Read as an
+//   A fragment with the k-slot map  slot c <-> col 2c,  slot c+4 <-> col 2c+1  it IS the next
+//   layer's A operand (any permutation of k is fine when B uses the same one), and under that map
+//   a B fragment (k-slots c, c+4 of output n = g) is the adjacent pair W[n][8j+2c], W[n][8j+2c+1] of
+//   the weight matrix in its natural [out][in] layout: ONE 8-byte shared load.
+//
+// So activations never round-trip through shared memory and the layers need no CTA barrier; shared
+// memory holds only the weights (natural layout, row stride = 8 mod 32 words: conflict-free 8-byte
+// fragment loads) and, for the weight gradients  gW[o][i] = sum_t gz[t][o] a[t][i]  that contract
+// over timesteps of ALL warps, transposed planes [feature][t] written from the C fragments; their
+// fragments are again adjacent pairs (t, t+1).  Bias gradients ride along as a ones column.
+// 3xTF32 error compensation as in policy_tile.cuh; every split happens in registers.
+#pragma once
+
+namespace pol {
+namespace rows {
+
+constexpr int TSR = 128;        // timesteps per CTA tile (8 warps x 16 rows)
+constexpr int LDT = TSR + 8;    // row stride of the transposed planes (= 8 mod 32)
+__host__ __device__ constexpr int ldx_of(int NP) { return ((NP + 8) % 16 == 8) ? NP + 8 : NP + 16; }
+
+struct RLayout {  // offsets in floats
+  int NP, LDX, LDW;
+  int X, XT, PA, PB, UT, XR, W0, V0, W1, V1, W1T, W2, V2, W2T, b0, vb0, b1, vb1, vb2, fisher, ishift, iden;
+  int total;
+  __host__ __device__ RLayout(int HP, int NPK, int n) {
+    NP = 8 * NPK; LDX = ldx_of(NP); LDW = HP + 8;
+    int o = 0;
+    auto take = [&](int cnt) { int r = o; o += (cnt + 3) & ~3; return r; };
+    PA = take(HP * LDT); PB = take(HP * LDT);   // contiguous: reused as the [d] staging vector
+    X = take(TSR * LDX); XT = take(NP * LDT); UT = take(16 * LDT);
+    XR = take(2 * TSR * n);
+    W0 = take(HP * LDX); V0 = take(HP * LDX);
+    W1 = take(HP * LDW); V1 = take(HP * LDW); W1T = take(HP * LDW);
+    W2 = take(8 * LDW); V2 = take(8 * LDW); W2T = take(HP * 8);
+    b0 = take(HP); vb0 = take(HP); b1 = take(HP); vb1 = take(HP); vb2 = take(8); fisher = take(8);
+    ishift = take(NP); iden = take(NP);
+    total = o;
+  }
+};
+
+// float2 (adjacent pair) -> B fragment (k-slot c = first, c+4 = second)
+__device__ __forceinline__ void split_b(Frag2& f, const float2 v) {
+  split_tf32(v.x, f.hi[0], f.lo[0]);
+  split_tf32(v.y, f.hi[1], f.lo[1]);
+}
+// C fragment (or two adjacent pairs of rows g / g+8) -> A fragment under the slot map
+__device__ __forceinline__ void split_a(Frag4& f, float r0c0, float r0c1, float r1c0, float r1c1) {
+  split_tf32(r0c0, f.hi[0], f.lo[0]);   // a0 (g,   slot c)
+  split_tf32(r1c0, f.hi[1], f.lo[1]);   // a1 (g+8, slot c)
+  split_tf32(r0c1, f.hi[2], f.lo[2]);   // a2 (g,   slot c+4)
+  split_tf32(r1c1, f.hi[3], f.lo[3]);   // a3 (g+8, slot c+4)
+}
+__device__ __forceinline__ void split_a(Frag4& f, const float (&cfrag)[4]) {
+  split_a(f, cfrag[0], cfrag[1], cfrag[2], cfrag[3]);
+}
+// one 3xTF32 term (0: lo*hi, 1: hi*lo, 2: hi*hi) of acc += a * b
+__device__ __forceinline__ void mma_term(float (&acc)[4], const Frag4& a, const Frag2& b, int term) {
+  mma_tf32(acc, term == 0 ? a.lo : a.hi, term == 1 ? b.lo : b.hi);
+}
+
+template <int HP, int NPK>
+__global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
+  constexpr int NF = HP / 8;          // 8-wide feature blocks of a hidden layer
+  constexpr int MT = HP / 16;         // 16-row bands of a weight gradient
+  constexpr int NP = 8 * NPK, LDX = ldx_of(NP), LDW = HP + 8;
+  constexpr int NW1 = MT * NF / 8;    // gW1 fragments per warp, all in one band
+  constexpr int NW0 = (MT * NPK + 7) / 8;
+  constexpr int G = NF < 4 ? NF : 4;  // n-blocks whose MMAs are interleaved term by term
+  static_assert(NF % NW1 == 0 && NF % G == 0, "fragment ownership");
+  extern __shared__ __align__(16) float sm[];
+  __shared__ uint64_t bar[2];
+  if (a.stop_flag && *a.stop_flag) return;
+
+  const RLayout L(HP, NPK, a.n);
+  const Flat F(a.n, a.m, a.h1, a.h2);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, c = lane & 3;
+  const int n = a.n, m = a.m;
+  float* sX = sm + L.X; float* sXT = sm + L.XT; float* sPA = sm + L.PA; float* sPB = sm + L.PB;
+  float* sUT = sm + L.UT; float* sXR = sm + L.XR;
+  const float* sW0 = sm + L.W0; const float* sV0 = sm + L.V0; const float* sW1 = sm + L.W1;
+  const float* sV1 = sm + L.V1; const float* sW1T = sm + L.W1T; const float* sW2 = sm + L.W2;
+  const float* sV2 = sm + L.V2; const float* sW2T = sm + L.W2T;
+
+  // ---- one-time staging: zero everything, then weights in their natural [out][in] layout ------
+  for (int i = tid; i < L.total; i += NTHREADS) sm[i] = 0.f;
+  if (tid == 0) { tma::mbar_init(&bar[0], 1); tma::mbar_init(&bar[1], 1); tma::mbar_init_fence(); }
+  __syncthreads();
+  {
+    const float* P = a.params; const float* V = a.vec;
+    for (int i = tid; i < F.h1 * n; i += NTHREADS) {
+      const int o = i / n, k = i - o * n;
+      sm[L.W0 + o * LDX + k] = __ldg(P + F.oW0 + i);
+      sm[L.V0 + o * LDX + k] = __ldg(V + F.oW0 + i);
+    }
+    for (int i = tid; i < F.h2 * F.h1; i += NTHREADS) {
+      const int o = i / F.h1, k = i - o * F.h1;
+      const float w = __ldg(P + F.oW1 + i);
+      sm[L.W1 + o * LDW + k] = w;
+      sm[L.W1T + k * LDW + o] = w;
+      sm[L.V1 + o * LDW + k] = __ldg(V + F.oW1 + i);
+    }
+    for (int i = tid; i < m * F.h2; i += NTHREADS) {
+      const int j = i / F.h2, k = i - j * F.h2;
+      const float w = __ldg(P + F.oW2 + i);
+      sm[L.W2 + j * LDW + k] = w;
+      sm[L.W2T + k * 8 + j] = w;
+      sm[L.V2 + j * LDW + k] = __ldg(V + F.oW2 + i);
+    }
+    for (int i = tid; i < F.h1; i += NTHREADS) { sm[L.b0 + i] = __ldg(P + F.ob0 + i); sm[L.vb0 + i] = __ldg(V + F.ob0 + i); }
+    for (int i = tid; i < F.h2; i += NTHREADS) { sm[L.b1 + i] = __ldg(P + F.ob1 + i); sm[L.vb1 + i] = __ldg(V + F.ob1 + i); }
+    for (int j = tid; j < m; j += NTHREADS) {
+      sm[L.vb2 + j] = __ldg(V + F.ob2 + j);
+      const float sg = expf(__ldg(P + F.ols + j));
+      const float os = a.out_scale ? __ldg(a.out_scale + j) : 1.f;
+      // d^2 KL / d mu^2 = 2/(2 sigma^2 + 1e-8)  (gaussian_mlp.py:137-138), chained through out_scale twice
+      sm[L.fisher + j] = os * os * (2.f / (2.f * sg * sg + 1e-8f));
+    }
+    for (int i = tid; i < NP; i += NTHREADS) {
+      sm[L.ishift + i] = (a.in_shift && i < n) ? __ldg(a.in_shift + i) : 0.f;
+      sm[L.iden + i] = (a.in_scale && i < n ? __ldg(a.in_scale + i) : 1.f) + 1e-8f;
+    }
+  }
+
+  // persistent weight-gradient accumulators (C fragments, unique owner per element)
+  float accW1[NW1][4], accB1[4], accW0[NW0][4], accW2[4], gb2acc = 0.f;
+#pragma unroll
+  for (int j = 0; j < NW1; ++j) accW1[j][0] = accW1[j][1] = accW1[j][2] = accW1[j][3] = 0.f;
+#pragma unroll
+  for (int j = 0; j < NW0; ++j) accW0[j][0] = accW0[j][1] = accW0[j][2] = accW0[j][3] = 0.f;
+  accB1[0] = accB1[1] = accB1[2] = accB1[3] = 0.f;
+  accW2[0] = accW2[1] = accW2[2] = accW2[3] = 0.f;
+  const int mt1 = (warp * NW1) / NF, nf1 = (warp * NW1) % NF;   // gW1 band / first block of this warp
+  const bool own_b1 = nf1 == 0;                                   // this warp also sums the band's gb1
+
+  const int ntiles = (int)((a.N + TSR - 1) / TSR);
+  const int tile_elems = TSR * n;
+  const bool base_ok = (reinterpret_cast<uintptr_t>(a.obs) & 15) == 0;
+  auto tile_rows = [&](int tile) { return tile + 1 < ntiles ? TSR : (int)(a.N - (long long)tile * TSR); };
+  auto bulk_ok = [&](int tile) { return base_ok && ((tile_rows(tile) * n) & 3) == 0; };
+  auto start_copy = [&](int tile, int buf) {  // one thread
+    if (bulk_ok(tile)) {
+      const uint32_t bytes = (uint32_t)(tile_rows(tile) * n) * 4u;
+      tma::mbar_expect(&bar[buf], bytes);
+      tma::bulk_g2s(sXR + (size_t)buf * tile_elems, a.obs + (long long)tile * tile_elems, bytes, &bar[buf]);
+    }
+  };
+  __syncthreads();
+  if (tid == 0 && (int)blockIdx.x < ntiles) start_copy(blockIdx.x, 0);
+
+  const int rA = 16 * warp + g, rB = rA + 8;   // this thread's two rows of the tile
+  int it = 0;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    const int buf = it & 1;
+    const long long t0 = (long long)tile * TSR;
+    const int rows = tile_rows(tile);
+    if (tid == 0 && tile + (int)gridDim.x < ntiles) start_copy(tile + gridDim.x, buf ^ 1);
+    // ---- P0: raw rows -> transformed X [t][k] and X^T [k][t], ones column at k = n ----------
+    {
+      float* raw = sXR + (size_t)buf * tile_elems;
+      if (bulk_ok(tile)) {
+        tma::mbar_wait(&bar[buf], (it >> 1) & 1);
+      } else {
+        stream_rows<NTHREADS>(a.obs + t0 * n, rows * n, n, tid, [&](int r, int k, float v) { raw[r * n + k] = v; });
+        __syncthreads();
+      }
+      const int cnt = rows * n;
+      const int dq = NTHREADS / n, dr = NTHREADS - dq * n;
+      int r = tid / n, k = tid - r * n;
+      for (int i = tid; i < cnt; i += NTHREADS) {
+        const float v = (raw[i] - sm[L.ishift + k]) / sm[L.iden + k];
+        sX[r * LDX + k] = v;
+        sXT[k * LDT + r] = v;
+        r += dq; k += dr;
+        if (k >= n) { k -= n; ++r; }
+      }
+      if (rows < TSR)
+        for (int i = rows * n + tid; i < tile_elems; i += NTHREADS) {
+          const int rr = i / n, kk = i - rr * n;
+          sX[rr * LDX + kk] = 0.f; sXT[kk * LDT + rr] = 0.f;
+        }
+      if (tid < TSR) {
+        const float one = tid < rows ? 1.f : 0.f;
+        sX[tid * LDX + n] = one; sXT[n * LDT + tid] = one;
+      }
+    }
+    __syncthreads();
+
+    // ---- layer 0: z1 = b0 + X W0^T, dz1 = vb0 + X V0^T ------------------------------------------
+    float h1[NF][4], d1[NF][4];
+#pragma unroll
+    for (int nf = 0; nf < NF; ++nf) {
+      const float2 b = *reinterpret_cast<const float2*>(sm + L.b0 + 8 * nf + 2 * c);
+      const float2 vb = *reinterpret_cast<const float2*>(sm + L.vb0 + 8 * nf + 2 * c);
+      h1[nf][0] = b.x; h1[nf][1] = b.y; h1[nf][2] = b.x; h1[nf][3] = b.y;
+      d1[nf][0] = vb.x; d1[nf][1] = vb.y; d1[nf][2] = vb.x; d1[nf][3] = vb.y;
+    }
+#pragma unroll
+    for (int ks = 0; ks < NPK; ++ks) {
+      const float2 xa = *reinterpret_cast<const float2*>(sX + rA * LDX + 8 * ks + 2 * c);
+      const float2 xb = *reinterpret_cast<const float2*>(sX + rB * LDX + 8 * ks + 2 * c);
+      Frag4 ax;
+      split_a(ax, xa.x, xa.y, xb.x, xb.y);
+#pragma unroll
+      for (int n0 = 0; n0 < NF; n0 += G) {
+        Frag2 bw[G], bv[G];
+#pragma unroll
+        for (int i = 0; i < G; ++i) {
+          split_b(bw[i], *reinterpret_cast<const float2*>(sW0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c));
+          split_b(bv[i], *reinterpret_cast<const float2*>(sV0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c));
+        }
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {
+#pragma unroll
+          for (int i = 0; i < G; ++i) mma_term(h1[n0 + i], ax, bw[i], term);
+#pragma unroll
+          for (int i = 0; i < G; ++i) mma_term(d1[n0 + i], ax, bv[i], term);
+        }
+      }
+    }
+#pragma unroll
+    for (int nf = 0; nf < NF; ++nf)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float h = tanh_fast(h1[nf][e]);
+        h1[nf][e] = h;
+        d1[nf][e] = (1.f - h * h) * d1[nf][e];
+      }
+    // H1^T plane for gW1
+#pragma unroll
+    for (int nf = 0; nf < NF; ++nf) {
+      float* p0 = sPA + (8 * nf + 2 * c) * LDT;
+      p0[rA] = h1[nf][0]; p0[LDT + rA] = h1[nf][1]; p0[rB] = h1[nf][2]; p0[LDT + rB] = h1[nf][3];
+    }
+
+    // ---- layer 1: z2 = b1 + H1 W1^T, dz2 = vb1 + H1 V1^T + D1 W1^T ------------------------------
+    float h2[NF][4], d2[NF][4];
+#pragma unroll
+    for (int nf = 0; nf < NF; ++nf) {
+      const float2 b = *reinterpret_cast<const float2*>(sm + L.b1 + 8 * nf + 2 * c);
+      const float2 vb = *reinterpret_cast<const float2*>(sm + L.vb1 + 8 * nf + 2 * c);
+      h2[nf][0] = b.x; h2[nf][1] = b.y; h2[nf][2] = b.x; h2[nf][3] = b.y;
+      d2[nf][0] = vb.x; d2[nf][1] = vb.y; d2[nf][2] = vb.x; d2[nf][3] = vb.y;
+    }
+#pragma unroll
+    for (int ks = 0; ks < NF; ++ks) {
+      Frag4 ah, ad;
+      split_a(ah, h1[ks]);
+      split_a(ad, d1[ks]);
+#pragma unroll
+      for (int n0 = 0; n0 < NF; n0 += G) {
+        Frag2 bw[G], bv[G];
+#pragma unroll
+        for (int i = 0; i < G; ++i) {
+          split_b(bw[i], *reinterpret_cast<const float2*>(sW1 + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c));
+          split_b(bv[i], *reinterpret_cast<const float2*>(sV1 + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c));
+        }
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {
+#pragma unroll
+          for (int i = 0; i < G; ++i) mma_term(h2[n0 + i], ah, bw[i], term);
+#pragma unroll
+          for (int i = 0; i < G; ++i) mma_term(d2[n0 + i], ah, bv[i], term);
+#pragma unroll
+          for (int i = 0; i < G; ++i) mma_term(d2[n0 + i], ad, bw[i], term);
+        }
+      }
+    }
+#pragma unroll
+    for (int nf = 0; nf < NF; ++nf)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float h = tanh_fast(h2[nf][e]);
+        h2[nf][e] = h;
+        d2[nf][e] = (1.f - h * h) * d2[nf][e];
+      }
+
+    // ---- head tangent: dy = H2 V2^T + D2 W2^T;  u = fisher * (dy + vb2), zero past N -----------
+    float u[4];
+    {
+      // four accumulators (product x k parity): a single one would chain 6*NF dependent MMAs
+      float uu[2][2][4];
+#pragma unroll
+      for (int x = 0; x < 2; ++x)
+#pragma unroll
+        for (int y = 0; y < 2; ++y) uu[x][y][0] = uu[x][y][1] = uu[x][y][2] = uu[x][y][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < NF; ++ks) {
+        Frag4 ah, ad;
+        Frag2 bw, bv;
+        split_a(ah, h2[ks]);
+        split_a(ad, d2[ks]);
+        split_b(bw, *reinterpret_cast<const float2*>(sW2 + g * LDW + 8 * ks + 2 * c));
+        split_b(bv, *reinterpret_cast<const float2*>(sV2 + g * LDW + 8 * ks + 2 * c));
+#pragma unroll
+        for (int term = 0; term < 3; ++term) {
+          mma_term(uu[ks & 1][0], ah, bv, term);
+          mma_term(uu[ks & 1][1], ad, bw, term);
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) u[e] = (uu[0][0][e] + uu[0][1][e]) + (uu[1][0][e] + uu[1][1][e]);
+    }
+    {
+      const float2 fj = *reinterpret_cast<const float2*>(sm + L.fisher + 2 * c);
+      const float2 vj = *reinterpret_cast<const float2*>(sm + L.vb2 + 2 * c);
+      const bool va = rA < rows, vb = rB < rows;
+      u[0] = va ? fj.x * (u[0] + vj.x) : 0.f; u[1] = va ? fj.y * (u[1] + vj.y) : 0.f;
+      u[2] = vb ? fj.x * (u[2] + vj.x) : 0.f; u[3] = vb ? fj.y * (u[3] + vj.y) : 0.f;
+      float* p0 = sUT + (2 * c) * LDT;
+      p0[rA] = u[0]; p0[LDT + rA] = u[1]; p0[rB] = u[2]; p0[LDT + rB] = u[3];
+    }
+
+    // ---- back through the head: gz2 = (U W2) * (1 - h2^2) ---------------------------------------
+    float gz[NF][4];   // gz2, later gz1
+    {
+      Frag4 au;
+      split_a(au, u);
+#pragma unroll
+      for (int n0 = 0; n0 < NF; n0 += G) {
+        Frag2 bw[G];
+#pragma unroll
+        for (int i = 0; i < G; ++i) {
+          split_b(bw[i], *reinterpret_cast<const float2*>(sW2T + (8 * (n0 + i) + g) * 8 + 2 * c));
+          gz[n0 + i][0] = gz[n0 + i][1] = gz[n0 + i][2] = gz[n0 + i][3] = 0.f;
+        }
+#pragma unroll
+        for (int term = 0; term < 3; ++term)
+#pragma unroll
+          for (int i = 0; i < G; ++i) mma_term(gz[n0 + i], au, bw[i], term);
+      }
+    }
+#pragma unroll
+    for (int nf = 0; nf < NF; ++nf) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) gz[nf][e] *= (1.f - h2[nf][e] * h2[nf][e]);
+      float* p0 = sPB + (8 * nf + 2 * c) * LDT;   // GZ2^T plane for gW1
+      p0[rA] = gz[nf][0]; p0[LDT + rA] = gz[nf][1]; p0[rB] = gz[nf][2]; p0[LDT + rB] = gz[nf][3];
+    }
+
+    // ---- gz1 = (GZ2 W1) * (1 - h1^2) --------------------------------------------------------------
+    {
+      float gh[NF][4];
+#pragma unroll
+      for (int nf = 0; nf < NF; ++nf) gh[nf][0] = gh[nf][1] = gh[nf][2] = gh[nf][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < NF; ++ks) {
+        Frag4 ag;
+        split_a(ag, gz[ks]);
+#pragma unroll
+        for (int n0 = 0; n0 < NF; n0 += G) {
+          Frag2 bw[G];
+#pragma unroll
+          for (int i = 0; i < G; ++i)
+            split_b(bw[i], *reinterpret_cast<const float2*>(sW1T + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c));
+#pragma unroll
+          for (int term = 0; term < 3; ++term)
+#pragma unroll
+            for (int i = 0; i < G; ++i) mma_term(gh[n0 + i], ag, bw[i], term);
+        }
+      }
+#pragma unroll
+      for (int nf = 0; nf < NF; ++nf)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) gz[nf][e] = gh[nf][e] * (1.f - h1[nf][e] * h1[nf][e]);
+    }
+    __syncthreads();   // (A) H1^T, GZ2^T, U^T of all warps visible
+
+    // ---- gW1[o][i] += sum_t GZ2[t][o] H1[t][i]   (+ gb1 through a ones column) -----------------
+#pragma unroll 2
+    for (int k8 = 0; k8 < TSR; k8 += 8) {
+      const float2 a0 = *reinterpret_cast<const float2*>(sPB + (16 * mt1 + g) * LDT + k8 + 2 * c);
+      const float2 a1 = *reinterpret_cast<const float2*>(sPB + (16 * mt1 + g + 8) * LDT + k8 + 2 * c);
+      Frag4 ag;
+      split_a(ag, a0.x, a0.y, a1.x, a1.y);
+      Frag2 bh[NW1];
+#pragma unroll
+      for (int j = 0; j < NW1; ++j)
+        split_b(bh[j], *reinterpret_cast<const float2*>(sPA + (8 * (nf1 + j) + g) * LDT + k8 + 2 * c));
+#pragma unroll
+      for (int term = 0; term < 3; ++term)
+#pragma unroll
+        for (int j = 0; j < NW1; ++j) mma_term(accW1[j], ag, bh[j], term);
+      if (own_b1) {   // warp-uniform; B = ones in column 0: hi = 1, lo = 0
+        const uint32_t one = g == 0 ? 0x3f800000u : 0u;
+        const uint32_t bo[2] = {one, one};
+        mma_tf32(accB1, ag.lo, bo);
+        mma_tf32(accB1, ag.hi, bo);
+      }
+    }
+    __syncthreads();   // (B) planes free
+    // GZ1^T -> PB, H2^T -> PA
+#pragma unroll
+    for (int nf = 0; nf < NF; ++nf) {
+      float* p0 = sPB + (8 * nf + 2 * c) * LDT;
+      p0[rA] = gz[nf][0]; p0[LDT + rA] = gz[nf][1]; p0[rB] = gz[nf][2]; p0[LDT + rB] = gz[nf][3];
+      float* q0 = sPA + (8 * nf + 2 * c) * LDT;
+      q0[rA] = h2[nf][0]; q0[LDT + rA] = h2[nf][1]; q0[rB] = h2[nf][2]; q0[LDT + rB] = h2[nf][3];
+    }
+    __syncthreads();   // (C)
+    // ---- gW0[o][i] += sum_t GZ1[t][o] X[t][i] (column n of X is ones: gb0);  gW2[j][f] += sum_t U[t][j] H2[t][f]
+#pragma unroll
+    for (int s = 0; s < NW0; ++s) {
+      const int f0 = warp + 8 * s;
+      if (f0 < MT * NPK) {   // warp-uniform
+        const int mt = f0 / NPK, nf = f0 - mt * NPK;
+#pragma unroll 4
+        for (int k8 = 0; k8 < TSR; k8 += 8) {
+          const float2 a0 = *reinterpret_cast<const float2*>(sPB + (16 * mt + g) * LDT + k8 + 2 * c);
+          const float2 a1 = *reinterpret_cast<const float2*>(sPB + (16 * mt + g + 8) * LDT + k8 + 2 * c);
+          Frag4 ag;
+          Frag2 bx;
+          split_a(ag, a0.x, a0.y, a1.x, a1.y);
+          split_b(bx, *reinterpret_cast<const float2*>(sXT + (8 * nf + g) * LDT + k8 + 2 * c));
+#pragma unroll
+          for (int term = 0; term < 3; ++term) mma_term(accW0[s], ag, bx, term);
+        }
+      }
+    }
+    if (warp < NF) {
+#pragma unroll 4
+      for (int k8 = 0; k8 < TSR; k8 += 8) {
+        const float2 a0 = *reinterpret_cast<const float2*>(sUT + g * LDT + k8 + 2 * c);
+        const float2 a1 = *reinterpret_cast<const float2*>(sUT + (g + 8) * LDT + k8 + 2 * c);
+        Frag4 au;
+        Frag2 bh;
+        split_a(au, a0.x, a0.y, a1.x, a1.y);
+        split_b(bh, *reinterpret_cast<const float2*>(sPA + (8 * warp + g) * LDT + k8 + 2 * c));
+#pragma unroll
+        for (int term = 0; term < 3; ++term) mma_term(accW2, au, bh, term);
+      }
+    }
+    if (warp < m) {   // gb2[j] += sum_t U[t][j], j = warp (m <= 8)
+      const float4 v = *reinterpret_cast<const float4*>(sUT + warp * LDT + 4 * lane);
+      float s = (v.x + v.y) + (v.z + v.w);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      gb2acc += s;
+    }
+    __syncthreads();   // (D) X, planes, U^T free for the next tile
+  }
+
+  // ---- per-CTA partial gradient: every element has exactly one owner -> flat [d] staging ---------
+  float* sG = sPA;
+  for (int i = tid; i < F.d; i += NTHREADS) sG[i] = 0.f;
+  __syncthreads();
+  const int h1n = F.h1, h2n = F.h2;
+#pragma unroll
+  for (int j = 0; j < NW1; ++j)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int o = 16 * mt1 + g + (e >> 1) * 8, i = 8 * (nf1 + j) + 2 * c + (e & 1);
+      if (o < h2n && i < h1n) sG[F.oW1 + o * h1n + i] = accW1[j][e];
+    }
+  if (own_b1 && c == 0) {
+    const int o = 16 * mt1 + g;
+    if (o < h2n) sG[F.ob1 + o] = accB1[0];
+    if (o + 8 < h2n) sG[F.ob1 + o + 8] = accB1[2];
+  }
+#pragma unroll
+  for (int s = 0; s < NW0; ++s) {
+    const int f0 = warp + 8 * s;
+    if (f0 < MT * NPK) {
+      const int mt = f0 / NPK, nf = f0 - mt * NPK;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int o = 16 * mt + g + (e >> 1) * 8, i = 8 * nf + 2 * c + (e & 1);
+        if (o < h1n) {
+          if (i < n) sG[F.oW0 + o * n + i] = accW0[s][e];
+          else if (i == n) sG[F.ob0 + o] = accW0[s][e];
+        }
+      }
+    }
+  }
+  if (warp < NF && g < m) {
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int f = 8 * warp + 2 * c + e;
+      if (f < h2n) sG[F.oW2 + g * h2n + f] = accW2[e];
+    }
+  }
+  if (warp < m && lane == 0) sG[F.ob2 + warp] = gb2acc;   // log_std block: filled by the finalize kernel
+  __syncthreads();
+  float* out = a.partials + (size_t)blockIdx.x * a.dstride;
+  for (int i = tid; i < F.d; i += NTHREADS) out[i] = sG[i];
+}
+
+}  // namespace rows
+}  // namespace pol

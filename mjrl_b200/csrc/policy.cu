@@ -703,6 +703,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
 
 }  // namespace pol
 
+#include "fvp_rows.cuh"
+
 // =========================================================================================
 // Second-stage reductions (fixed order => bit-reproducible run to run)
 // =========================================================================================
@@ -804,12 +806,63 @@ int launch_slots(mjrl_ctx* ctx, const Args& a, int slots, int grid, size_t smem,
   }
 }
 
+// FVP variant selection: "rows in registers" (fvp_rows.cuh) when the shape fits it, unless
+// MJRL_B200_FVP=tile asks for the shared-memory tile kernel.
+inline bool want_rows() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("MJRL_B200_FVP");
+    v = (e && e[0] == 't') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+template <int HP, int NPK>
+int launch_rows_one(mjrl_ctx* ctx, const Args& a, int grid, size_t smem, cudaStream_t s) {
+  auto kern = rows::fvp_rows_kernel<HP, NPK>;
+  static size_t attr = 0;   // the kernel also has a few static bytes: ask for what is needed, not the maximum
+  if (smem > attr) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    attr = smem;
+  }
+  kern<<<grid, NTHREADS, smem, s>>>(a);
+  return mjrl_check_launch("fvp_rows_kernel");
+}
+
+// returns -1 when the shape does not fit this variant
+inline int launch_fvp_rows(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
+  const int hmax = a.h1 > a.h2 ? a.h1 : a.h2;
+  if (!want_mma() || !want_rows() || hmax > 64 || a.m > 8 || a.n + 1 > 32) return -1;
+  const int HP = hmax <= 32 ? 32 : 64, NPK = (a.n + 1 + 7) / 8;
+  const Flat F(a.n, a.m, a.h1, a.h2);
+  const rows::RLayout L(HP, NPK, a.n);
+  const size_t smem = sizeof(float) * (size_t)L.total;
+  if (smem + 64 > (size_t)ctx->max_smem_optin || F.d > 2 * HP * rows::LDT) return -1;
+  const long long ntiles = (a.N + rows::TSR - 1) / rows::TSR;
+  int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
+  if (grid < 1) grid = 1;
+  *grid_out = grid;
+  a.dstride = (F.d + 31) & ~31;
+  a.partials = (float*)mjrl_scratch(ctx, sizeof(float) * (size_t)grid * a.dstride);
+  if (!a.partials) return MJRL_E_STATE;
+#define ROWS_CASE(H, K) if (HP == H && NPK == K) return launch_rows_one<H, K>(ctx, a, grid, smem, s)
+  ROWS_CASE(64, 1); ROWS_CASE(64, 2); ROWS_CASE(64, 3); ROWS_CASE(64, 4);
+  ROWS_CASE(32, 1); ROWS_CASE(32, 2); ROWS_CASE(32, 3); ROWS_CASE(32, 4);
+#undef ROWS_CASE
+  return -1;
+}
+
 template <int MODE>
 int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
   const int hmax = a.h1 > a.h2 ? a.h1 : a.h2;
   MJRL_REQUIRE(a.h1 > 0 && a.h2 > 0, MJRL_E_SHAPE, "policy: MLP kernels need two hidden layers");
   MJRL_REQUIRE(hmax <= 64, MJRL_E_SHAPE, "policy: hidden sizes (%d,%d) > 64 are not supported yet",
                a.h1, a.h2);
+  if constexpr (MODE == M_FVP) {
+    const int rc = launch_fvp_rows(ctx, a, grid_out, s);
+    if (rc >= 0) return rc;
+  }
   const int HP = hmax <= 32 ? 32 : 64;
   const Flat F(a.n, a.m, a.h1, a.h2);
   const bool bwd = MODE == M_GRAD || MODE == M_FVP;
