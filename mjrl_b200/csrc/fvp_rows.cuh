@@ -1,8 +1,11 @@
 // Fisher-vector product, "rows in registers" variant (included by policy.cu, namespace pol).
 //
 // Same math as mlp_kernel<.., M_FVP, ..> (npg_cg.py:55-74 replaced by the analytic Gauss-Newton
-// product), different dataflow.  A CTA tile is 128 timesteps; warp w owns rows 16w..16w+15 and keeps
-// the WHOLE forward / tangent / backward chain of those rows in registers:
+// product), different dataflow.  The CTA is two independent HALVES of 4 warps; a half walks its own
+// tiles of 64 timesteps and synchronises only with itself (named barriers), so the two warps that
+// share an SM sub-partition drift apart and one feeds the tensor pipe while the other is in an
+// epilogue or at a barrier.  Warp w of a half owns rows 16w..16w+15 of the half's tile and keeps the
+// WHOLE forward / tangent / backward chain of those rows in registers:
 //
 //   The C fragment of mma.m16n8k8 holds (row g, cols 2c,2c+1 | row g+8, cols 2c,2c+1).  Read as an
 //   A fragment with the k-slot map  slot c <-> col 2c,  slot c+4 <-> col 2c+1  it IS the next
@@ -21,21 +24,25 @@
 namespace pol {
 namespace rows {
 
-constexpr int TSR = 128;        // timesteps per CTA tile (8 warps x 16 rows)
+constexpr int TSR = 64;         // timesteps per half-CTA tile (4 warps x 16 rows)
 constexpr int LDT = TSR + 8;    // row stride of the transposed planes (= 8 mod 32)
+constexpr int HTHREADS = 128;   // threads of a half
 __host__ __device__ constexpr int ldx_of(int NP) { return ((NP + 8) % 16 == 8) ? NP + 8 : NP + 16; }
 
 struct RLayout {  // offsets in floats
   int NP, LDX, LDW;
   int X, XT, PA, PB, UT, XR, W0, V0, W1, V1, W1T, W2, V2, W2T, b0, vb0, b1, vb1, vb2, fisher, ishift, iden;
-  int total;
+  int half_stride, total;
   __host__ __device__ RLayout(int HP, int NPK, int n) {
     NP = 8 * NPK; LDX = ldx_of(NP); LDW = HP + 8;
     int o = 0;
     auto take = [&](int cnt) { int r = o; o += (cnt + 3) & ~3; return r; };
-    PA = take(HP * LDT); PB = take(HP * LDT);   // contiguous: reused as the [d] staging vector
+    // per-half regions (half 1 at + half_stride); PA|PB of half 0 double as the [d] staging vector
+    PA = take(HP * LDT); PB = take(HP * LDT);
     X = take(TSR * LDX); XT = take(NP * LDT); UT = take(16 * LDT);
     XR = take(2 * TSR * n);
+    half_stride = o;
+    o *= 2;
     W0 = take(HP * LDX); V0 = take(HP * LDX);
     W1 = take(HP * LDW); V1 = take(HP * LDW); W1T = take(HP * LDW);
     W2 = take(8 * LDW); V2 = take(8 * LDW); W2T = take(HP * 8);
@@ -65,32 +72,43 @@ __device__ __forceinline__ void mma_term(float (&acc)[4], const Frag4& a, const 
   mma_tf32(acc, term == 0 ? a.lo : a.hi, term == 1 ? b.lo : b.hi);
 }
 
+__device__ __forceinline__ void half_sync(int half) {
+  asm volatile("bar.sync %0, %1;" :: "r"(half + 1), "n"(HTHREADS) : "memory");
+}
+
 template <int HP, int NPK>
 __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
   constexpr int NF = HP / 8;          // 8-wide feature blocks of a hidden layer
   constexpr int MT = HP / 16;         // 16-row bands of a weight gradient
   constexpr int NP = 8 * NPK, LDX = ldx_of(NP), LDW = HP + 8;
-  constexpr int NW1 = MT * NF / 8;    // gW1 fragments per warp, all in one band
-  constexpr int NW0 = (MT * NPK + 7) / 8;
-  constexpr int G = NF < 4 ? NF : 4;  // n-blocks whose MMAs are interleaved term by term
+  constexpr int NW1 = MT * NF / 4;    // gW1 fragments per warp of a half, all in one band
+  constexpr int NW0 = (MT * NPK + 3) / 4;
+  constexpr int NW2 = (NF + 3) / 4;
+  constexpr int G = 2;                // n-blocks whose MMAs are interleaved term by term
   static_assert(NF % NW1 == 0 && NF % G == 0, "fragment ownership");
   extern __shared__ __align__(16) float sm[];
-  __shared__ uint64_t bar[2];
+  __shared__ uint64_t bar[2][2];
   if (a.stop_flag && *a.stop_flag) return;
 
   const RLayout L(HP, NPK, a.n);
   const Flat F(a.n, a.m, a.h1, a.h2);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, c = lane & 3;
+  const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, c = lane & 3;
+  const int half = tid >> 7, htid = tid & (HTHREADS - 1), hw = htid >> 5;   // half, thread / warp in half
   const int n = a.n, m = a.m;
-  float* sX = sm + L.X; float* sXT = sm + L.XT; float* sPA = sm + L.PA; float* sPB = sm + L.PB;
-  float* sUT = sm + L.UT; float* sXR = sm + L.XR;
+  float* hs = sm + (size_t)half * L.half_stride;
+  float* sX = hs + L.X; float* sXT = hs + L.XT; float* sPA = hs + L.PA; float* sPB = hs + L.PB;
+  float* sUT = hs + L.UT; float* sXR = hs + L.XR;
   const float* sW0 = sm + L.W0; const float* sV0 = sm + L.V0; const float* sW1 = sm + L.W1;
   const float* sV1 = sm + L.V1; const float* sW1T = sm + L.W1T; const float* sW2 = sm + L.W2;
   const float* sV2 = sm + L.V2; const float* sW2T = sm + L.W2T;
 
   // ---- one-time staging: zero everything, then weights in their natural [out][in] layout ------
   for (int i = tid; i < L.total; i += NTHREADS) sm[i] = 0.f;
-  if (tid == 0) { tma::mbar_init(&bar[0], 1); tma::mbar_init(&bar[1], 1); tma::mbar_init_fence(); }
+  if (tid == 0) {
+    tma::mbar_init(&bar[0][0], 1); tma::mbar_init(&bar[0][1], 1);
+    tma::mbar_init(&bar[1][0], 1); tma::mbar_init(&bar[1][1], 1);
+    tma::mbar_init_fence();
+  }
   __syncthreads();
   {
     const float* P = a.params; const float* V = a.vec;
@@ -128,52 +146,54 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
     }
   }
 
-  // persistent weight-gradient accumulators (C fragments, unique owner per element)
-  float accW1[NW1][4], accB1[4], accW0[NW0][4], accW2[4], gb2acc = 0.f;
+  // persistent weight-gradient accumulators (C fragments, unique owner per element within a half)
+  float accW1[NW1][4], accB1[4], accW0[NW0][4], accW2[NW2][4], gb2acc[2] = {0.f, 0.f};
 #pragma unroll
   for (int j = 0; j < NW1; ++j) accW1[j][0] = accW1[j][1] = accW1[j][2] = accW1[j][3] = 0.f;
 #pragma unroll
   for (int j = 0; j < NW0; ++j) accW0[j][0] = accW0[j][1] = accW0[j][2] = accW0[j][3] = 0.f;
+#pragma unroll
+  for (int j = 0; j < NW2; ++j) accW2[j][0] = accW2[j][1] = accW2[j][2] = accW2[j][3] = 0.f;
   accB1[0] = accB1[1] = accB1[2] = accB1[3] = 0.f;
-  accW2[0] = accW2[1] = accW2[2] = accW2[3] = 0.f;
-  const int mt1 = (warp * NW1) / NF, nf1 = (warp * NW1) % NF;   // gW1 band / first block of this warp
-  const bool own_b1 = nf1 == 0;                                   // this warp also sums the band's gb1
+  const int mt1 = (hw * NW1) / NF, nf1 = (hw * NW1) % NF;   // gW1 band / first block of this warp
+  const bool own_b1 = nf1 == 0;                               // this warp also sums the band's gb1
 
   const int ntiles = (int)((a.N + TSR - 1) / TSR);
   const int tile_elems = TSR * n;
   const bool base_ok = (reinterpret_cast<uintptr_t>(a.obs) & 15) == 0;
   auto tile_rows = [&](int tile) { return tile + 1 < ntiles ? TSR : (int)(a.N - (long long)tile * TSR); };
   auto bulk_ok = [&](int tile) { return base_ok && ((tile_rows(tile) * n) & 3) == 0; };
-  auto start_copy = [&](int tile, int buf) {  // one thread
+  auto start_copy = [&](int tile, int buf) {  // one thread of the half
     if (bulk_ok(tile)) {
       const uint32_t bytes = (uint32_t)(tile_rows(tile) * n) * 4u;
-      tma::mbar_expect(&bar[buf], bytes);
-      tma::bulk_g2s(sXR + (size_t)buf * tile_elems, a.obs + (long long)tile * tile_elems, bytes, &bar[buf]);
+      tma::mbar_expect(&bar[half][buf], bytes);
+      tma::bulk_g2s(sXR + (size_t)buf * tile_elems, a.obs + (long long)tile * tile_elems, bytes, &bar[half][buf]);
     }
   };
   __syncthreads();
-  if (tid == 0 && (int)blockIdx.x < ntiles) start_copy(blockIdx.x, 0);
+  const int tile_first = 2 * blockIdx.x + half, tile_step = 2 * gridDim.x;
+  if (htid == 0 && tile_first < ntiles) start_copy(tile_first, 0);
 
-  const int rA = 16 * warp + g, rB = rA + 8;   // this thread's two rows of the tile
+  const int rA = 16 * hw + g, rB = rA + 8;   // this thread's two rows of the half's tile
   int it = 0;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+  for (int tile = tile_first; tile < ntiles; tile += tile_step, ++it) {
     const int buf = it & 1;
     const long long t0 = (long long)tile * TSR;
     const int rows = tile_rows(tile);
-    if (tid == 0 && tile + (int)gridDim.x < ntiles) start_copy(tile + gridDim.x, buf ^ 1);
+    if (htid == 0 && tile + tile_step < ntiles) start_copy(tile + tile_step, buf ^ 1);
     // ---- P0: raw rows -> transformed X [t][k] and X^T [k][t], ones column at k = n ----------
     {
       float* raw = sXR + (size_t)buf * tile_elems;
       if (bulk_ok(tile)) {
-        tma::mbar_wait(&bar[buf], (it >> 1) & 1);
+        tma::mbar_wait(&bar[half][buf], (it >> 1) & 1);
       } else {
-        stream_rows<NTHREADS>(a.obs + t0 * n, rows * n, n, tid, [&](int r, int k, float v) { raw[r * n + k] = v; });
-        __syncthreads();
+        stream_rows<HTHREADS>(a.obs + t0 * n, rows * n, n, htid, [&](int r, int k, float v) { raw[r * n + k] = v; });
+        half_sync(half);
       }
       const int cnt = rows * n;
-      const int dq = NTHREADS / n, dr = NTHREADS - dq * n;
-      int r = tid / n, k = tid - r * n;
-      for (int i = tid; i < cnt; i += NTHREADS) {
+      const int dq = HTHREADS / n, dr = HTHREADS - dq * n;
+      int r = htid / n, k = htid - r * n;
+      for (int i = htid; i < cnt; i += HTHREADS) {
         const float v = (raw[i] - sm[L.ishift + k]) / sm[L.iden + k];
         sX[r * LDX + k] = v;
         sXT[k * LDT + r] = v;
@@ -181,16 +201,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         if (k >= n) { k -= n; ++r; }
       }
       if (rows < TSR)
-        for (int i = rows * n + tid; i < tile_elems; i += NTHREADS) {
+        for (int i = rows * n + htid; i < tile_elems; i += HTHREADS) {
           const int rr = i / n, kk = i - rr * n;
           sX[rr * LDX + kk] = 0.f; sXT[kk * LDT + rr] = 0.f;
         }
-      if (tid < TSR) {
-        const float one = tid < rows ? 1.f : 0.f;
-        sX[tid * LDX + n] = one; sXT[n * LDT + tid] = one;
+      if (htid < TSR) {
+        const float one = htid < rows ? 1.f : 0.f;
+        sX[htid * LDX + n] = one; sXT[n * LDT + htid] = one;
       }
     }
-    __syncthreads();
+    half_sync(half);
 
     // ---- layer 0: z1 = b0 + X W0^T, dz1 = vb0 + X V0^T ------------------------------------------
     float h1[NF][4], d1[NF][4];
@@ -370,7 +390,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
 #pragma unroll
         for (int e = 0; e < 4; ++e) gz[nf][e] = gh[nf][e] * (1.f - h1[nf][e] * h1[nf][e]);
     }
-    __syncthreads();   // (A) H1^T, GZ2^T, U^T of all warps visible
+    half_sync(half);   // (A) H1^T, GZ2^T, U^T of the half's warps visible
 
     // ---- gW1[o][i] += sum_t GZ2[t][o] H1[t][i]   (+ gb1 through a ones column) -----------------
 #pragma unroll 2
@@ -379,14 +399,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
       const float2 a1 = *reinterpret_cast<const float2*>(sPB + (16 * mt1 + g + 8) * LDT + k8 + 2 * c);
       Frag4 ag;
       split_a(ag, a0.x, a0.y, a1.x, a1.y);
-      Frag2 bh[NW1];
 #pragma unroll
-      for (int j = 0; j < NW1; ++j)
-        split_b(bh[j], *reinterpret_cast<const float2*>(sPA + (8 * (nf1 + j) + g) * LDT + k8 + 2 * c));
+      for (int j0 = 0; j0 < NW1; j0 += 4) {
+        Frag2 bh[4];
 #pragma unroll
-      for (int term = 0; term < 3; ++term)
+        for (int j = 0; j < 4; ++j)
+          if (j0 + j < NW1)
+            split_b(bh[j], *reinterpret_cast<const float2*>(sPA + (8 * (nf1 + j0 + j) + g) * LDT + k8 + 2 * c));
 #pragma unroll
-        for (int j = 0; j < NW1; ++j) mma_term(accW1[j], ag, bh[j], term);
+        for (int term = 0; term < 3; ++term)
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (j0 + j < NW1) mma_term(accW1[j0 + j], ag, bh[j], term);
+      }
       if (own_b1) {   // warp-uniform; B = ones in column 0: hi = 1, lo = 0
         const uint32_t one = g == 0 ? 0x3f800000u : 0u;
         const uint32_t bo[2] = {one, one};
@@ -394,7 +419,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         mma_tf32(accB1, ag.hi, bo);
       }
     }
-    __syncthreads();   // (B) planes free
+    half_sync(half);   // (B) planes free
     // GZ1^T -> PB, H2^T -> PA
 #pragma unroll
     for (int nf = 0; nf < NF; ++nf) {
@@ -403,11 +428,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
       float* q0 = sPA + (8 * nf + 2 * c) * LDT;
       q0[rA] = h2[nf][0]; q0[LDT + rA] = h2[nf][1]; q0[rB] = h2[nf][2]; q0[LDT + rB] = h2[nf][3];
     }
-    __syncthreads();   // (C)
+    half_sync(half);   // (C)
     // ---- gW0[o][i] += sum_t GZ1[t][o] X[t][i] (column n of X is ones: gb0);  gW2[j][f] += sum_t U[t][j] H2[t][f]
 #pragma unroll
     for (int s = 0; s < NW0; ++s) {
-      const int f0 = warp + 8 * s;
+      const int f0 = hw + 4 * s;
       if (f0 < MT * NPK) {   // warp-uniform
         const int mt = f0 / NPK, nf = f0 - mt * NPK;
 #pragma unroll 4
@@ -423,70 +448,89 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         }
       }
     }
-    if (warp < NF) {
+#pragma unroll
+    for (int s = 0; s < NW2; ++s) {
+      const int nf = hw + 4 * s;
+      if (nf < NF) {
 #pragma unroll 4
-      for (int k8 = 0; k8 < TSR; k8 += 8) {
-        const float2 a0 = *reinterpret_cast<const float2*>(sUT + g * LDT + k8 + 2 * c);
-        const float2 a1 = *reinterpret_cast<const float2*>(sUT + (g + 8) * LDT + k8 + 2 * c);
-        Frag4 au;
-        Frag2 bh;
-        split_a(au, a0.x, a0.y, a1.x, a1.y);
-        split_b(bh, *reinterpret_cast<const float2*>(sPA + (8 * warp + g) * LDT + k8 + 2 * c));
+        for (int k8 = 0; k8 < TSR; k8 += 8) {
+          const float2 a0 = *reinterpret_cast<const float2*>(sUT + g * LDT + k8 + 2 * c);
+          Frag4 au;   // rows 8..15 of U^T are zero: no load
+          Frag2 bh;
+          split_a(au, a0.x, a0.y, 0.f, 0.f);
+          split_b(bh, *reinterpret_cast<const float2*>(sPA + (8 * nf + g) * LDT + k8 + 2 * c));
 #pragma unroll
-        for (int term = 0; term < 3; ++term) mma_term(accW2, au, bh, term);
-      }
-    }
-    if (warp < m) {   // gb2[j] += sum_t U[t][j], j = warp (m <= 8)
-      const float4 v = *reinterpret_cast<const float4*>(sUT + warp * LDT + 4 * lane);
-      float s = (v.x + v.y) + (v.z + v.w);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      gb2acc += s;
-    }
-    __syncthreads();   // (D) X, planes, U^T free for the next tile
-  }
-
-  // ---- per-CTA partial gradient: every element has exactly one owner -> flat [d] staging ---------
-  float* sG = sPA;
-  for (int i = tid; i < F.d; i += NTHREADS) sG[i] = 0.f;
-  __syncthreads();
-  const int h1n = F.h1, h2n = F.h2;
-#pragma unroll
-  for (int j = 0; j < NW1; ++j)
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int o = 16 * mt1 + g + (e >> 1) * 8, i = 8 * (nf1 + j) + 2 * c + (e & 1);
-      if (o < h2n && i < h1n) sG[F.oW1 + o * h1n + i] = accW1[j][e];
-    }
-  if (own_b1 && c == 0) {
-    const int o = 16 * mt1 + g;
-    if (o < h2n) sG[F.ob1 + o] = accB1[0];
-    if (o + 8 < h2n) sG[F.ob1 + o + 8] = accB1[2];
-  }
-#pragma unroll
-  for (int s = 0; s < NW0; ++s) {
-    const int f0 = warp + 8 * s;
-    if (f0 < MT * NPK) {
-      const int mt = f0 / NPK, nf = f0 - mt * NPK;
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int o = 16 * mt + g + (e >> 1) * 8, i = 8 * nf + 2 * c + (e & 1);
-        if (o < h1n) {
-          if (i < n) sG[F.oW0 + o * n + i] = accW0[s][e];
-          else if (i == n) sG[F.ob0 + o] = accW0[s][e];
+          for (int term = 0; term < 3; ++term) mma_term(accW2[s], au, bh, term);
         }
       }
     }
-  }
-  if (warp < NF && g < m) {
 #pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int f = 8 * warp + 2 * c + e;
-      if (f < h2n) sG[F.oW2 + g * h2n + f] = accW2[e];
+    for (int s = 0; s < 2; ++s) {   // gb2[j] += sum_t U[t][j], j = hw + 4 s (m <= 8)
+      const int j = hw + 4 * s;
+      if (j < m) {
+        const float2 v = *reinterpret_cast<const float2*>(sUT + j * LDT + 2 * lane);
+        float sum = v.x + v.y;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        gb2acc[s] += sum;
+      }
     }
+    half_sync(half);   // (D) X, planes, U^T free for the half's next tile
   }
-  if (warp < m && lane == 0) sG[F.ob2 + warp] = gb2acc;   // log_std block: filled by the finalize kernel
+
+  // ---- per-CTA partial gradient: within a half every element has exactly one owner; half 0 writes
+  // the flat [d] staging vector, half 1 adds to it (fixed order) ------------------------------------
   __syncthreads();
+  float* sG = sm + L.PA;
+  for (int i = tid; i < F.d; i += NTHREADS) sG[i] = 0.f;
+  __syncthreads();
+  const int h1n = F.h1, h2n = F.h2;
+  for (int hh = 0; hh < 2; ++hh) {
+    if (half == hh) {
+#pragma unroll
+      for (int j = 0; j < NW1; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int o = 16 * mt1 + g + (e >> 1) * 8, i = 8 * (nf1 + j) + 2 * c + (e & 1);
+          if (o < h2n && i < h1n) sG[F.oW1 + o * h1n + i] += accW1[j][e];
+        }
+      if (own_b1 && c == 0) {
+        const int o = 16 * mt1 + g;
+        if (o < h2n) sG[F.ob1 + o] += accB1[0];
+        if (o + 8 < h2n) sG[F.ob1 + o + 8] += accB1[2];
+      }
+#pragma unroll
+      for (int s = 0; s < NW0; ++s) {
+        const int f0 = hw + 4 * s;
+        if (f0 < MT * NPK) {
+          const int mt = f0 / NPK, nf = f0 - mt * NPK;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int o = 16 * mt + g + (e >> 1) * 8, i = 8 * nf + 2 * c + (e & 1);
+            if (o < h1n) {
+              if (i < n) sG[F.oW0 + o * n + i] += accW0[s][e];
+              else if (i == n) sG[F.ob0 + o] += accW0[s][e];
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < NW2; ++s) {
+        const int nf = hw + 4 * s;
+        if (nf < NF && g < m) {
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int f = 8 * nf + 2 * c + e;
+            if (f < h2n) sG[F.oW2 + g * h2n + f] += accW2[s][e];
+          }
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+        if (hw + 4 * s < m && lane == 0) sG[F.ob2 + hw + 4 * s] += gb2acc[s];   // log_std block: finalize kernel
+    }
+    __syncthreads();
+  }
   float* out = a.partials + (size_t)blockIdx.x * a.dstride;
   for (int i = tid; i < F.d; i += NTHREADS) out[i] = sG[i];
 }

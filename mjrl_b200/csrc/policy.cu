@@ -839,7 +839,7 @@ inline int launch_fvp_rows(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s
   const rows::RLayout L(HP, NPK, a.n);
   const size_t smem = sizeof(float) * (size_t)L.total;
   if (smem + 64 > (size_t)ctx->max_smem_optin || F.d > 2 * HP * rows::LDT) return -1;
-  const long long ntiles = (a.N + rows::TSR - 1) / rows::TSR;
+  const long long ntiles = (a.N + 2 * rows::TSR - 1) / (2 * rows::TSR);   // a CTA walks two tiles at a time
   int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
   if (grid < 1) grid = 1;
   *grid_out = grid;
