@@ -31,7 +31,7 @@ __host__ __device__ constexpr int ldx_of(int NP) { return ((NP + 8) % 16 == 8) ?
 
 struct RLayout {  // offsets in floats
   int NP, LDX, LDW;
-  int X, XT, PA, PB, UT, XR, W0, V0, W1, V1, W1T, W2, V2, W2T, b0, vb0, b1, vb1, vb2, fisher, ishift, iden;
+  int X, XT, PA, PB, UT, XR, W0, V0, W1, V1, W2, V2, W2T, b0, vb0, b1, vb1, vb2, fisher, ishift, iden;
   int half_stride, total;
   __host__ __device__ RLayout(int HP, int NPK, int n) {
     NP = 8 * NPK; LDX = ldx_of(NP); LDW = HP + 8;
@@ -39,13 +39,14 @@ struct RLayout {  // offsets in floats
     auto take = [&](int cnt) { int r = o; o += (cnt + 3) & ~3; return r; };
     // per-half regions (half 1 at + half_stride); PA|PB of half 0 double as the [d] staging vector
     PA = take(HP * LDT); PB = take(HP * LDT);
-    X = take(TSR * LDX); XT = take(NP * LDT); UT = take(16 * LDT);
+    X = take(TSR * LDX); XT = take(NP * LDT); UT = take(8 * LDT);
     XR = take(2 * TSR * n);
     half_stride = o;
     o *= 2;
-    W0 = take(HP * LDX); V0 = take(HP * LDX);
-    W1 = take(HP * LDW); V1 = take(HP * LDW); W1T = take(HP * LDW);
-    W2 = take(8 * LDW); V2 = take(8 * LDW); W2T = take(HP * 8);
+    // weights: tf32 hi plane immediately followed by the lo plane (split once at staging)
+    W0 = take(2 * HP * LDX); V0 = take(2 * HP * LDX);
+    W1 = take(2 * HP * LDW); V1 = take(2 * HP * LDW);
+    W2 = take(2 * 8 * LDW); V2 = take(2 * 8 * LDW); W2T = take(2 * HP * 8);
     b0 = take(HP); vb0 = take(HP); b1 = take(HP); vb1 = take(HP); vb2 = take(8); fisher = take(8);
     ishift = take(NP); iden = take(NP);
     total = o;
@@ -56,6 +57,18 @@ struct RLayout {  // offsets in floats
 __device__ __forceinline__ void split_b(Frag2& f, const float2 v) {
   split_tf32(v.x, f.hi[0], f.lo[0]);
   split_tf32(v.y, f.hi[1], f.lo[1]);
+}
+// pre-split weight planes: hi pair at p, lo pair at p + plane
+__device__ __forceinline__ void load_b(Frag2& f, const float* __restrict__ p, int plane) {
+  const float2 h = *reinterpret_cast<const float2*>(p);
+  const float2 l = *reinterpret_cast<const float2*>(p + plane);
+  f.hi[0] = __float_as_uint(h.x); f.hi[1] = __float_as_uint(h.y);
+  f.lo[0] = __float_as_uint(l.x); f.lo[1] = __float_as_uint(l.y);
+}
+// same from two rows (k-slots c / c+4 in different rows of the plane): four 4-byte loads
+__device__ __forceinline__ void load_b_rows(Frag2& f, const float* __restrict__ p, int row_stride, int plane) {
+  f.hi[0] = __float_as_uint(p[0]); f.hi[1] = __float_as_uint(p[row_stride]);
+  f.lo[0] = __float_as_uint(p[plane]); f.lo[1] = __float_as_uint(p[plane + row_stride]);
 }
 // C fragment (or two adjacent pairs of rows g / g+8) -> A fragment under the slot map
 __device__ __forceinline__ void split_a(Frag4& f, float r0c0, float r0c1, float r1c0, float r1c1) {
@@ -99,8 +112,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
   float* sX = hs + L.X; float* sXT = hs + L.XT; float* sPA = hs + L.PA; float* sPB = hs + L.PB;
   float* sUT = hs + L.UT; float* sXR = hs + L.XR;
   const float* sW0 = sm + L.W0; const float* sV0 = sm + L.V0; const float* sW1 = sm + L.W1;
-  const float* sV1 = sm + L.V1; const float* sW1T = sm + L.W1T; const float* sW2 = sm + L.W2;
+  const float* sV1 = sm + L.V1; const float* sW2 = sm + L.W2;
   const float* sV2 = sm + L.V2; const float* sW2T = sm + L.W2T;
+  constexpr int PL0 = HP * LDX, PL1 = HP * LDW, PL2 = 8 * LDW, PL2T = HP * 8;   // hi -> lo plane distance
 
   // ---- one-time staging: zero everything, then weights in their natural [out][in] layout ------
   for (int i = tid; i < L.total; i += NTHREADS) sm[i] = 0.f;
@@ -112,24 +126,27 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
   __syncthreads();
   {
     const float* P = a.params; const float* V = a.vec;
+    auto put = [&](int at, int plane, float w) {
+      uint32_t hi, lo;
+      split_tf32(w, hi, lo);
+      sm[at] = __uint_as_float(hi); sm[at + plane] = __uint_as_float(lo);
+    };
     for (int i = tid; i < F.h1 * n; i += NTHREADS) {
       const int o = i / n, k = i - o * n;
-      sm[L.W0 + o * LDX + k] = __ldg(P + F.oW0 + i);
-      sm[L.V0 + o * LDX + k] = __ldg(V + F.oW0 + i);
+      put(L.W0 + o * LDX + k, PL0, __ldg(P + F.oW0 + i));
+      put(L.V0 + o * LDX + k, PL0, __ldg(V + F.oW0 + i));
     }
     for (int i = tid; i < F.h2 * F.h1; i += NTHREADS) {
       const int o = i / F.h1, k = i - o * F.h1;
-      const float w = __ldg(P + F.oW1 + i);
-      sm[L.W1 + o * LDW + k] = w;
-      sm[L.W1T + k * LDW + o] = w;
-      sm[L.V1 + o * LDW + k] = __ldg(V + F.oW1 + i);
+      put(L.W1 + o * LDW + k, PL1, __ldg(P + F.oW1 + i));
+      put(L.V1 + o * LDW + k, PL1, __ldg(V + F.oW1 + i));
     }
     for (int i = tid; i < m * F.h2; i += NTHREADS) {
       const int j = i / F.h2, k = i - j * F.h2;
       const float w = __ldg(P + F.oW2 + i);
-      sm[L.W2 + j * LDW + k] = w;
-      sm[L.W2T + k * 8 + j] = w;
-      sm[L.V2 + j * LDW + k] = __ldg(V + F.oW2 + i);
+      put(L.W2 + j * LDW + k, PL2, w);
+      put(L.W2T + k * 8 + j, PL2T, w);
+      put(L.V2 + j * LDW + k, PL2, __ldg(V + F.oW2 + i));
     }
     for (int i = tid; i < F.h1; i += NTHREADS) { sm[L.b0 + i] = __ldg(P + F.ob0 + i); sm[L.vb0 + i] = __ldg(V + F.ob0 + i); }
     for (int i = tid; i < F.h2; i += NTHREADS) { sm[L.b1 + i] = __ldg(P + F.ob1 + i); sm[L.vb1 + i] = __ldg(V + F.ob1 + i); }
@@ -232,8 +249,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         Frag2 bw[G], bv[G];
 #pragma unroll
         for (int i = 0; i < G; ++i) {
-          split_b(bw[i], *reinterpret_cast<const float2*>(sW0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c));
-          split_b(bv[i], *reinterpret_cast<const float2*>(sV0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c));
+          load_b(bw[i], sW0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c, PL0);
+          load_b(bv[i], sV0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c, PL0);
         }
 #pragma unroll
         for (int term = 0; term < 3; ++term) {
@@ -278,8 +295,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         Frag2 bw[G], bv[G];
 #pragma unroll
         for (int i = 0; i < G; ++i) {
-          split_b(bw[i], *reinterpret_cast<const float2*>(sW1 + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c));
-          split_b(bv[i], *reinterpret_cast<const float2*>(sV1 + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c));
+          load_b(bw[i], sW1 + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c, PL1);
+          load_b(bv[i], sV1 + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c, PL1);
         }
 #pragma unroll
         for (int term = 0; term < 3; ++term) {
@@ -316,8 +333,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         Frag2 bw, bv;
         split_a(ah, h2[ks]);
         split_a(ad, d2[ks]);
-        split_b(bw, *reinterpret_cast<const float2*>(sW2 + g * LDW + 8 * ks + 2 * c));
-        split_b(bv, *reinterpret_cast<const float2*>(sV2 + g * LDW + 8 * ks + 2 * c));
+        load_b(bw, sW2 + g * LDW + 8 * ks + 2 * c, PL2);
+        load_b(bv, sV2 + g * LDW + 8 * ks + 2 * c, PL2);
 #pragma unroll
         for (int term = 0; term < 3; ++term) {
           mma_term(uu[ks & 1][0], ah, bv, term);
@@ -347,7 +364,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         Frag2 bw[G];
 #pragma unroll
         for (int i = 0; i < G; ++i) {
-          split_b(bw[i], *reinterpret_cast<const float2*>(sW2T + (8 * (n0 + i) + g) * 8 + 2 * c));
+          load_b(bw[i], sW2T + (8 * (n0 + i) + g) * 8 + 2 * c, PL2T);
           gz[n0 + i][0] = gz[n0 + i][1] = gz[n0 + i][2] = gz[n0 + i][3] = 0.f;
         }
 #pragma unroll
@@ -378,7 +395,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
           Frag2 bw[G];
 #pragma unroll
           for (int i = 0; i < G; ++i)
-            split_b(bw[i], *reinterpret_cast<const float2*>(sW1T + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c));
+            load_b_rows(bw[i], sW1 + (8 * ks + 2 * c) * LDW + 8 * (n0 + i) + g, LDW, PL1);   // B[k = o][n = i] = W1[o][i]
 #pragma unroll
           for (int term = 0; term < 3; ++term)
 #pragma unroll
