@@ -179,6 +179,16 @@ int mjrl_policy_grad(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* p
 int mjrl_policy_fvp(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
                     const float* obs, int64_t N, const float* vec, double* fvp_sum,
                     const int32_t* stop_flag, void* stream);
+/* The same product with the forward activations of the (fixed) policy kept in HBM between calls:
+ * inside one CG solve (cg_solve.py:10-20 calls the operator with the SAME parameters and obs every
+ * iteration, npg_cg.py:103-106) only `vec` changes, so tanh layers need computing once.
+ * cache: device fp32 [mjrl_policy_fvp_cache_count(...)] (0 = this shape has no cached variant: pass
+ * cache_mode 0).  cache_mode 1 = compute and fill, 2 = use (caller guarantees params/obs/N are
+ * those of the filling call), 0 = plain mjrl_policy_fvp.  Results are bit-identical in all modes. */
+int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N);
+int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                           const float* obs, int64_t N, const float* vec, double* fvp_sum,
+                           const int32_t* stop_flag, float* cache, int32_t cache_mode, void* stream);
 
 /* ---- (d) conjugate gradient on device: mjrl/utils/cg_solve.py:3-22 ------------------- */
 /* CG state: caller-allocated DEVICE arrays.  x, r, p, z are fp64 [d] (z is the operator

@@ -37,7 +37,7 @@ def load():
     lib.mjrl_last_error.restype = ctypes.c_char_p
     for name in declared_symbols():
         fn = getattr(lib, name)  # raises AttributeError if a declared symbol is not exported
-        if name.endswith("_param_count"):
+        if name.endswith("_count"):   # size queries return int64, not a status
             fn.restype = ctypes.c_int64
         elif name != "mjrl_last_error":
             fn.restype = ctypes.c_int
@@ -96,6 +96,7 @@ class Context:
 # kernels each entry point launches (csrc/*.cu), for the launch count bench.py reports
 KERNELS_PER_CALL = {"mjrl_moments": 4, "mjrl_path_return_stats": 2, "mjrl_linbase_gram": 2,
                     "mjrl_policy_eval": 2, "mjrl_policy_grad": 3, "mjrl_policy_fvp": 2,
+                    "mjrl_policy_fvp_cached": 2,
                     "mjrl_policy_act": 2, "mjrl_mlpbase_features": 2, "mjrl_mlpbase_sqerr": 2}
 
 _ctx = {}

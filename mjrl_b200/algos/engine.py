@@ -10,6 +10,7 @@ Multi-GPU: every rank owns whole paths; `dist` (torch.distributed, NCCL) all-red
 small fp64 vectors (gradient+surrogate, each FVP, two scalars) -- SURVEY.md section 8(e).
 """
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -70,6 +71,7 @@ class UpdateEngine:
         self.mom = f64(4)
         self.new_params = torch.zeros(d, dtype=torch.float32, device=dev)
         self.launches = 0  # kernels launched by this engine (bench's gpu_launches)
+        self._cache = None  # forward activations shared by the FVPs of one CG solve
 
     # ------------------------------------------------------------------ building blocks
     def whiten(self, adv64, eps=1e-6, scale=1.0, N_global=None):
@@ -114,10 +116,30 @@ class UpdateEngine:
             self.grad[:d] += tgt[:d]   # demo term: only the gradient, not the surrogate (dapg.py:93,98)
         return self.grad
 
-    def fvp(self, params, obs, vec32, out64):
-        self.ctx.call("mjrl_policy_fvp", self.dv.desc_ref(), ptr(params), ptr(obs), c_i64(obs.shape[0]),
-                      ptr(vec32), ptr(out64), ptr(self.cg_flags), stream_ptr())
+    def fvp(self, params, obs, vec32, out64, cache_mode=0):
+        """Fisher-vector product sum over obs.  cache_mode 1 / 2: fill / reuse the forward
+        activations of `params` on `obs` (same tensors in both calls -- one CG solve)."""
+        cache = self._fvp_cache(obs.shape[0]) if cache_mode else None
+        if cache is None:
+            cache_mode = 0
+        self.ctx.call("mjrl_policy_fvp_cached", self.dv.desc_ref(), ptr(params), ptr(obs),
+                      c_i64(obs.shape[0]), ptr(vec32), ptr(out64), ptr(self.cg_flags), ptr(cache),
+                      c_int(cache_mode), stream_ptr())
         self.launches += 2
+
+    def _fvp_cache(self, N):
+        """Device buffer for the cached-activation FVP (None when the kernel variant that uses it
+        does not take this policy shape, or MJRL_B200_FVP_CACHE=0)."""
+        if os.environ.get("MJRL_B200_FVP_CACHE", "1") == "0":
+            return None
+        lib = _lib.load()
+        cnt = int(lib.mjrl_policy_fvp_cache_count(self.ctx.h, self.dv.desc_ref(), c_i64(N)))
+        if cnt <= 0:
+            return None
+        if self._cache is None or self._cache.numel() < cnt:
+            self._cache = None   # release before growing
+            self._cache = torch.empty(cnt, dtype=torch.float32, device=self.device)
+        return self._cache
 
     def cg_solve(self, params, obs, g_scale, N_global, iters, damping, tol=1e-10, trace=None,
                  subsample=None):
@@ -126,10 +148,13 @@ class UpdateEngine:
         self.ctx.call("mjrl_cg_init", ctypes.byref(self.cg), c_i64(d), ptr(self.grad), c_double(g_scale),
                       stream_ptr())
         self.launches += 1
-        for _ in range(iters):
+        for k in range(iters):
             o = obs if subsample is None else subsample()
             cnt = N_global if subsample is None else self.dist.global_count(o.shape[0], self.device)
-            self.fvp(params, o, self.cg_p32, self.cg_z)
+            # params and obs are fixed across the iterations of one solve (unless the operator
+            # subsamples): the first product fills the activation cache, the others reuse it
+            mode = 0 if subsample is not None else (1 if k == 0 else 2)
+            self.fvp(params, o, self.cg_p32, self.cg_z, cache_mode=mode)
             self.dist.allreduce(self.cg_z)
             self.ctx.call("mjrl_cg_update", ctypes.byref(self.cg), c_i64(d), c_double(1.0 / cnt),
                           c_double(damping), c_double(tol), stream_ptr())

@@ -89,7 +89,17 @@ __device__ __forceinline__ void half_sync(int half) {
   asm volatile("bar.sync %0, %1;" :: "r"(half + 1), "n"(HTHREADS) : "memory");
 }
 
-template <int HP, int NPK>
+// float2 slots of the activation cache per (tile, warp): [layer 0/1][block nf][row g / g+8][lane]
+__device__ __forceinline__ float2 ld_cache(const float2* p) {
+  float2 v;
+  asm("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+  return v;
+}
+
+// USE_CACHE = false: compute h1, h2 (and store them in fragment order when a.cache is set);
+// USE_CACHE = true : read them back -- during CG the policy is fixed, only the vector changes, so the
+// forward products and their tanh are done once per update instead of once per iteration.
+template <int HP, int NPK, bool USE_CACHE>
 __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
   constexpr int NF = HP / 8;          // 8-wide feature blocks of a hidden layer
   constexpr int MT = HP / 16;         // 16-row bands of a weight gradient
@@ -238,6 +248,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
       h1[nf][0] = b.x; h1[nf][1] = b.y; h1[nf][2] = b.x; h1[nf][3] = b.y;
       d1[nf][0] = vb.x; d1[nf][1] = vb.y; d1[nf][2] = vb.x; d1[nf][3] = vb.y;
     }
+    // this warp's slice of the activation cache
+    float2* cslot = reinterpret_cast<float2*>(a.cache) + ((size_t)tile * 4 + hw) * (4 * NF * 32) + lane;
+    if (USE_CACHE) {
+#pragma unroll
+      for (int nf = 0; nf < NF; ++nf) {
+        const float2 lo = ld_cache(cslot + (2 * nf) * 32), hi = ld_cache(cslot + (2 * nf + 1) * 32);
+        h1[nf][0] = lo.x; h1[nf][1] = lo.y; h1[nf][2] = hi.x; h1[nf][3] = hi.y;
+      }
+    }
 #pragma unroll
     for (int ks = 0; ks < NPK; ++ks) {
       const float2 xa = *reinterpret_cast<const float2*>(sX + rA * LDX + 8 * ks + 2 * c);
@@ -249,13 +268,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         Frag2 bw[G], bv[G];
 #pragma unroll
         for (int i = 0; i < G; ++i) {
-          load_b(bw[i], sW0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c, PL0);
+          if (!USE_CACHE) load_b(bw[i], sW0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c, PL0);
           load_b(bv[i], sV0 + (8 * (n0 + i) + g) * LDX + 8 * ks + 2 * c, PL0);
         }
 #pragma unroll
         for (int term = 0; term < 3; ++term) {
+          if (!USE_CACHE) {
 #pragma unroll
-          for (int i = 0; i < G; ++i) mma_term(h1[n0 + i], ax, bw[i], term);
+            for (int i = 0; i < G; ++i) mma_term(h1[n0 + i], ax, bw[i], term);
+          }
 #pragma unroll
           for (int i = 0; i < G; ++i) mma_term(d1[n0 + i], ax, bv[i], term);
         }
@@ -265,10 +286,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
     for (int nf = 0; nf < NF; ++nf)
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
-        const float h = tanh_fast(h1[nf][e]);
+        const float h = USE_CACHE ? h1[nf][e] : tanh_fast(h1[nf][e]);
         h1[nf][e] = h;
         d1[nf][e] = (1.f - h * h) * d1[nf][e];
       }
+    if (!USE_CACHE && a.cache) {
+#pragma unroll
+      for (int nf = 0; nf < NF; ++nf) {
+        cslot[(2 * nf) * 32] = make_float2(h1[nf][0], h1[nf][1]);
+        cslot[(2 * nf + 1) * 32] = make_float2(h1[nf][2], h1[nf][3]);
+      }
+    }
     // H1^T plane for gW1
 #pragma unroll
     for (int nf = 0; nf < NF; ++nf) {
@@ -285,6 +313,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
       h2[nf][0] = b.x; h2[nf][1] = b.y; h2[nf][2] = b.x; h2[nf][3] = b.y;
       d2[nf][0] = vb.x; d2[nf][1] = vb.y; d2[nf][2] = vb.x; d2[nf][3] = vb.y;
     }
+    if (USE_CACHE) {   // issued here, consumed after the layer's MMAs
+#pragma unroll
+      for (int nf = 0; nf < NF; ++nf) {
+        const float2 lo = ld_cache(cslot + (2 * (NF + nf)) * 32), hi = ld_cache(cslot + (2 * (NF + nf) + 1) * 32);
+        h2[nf][0] = lo.x; h2[nf][1] = lo.y; h2[nf][2] = hi.x; h2[nf][3] = hi.y;
+      }
+    }
 #pragma unroll
     for (int ks = 0; ks < NF; ++ks) {
       Frag4 ah, ad;
@@ -300,8 +335,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
         }
 #pragma unroll
         for (int term = 0; term < 3; ++term) {
+          if (!USE_CACHE) {
 #pragma unroll
-          for (int i = 0; i < G; ++i) mma_term(h2[n0 + i], ah, bw[i], term);
+            for (int i = 0; i < G; ++i) mma_term(h2[n0 + i], ah, bw[i], term);
+          }
 #pragma unroll
           for (int i = 0; i < G; ++i) mma_term(d2[n0 + i], ah, bv[i], term);
 #pragma unroll
@@ -313,10 +350,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_rows_kernel(const Args a) {
     for (int nf = 0; nf < NF; ++nf)
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
-        const float h = tanh_fast(h2[nf][e]);
+        const float h = USE_CACHE ? h2[nf][e] : tanh_fast(h2[nf][e]);
         h2[nf][e] = h;
         d2[nf][e] = (1.f - h * h) * d2[nf][e];
       }
+    if (!USE_CACHE && a.cache) {
+#pragma unroll
+      for (int nf = 0; nf < NF; ++nf) {
+        cslot[(2 * (NF + nf)) * 32] = make_float2(h2[nf][0], h2[nf][1]);
+        cslot[(2 * (NF + nf) + 1) * 32] = make_float2(h2[nf][2], h2[nf][3]);
+      }
+    }
 
     // ---- head tangent: dy = H2 V2^T + D2 W2^T;  u = fisher * (dy + vb2), zero past N -----------
     float u[4];

@@ -42,6 +42,8 @@ struct Args {
   long long N;
   int n, m, h1, h2, dstride;
   int prefetch;   // 1: double-buffered obs/act staging (Layout::XR/AR present)
+  float* cache;   // FVP rows kernel: forward activations in fragment order (fill or use), may be null
+  int cache_mode; // 0 none, 1 fill, 2 use
 };
 
 // Shared-memory carve-up (offsets in floats), identical on host and device.
@@ -817,9 +819,9 @@ inline bool want_rows() {
   return v == 1;
 }
 
-template <int HP, int NPK>
+template <int HP, int NPK, bool USE_CACHE>
 int launch_rows_one(mjrl_ctx* ctx, const Args& a, int grid, size_t smem, cudaStream_t s) {
-  auto kern = rows::fvp_rows_kernel<HP, NPK>;
+  auto kern = rows::fvp_rows_kernel<HP, NPK, USE_CACHE>;
   static size_t attr = 0;   // the kernel also has a few static bytes: ask for what is needed, not the maximum
   if (smem > attr) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -830,15 +832,25 @@ int launch_rows_one(mjrl_ctx* ctx, const Args& a, int grid, size_t smem, cudaStr
   return mjrl_check_launch("fvp_rows_kernel");
 }
 
+// does the rows variant take this shape?  (HP, NPK, shared memory)
+inline bool rows_fits(const mjrl_ctx* ctx, int n, int m, int h1, int h2, int* HP_out, int* NPK_out, size_t* smem_out) {
+  const int hmax = h1 > h2 ? h1 : h2;
+  if (!want_mma() || !want_rows() || h1 <= 0 || h2 <= 0 || hmax > 64 || m > 8 || n + 1 > 24) return false;
+  const int HP = hmax <= 32 ? 32 : 64, NPK = (n + 1 + 7) / 8;
+  const Flat F(n, m, h1, h2);
+  const rows::RLayout L(HP, NPK, n);
+  const size_t smem = sizeof(float) * (size_t)L.total;
+  if (smem + 64 > (size_t)ctx->max_smem_optin || F.d > 2 * HP * rows::LDT) return false;
+  *HP_out = HP; *NPK_out = NPK; *smem_out = smem;
+  return true;
+}
+
 // returns -1 when the shape does not fit this variant
 inline int launch_fvp_rows(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
-  const int hmax = a.h1 > a.h2 ? a.h1 : a.h2;
-  if (!want_mma() || !want_rows() || hmax > 64 || a.m > 8 || a.n + 1 > 32) return -1;
-  const int HP = hmax <= 32 ? 32 : 64, NPK = (a.n + 1 + 7) / 8;
+  int HP, NPK;
+  size_t smem;
+  if (!rows_fits(ctx, a.n, a.m, a.h1, a.h2, &HP, &NPK, &smem)) return -1;
   const Flat F(a.n, a.m, a.h1, a.h2);
-  const rows::RLayout L(HP, NPK, a.n);
-  const size_t smem = sizeof(float) * (size_t)L.total;
-  if (smem + 64 > (size_t)ctx->max_smem_optin || F.d > 2 * HP * rows::LDT) return -1;
   const long long ntiles = (a.N + 2 * rows::TSR - 1) / (2 * rows::TSR);   // a CTA walks two tiles at a time
   int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
   if (grid < 1) grid = 1;
@@ -846,9 +858,14 @@ inline int launch_fvp_rows(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s
   a.dstride = (F.d + 31) & ~31;
   a.partials = (float*)mjrl_scratch(ctx, sizeof(float) * (size_t)grid * a.dstride);
   if (!a.partials) return MJRL_E_STATE;
-#define ROWS_CASE(H, K) if (HP == H && NPK == K) return launch_rows_one<H, K>(ctx, a, grid, smem, s)
-  ROWS_CASE(64, 1); ROWS_CASE(64, 2); ROWS_CASE(64, 3); ROWS_CASE(64, 4);
-  ROWS_CASE(32, 1); ROWS_CASE(32, 2); ROWS_CASE(32, 3); ROWS_CASE(32, 4);
+  const bool use = a.cache && a.cache_mode == 2;
+  if (a.cache_mode != 1 && !use) a.cache = nullptr;
+#define ROWS_CASE(H, K)                                                                     \
+  if (HP == H && NPK == K)                                                                  \
+    return use ? launch_rows_one<H, K, true>(ctx, a, grid, smem, s)                         \
+               : launch_rows_one<H, K, false>(ctx, a, grid, smem, s)
+  ROWS_CASE(64, 1); ROWS_CASE(64, 2); ROWS_CASE(64, 3);
+  ROWS_CASE(32, 1); ROWS_CASE(32, 2); ROWS_CASE(32, 3);
 #undef ROWS_CASE
   return -1;
 }
@@ -1321,15 +1338,33 @@ int mjrl_policy_grad(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* p
   return mjrl_check_launch("policy_grad reduce");
 }
 
+int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N) {
+  if (!ctx || !desc || N <= 0) return 0;
+  int HP, NPK;
+  size_t smem;
+  if (!rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem)) return 0;
+  const int64_t ntiles = (N + rows::TSR - 1) / rows::TSR;
+  return ntiles * rows::TSR * 2 * HP;   // h1 and h2 of every (padded) timestep
+}
+
 int mjrl_policy_fvp(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
                     const float* obs, int64_t N, const float* vec, double* fvp_sum,
                     const int32_t* stop_flag, void* stream) {
+  return mjrl_policy_fvp_cached(ctx, desc, params, obs, N, vec, fvp_sum, stop_flag, nullptr, 0, stream);
+}
+
+int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                           const float* obs, int64_t N, const float* vec, double* fvp_sum,
+                           const int32_t* stop_flag, float* cache, int32_t cache_mode, void* stream) {
   int rc = check_desc(desc, "policy_fvp");
   if (rc) return rc;
   MJRL_REQUIRE(ctx && params && obs && vec && fvp_sum && N > 0, MJRL_E_ARG, "policy_fvp: bad argument");
+  MJRL_REQUIRE(cache_mode >= 0 && cache_mode <= 2 && (cache_mode == 0 || cache), MJRL_E_ARG,
+               "policy_fvp: cache_mode %d needs a cache buffer", cache_mode);
   Args a = {};
   fill_desc(a, desc);
   a.params = params; a.obs = obs; a.vec = vec; a.N = N; a.stop_flag = stop_flag;
+  a.cache = cache; a.cache_mode = cache_mode;
   int grid;
   cudaStream_t s = (cudaStream_t)stream;
   rc = launch_any<M_FVP>(ctx, a, &grid, s);

@@ -180,3 +180,38 @@ def test_batched_actions_philox():
     # exact parity on the mean with the single-observation API (gaussian_mlp.py:92-98)
     act, info = pol.get_action(obs[3].astype(np.float64))
     np.testing.assert_allclose(info["mean"], m1[3], rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("n,m,hidden,N", [(11, 3, (64, 64), 1000), (11, 3, (64, 64), 777), (17, 6, (32, 32), 300),
+                                           (8, 2, (64, 32), 129), (3, 1, (16, 16), 64)])
+def test_fvp_variants_agree_and_cache_is_bit_exact(n, m, hidden, N):
+    """FVP kernel variants over shapes that take the rows-in-registers kernel (hidden 64 / 32 / mixed,
+    ragged N, several obs widths) against the oracle's fp64 Gauss-Newton product, and the activation
+    cache: fill / use must reproduce the plain call bit for bit."""
+    import torch
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.algos.engine import UpdateEngine
+    from oracle import mjrl_oracle as O
+    rng = np.random.default_rng(n * 100 + N)
+    pol = MLP(EnvSpec(n, m, 100, 1), hidden_sizes=hidden, seed=5)
+    flat = pol.get_param_values()
+    flat = flat + 0.3 * rng.standard_normal(flat.shape).astype(np.float32)
+    pol.set_param_values(flat.copy(), True, True)
+    eng = UpdateEngine(pol)
+    dev = eng.device
+    obs = torch.from_numpy(rng.standard_normal((N, n)).astype(np.float32)).to(dev)
+    vec = torch.from_numpy(rng.standard_normal(flat.shape[0]).astype(np.float32) * 0.1).to(dev)
+    params = eng.dv.params("new")
+    outs = []
+    for mode in (0, 1, 2, 2):
+        out = torch.zeros(flat.shape[0], dtype=torch.float64, device=dev)
+        eng.cg_flags.zero_()
+        eng.fvp(params, obs, vec, out, cache_mode=mode)
+        outs.append(out.cpu().numpy())
+    for o in outs[1:]:
+        np.testing.assert_array_equal(o, outs[0])
+    # fp64 truth: sum_t J^T diag(2/(2 sigma^2 + 1e-8)) J v on the network block, N h(sigma) v on log_std
+    tp = O.TruthPolicy(O.GaussianPolicy(n, m, hidden, flat.copy()))
+    truth = N * tp.fvp(obs.cpu().numpy(), vec.cpu().numpy().astype(np.float64))
+    assert rel_l2(outs[0], truth) < 1e-5
