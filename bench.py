@@ -314,19 +314,27 @@ def run_b200(args):
     vec = torch.randn(d, dtype=torch.float32, device=dev) * 0.01
     out64 = torch.empty(d, dtype=torch.float64, device=dev)
     eng.cg_flags.zero_()
-    for _ in range(3):
-        eng.fvp(params, resident.obs, vec, out64)
-    reps = 20
-    fe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
-    torch.cuda.synchronize()
-    for a, bq in fe:
-        a.record(); eng.fvp(params, resident.obs, vec, out64); bq.record()
-    torch.cuda.synchronize()
-    fvp_ms = sorted(a.elapsed_time(bq) for a, bq in fe)[reps // 2]
+
+    def time_fvp(mode, reps=20):
+        for _ in range(3):
+            eng.fvp(params, resident.obs, vec, out64, cache_mode=mode)
+        fe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+        torch.cuda.synchronize()
+        for a, bq in fe:
+            a.record(); eng.fvp(params, resident.obs, vec, out64, cache_mode=mode); bq.record()
+        torch.cuda.synchronize()
+        return sorted(a.elapsed_time(bq) for a, bq in fe)[reps // 2]
+
+    fvp_fill_ms = time_fvp(1)          # computes the forward pass, fills the activation cache
+    cached = hidden and eng._fvp_cache(N) is not None
+    fvp_ms = time_fvp(2) if cached else fvp_fill_ms   # the other 9 of 10 products of an update
     hbm_peak, peak_src, sm_max = peaks()
     U = (n * hidden[0] + hidden[0] * hidden[1] + hidden[1] * m) if hidden else n * m
-    fvp_flop = 2.0 * (5 * U - 2 * n * (hidden[0] if hidden else 0)) if hidden else 2.0 * 2 * U
-    fvp_bytes = 4.0 * n                                   # FVP reads obs only
+    # MACs per timestep: forward U, tangent U + (h1 h2 + h2 m), backward data h1 h2 + h2 m, weight grads U
+    fill_flop = 2.0 * (5 * U - 2 * n * (hidden[0] if hidden else 0)) if hidden else 2.0 * 2 * U
+    fvp_flop = fill_flop - 2.0 * U if cached else fill_flop       # cached: the forward pass is read back
+    hp = (32 if max(hidden) <= 32 else 64) if hidden else 0
+    fvp_bytes = 4.0 * n + (4.0 * 2 * hp if cached else 0.0)       # obs (+ cached h1, h2)
     ach = N * fvp_bytes / (fvp_ms * 1e-3) / 1e9
     fma_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12          # nominal fp32 FMA peak at max clock
     bf16_peak = None
@@ -337,19 +345,28 @@ def run_b200(args):
     traffic = None
     tp = os.path.join(ROOT, "profiles", "r01_fvp_traffic.json")
     if os.path.exists(tp) and args.workload == "C3-hopper":
-        traffic = float(json.load(open(tp))["dram_bytes_per_timestep"]) * N
+        tj = json.load(open(tp))
+        key = "dram_bytes_per_timestep_cached" if cached else "dram_bytes_per_timestep"
+        if key in tj:
+            traffic = float(tj[key]) * N
     ach_tf = N * fvp_flop / (fvp_ms * 1e-3) / 1e12
     roofline = {
-        "kernel": "mlp_kernel<FVP> (analytic Fisher-vector product, %d per update)" % CG_ITERS,
+        "kernel": "fvp_rows_kernel<use cache> (analytic Fisher-vector product; %d of the %d products of an "
+                  "update, the first one also computes the forward pass and fills the cache)"
+                  % (CG_ITERS - 1, CG_ITERS) if cached else
+                  "FVP kernel (analytic Fisher-vector product, %d per update)" % CG_ITERS,
         "bound": "tensor", "achieved": ach_tf, "peak": tensor_peak, "unit": "TFLOP/s",
         "frac": ach_tf / tensor_peak, "peak_source": tensor_src + ", dense bf16 burst",
         "traffic": traffic, "traffic_source": "ncu dram bytes of one launch (profiles/r01_fvp_traffic.json) scaled by N",
-        "ms_per_launch": fvp_ms, "algorithmic_flop_per_timestep": fvp_flop,
+        "ms_per_launch": fvp_ms, "ms_per_launch_fill": fvp_fill_ms,
+        "algorithmic_flop_per_timestep": fvp_flop, "algorithmic_flop_per_timestep_fill": fill_flop,
         "algorithmic_bytes_per_timestep": fvp_bytes,
         "note": "compute bound (%.0f flop per byte, SURVEY F13/H3).  The pass must hold fp32 accuracy "
                 "(1e-4 parity gate, measured ~1e-6), so every algorithmic flop is 3 TF32 tensor flops "
-                "(a_hi*b_hi + a_hi*b_lo + a_lo*b_hi) on the mma.sync path; TF32 dense peak is half the "
-                "bf16 peak used as denominator here.  fp32_fma and hbm give the other two rooflines."
+                "(a_hi*b_hi + a_hi*b_lo + a_lo*b_hi) on mma.sync m16n8k8 (tcgen05 has no fp32-accurate "
+                "kind and its per-instruction issue floor at N=64 gives no gain here, DESIGN.md); ncu "
+                "shows the tensor pipe 62%% busy (profiles/).  TF32 dense peak is half the bf16 peak "
+                "used as denominator.  fp32_fma and hbm give the other two rooflines."
                 % (fvp_flop / fvp_bytes),
         "tensor_flops_issued_tflops": 3.0 * ach_tf,
         "fp32_fma": {"achieved_tflops": ach_tf, "peak_tflops_nominal": fma_peak,

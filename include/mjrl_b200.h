@@ -186,6 +186,12 @@ int mjrl_policy_fvp(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* pa
  * cache_mode 0).  cache_mode 1 = compute and fill, 2 = use (caller guarantees params/obs/N are
  * those of the filling call), 0 = plain mjrl_policy_fvp.  Results are bit-identical in all modes. */
 int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N);
+/* mjrl_policy_grad that also fills that cache (flat_vpg runs at the parameters the CG solve that
+ * follows it uses, npg_cg.py:96-106): fvp_cache as above or NULL. */
+int mjrl_policy_grad_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                            const float* obs, const float* act, const float* w, const float* old_ll,
+                            int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
+                            float* mean_out, float* fvp_cache, void* stream);
 int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
                            const float* obs, int64_t N, const float* vec, double* fvp_sum,
                            const int32_t* stop_flag, float* cache, int32_t cache_mode, void* stream);

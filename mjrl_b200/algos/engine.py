@@ -72,6 +72,7 @@ class UpdateEngine:
         self.new_params = torch.zeros(d, dtype=torch.float32, device=dev)
         self.launches = 0  # kernels launched by this engine (bench's gpu_launches)
         self._cache = None  # forward activations shared by the FVPs of one CG solve
+        self._cache_key = None
 
     # ------------------------------------------------------------------ building blocks
     def whiten(self, adv64, eps=1e-6, scale=1.0, N_global=None):
@@ -108,9 +109,12 @@ class UpdateEngine:
         N = obs.shape[0]
         tgt = self.grad if not accumulate else torch.empty_like(self.grad)
         ll_out, mean_out = cache if cache is not None else (None, None)
-        self.ctx.call("mjrl_policy_grad", self.dv.desc_ref(), ptr(params), ptr(obs), ptr(act), ptr(w),
+        # the pass computes h1, h2 of (params, obs) anyway: leave them for the FVPs of the CG solve
+        fcache = self._fvp_cache(N)
+        self.ctx.call("mjrl_policy_grad_cached", self.dv.desc_ref(), ptr(params), ptr(obs), ptr(act), ptr(w),
                       ptr(old_ll), c_i64(N), ptr(tgt), c_void_p(tgt.data_ptr() + 8 * d),
-                      ptr(ll_out), ptr(mean_out), stream_ptr())
+                      ptr(ll_out), ptr(mean_out), ptr(fcache), stream_ptr())
+        self._cache_key = self._key(params, obs) if fcache is not None else None
         self.launches += 3
         if accumulate:
             self.grad[:d] += tgt[:d]   # demo term: only the gradient, not the surrogate (dapg.py:93,98)
@@ -126,6 +130,11 @@ class UpdateEngine:
                       c_i64(obs.shape[0]), ptr(vec32), ptr(out64), ptr(self.cg_flags), ptr(cache),
                       c_int(cache_mode), stream_ptr())
         self.launches += 2
+
+    @staticmethod
+    def _key(params, obs):
+        """Identity + in-place-modification counters of the tensors a cache was filled from."""
+        return (params.data_ptr(), params._version, obs.data_ptr(), obs._version, obs.shape[0])
 
     def _fvp_cache(self, N):
         """Device buffer for the cached-activation FVP (None when the kernel variant that uses it
@@ -153,8 +162,15 @@ class UpdateEngine:
             cnt = N_global if subsample is None else self.dist.global_count(o.shape[0], self.device)
             # params and obs are fixed across the iterations of one solve (unless the operator
             # subsamples): the first product fills the activation cache, the others reuse it
-            mode = 0 if subsample is not None else (1 if k == 0 else 2)
+            if subsample is not None:
+                mode = 0
+            elif self._cache_key is not None and self._cache_key == self._key(params, o):
+                mode = 2      # filled by the gradient pass (or the first product) at these tensors
+            else:
+                mode = 1
             self.fvp(params, o, self.cg_p32, self.cg_z, cache_mode=mode)
+            if mode == 1 and self._cache is not None:
+                self._cache_key = self._key(params, o)
             self.dist.allreduce(self.cg_z)
             self.ctx.call("mjrl_cg_update", ctypes.byref(self.cg), c_i64(d), c_double(1.0 / cnt),
                           c_double(damping), c_double(tol), stream_ptr())

@@ -706,6 +706,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
 }  // namespace pol
 
 #include "fvp_rows.cuh"
+#include "pol_rows.cuh"
 
 // =========================================================================================
 // Second-stage reductions (fixed order => bit-reproducible run to run)
@@ -870,6 +871,47 @@ inline int launch_fvp_rows(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s
   return -1;
 }
 
+template <int HP, int NPK, int MODE>
+int launch_polrows_one(mjrl_ctx* ctx, const Args& a, int grid, size_t smem, cudaStream_t s) {
+  auto kern = rows::pol_rows_kernel<HP, NPK, MODE>;
+  static size_t attr = 0;
+  if (smem > attr) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    attr = smem;
+  }
+  kern<<<grid, NTHREADS, smem, s>>>(a);
+  return mjrl_check_launch("pol_rows_kernel");
+}
+
+// gradient / evaluation in the rows form; returns -1 when the shape does not fit
+template <int MODE>
+int launch_pol_rows(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
+  int HP, NPK;
+  size_t smem_fvp;
+  if (!rows_fits(ctx, a.n, a.m, a.h1, a.h2, &HP, &NPK, &smem_fvp)) return -1;
+  const Flat F(a.n, a.m, a.h1, a.h2);
+  const rows::GLayout L(HP, NPK, a.n, MODE == M_GRAD);
+  const size_t smem = sizeof(float) * (size_t)L.total;
+  if (smem + 128 > (size_t)ctx->max_smem_optin) return -1;
+  const long long ntiles = (a.N + 2 * rows::TSR - 1) / (2 * rows::TSR);
+  int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
+  if (grid < 1) grid = 1;
+  *grid_out = grid;
+  a.dstride = (F.d + 31) & ~31;
+  if (MODE == M_GRAD) {
+    a.partials = (float*)mjrl_scratch(ctx, sizeof(float) * (size_t)grid * a.dstride);
+    if (!a.partials) return MJRL_E_STATE;
+  }
+  a.spartials = (double*)mjrl_scratch2(ctx, sizeof(double) * 2 * grid);
+  if (!a.spartials) return MJRL_E_STATE;
+#define POLROWS_CASE(H, K) if (HP == H && NPK == K) return launch_polrows_one<H, K, MODE>(ctx, a, grid, smem, s)
+  POLROWS_CASE(64, 1); POLROWS_CASE(64, 2); POLROWS_CASE(64, 3);
+  POLROWS_CASE(32, 1); POLROWS_CASE(32, 2); POLROWS_CASE(32, 3);
+#undef POLROWS_CASE
+  return -1;
+}
+
 template <int MODE>
 int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
   const int hmax = a.h1 > a.h2 ? a.h1 : a.h2;
@@ -880,6 +922,11 @@ int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
     const int rc = launch_fvp_rows(ctx, a, grid_out, s);
     if (rc >= 0) return rc;
   }
+  if constexpr (MODE == M_GRAD || MODE == M_EVAL) {
+    const int rc = launch_pol_rows<MODE>(ctx, a, grid_out, s);
+    if (rc >= 0) return rc;
+  }
+  a.cache = nullptr;   // the tile kernels below neither fill nor use the activation cache
   const int HP = hmax <= 32 ? 32 : 64;
   const Flat F(a.n, a.m, a.h1, a.h2);
   const bool bwd = MODE == M_GRAD || MODE == M_FVP;
@@ -1319,6 +1366,14 @@ int mjrl_policy_grad(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* p
                      const float* obs, const float* act, const float* w, const float* old_ll,
                      int64_t N, double* grad_sum, double* surr_sum, float* ll_out, float* mean_out,
                      void* stream) {
+  return mjrl_policy_grad_cached(ctx, desc, params, obs, act, w, old_ll, N, grad_sum, surr_sum, ll_out,
+                                 mean_out, nullptr, stream);
+}
+
+int mjrl_policy_grad_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                            const float* obs, const float* act, const float* w, const float* old_ll,
+                            int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
+                            float* mean_out, float* fvp_cache, void* stream) {
   int rc = check_desc(desc, "policy_grad");
   if (rc) return rc;
   MJRL_REQUIRE(ctx && params && obs && act && w && grad_sum && N > 0, MJRL_E_ARG,
@@ -1327,6 +1382,7 @@ int mjrl_policy_grad(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* p
   fill_desc(a, desc);
   a.params = params; a.obs = obs; a.act = act; a.w = w; a.old_ll = old_ll; a.N = N;
   a.ll_out = ll_out; a.mean_out = mean_out;
+  a.cache = fvp_cache; a.cache_mode = fvp_cache ? 1 : 0;
   int grid;
   cudaStream_t s = (cudaStream_t)stream;
   rc = launch_any<M_GRAD>(ctx, a, &grid, s);
