@@ -372,20 +372,25 @@ linbase_gram_tiles_kernel(const float* __restrict__ obs, const double* __restric
   }
 }
 
-// gram[i*(F+1)+j] = sum_cta S[i][j] (upper) mirrored; gram[F*(F+1)] = y^T y
-__global__ void linbase_gram_reduce_kernel(const double* __restrict__ partial, int nparts, int F,
-                                           int FP, double* __restrict__ gram) {
+// gram[i*(F+1)+j] = sum_cta S[i][j] (upper) mirrored; gram[F*(F+1)] = y^T y.  One 64-thread CTA per
+// entry: thread k adds partials k, k+64, ... then a fixed-order shuffle + 2-slot sum (deterministic).
+__global__ void __launch_bounds__(64)
+linbase_gram_reduce_kernel(const double* __restrict__ partial, int nparts, int F, int FP,
+                           double* __restrict__ gram) {
+  __shared__ double sw[2];
   const int F1 = F + 1;
-  const int total = F * F1 + 1;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
-    int i, j;
-    if (idx == F * F1) { i = F; j = F; } else { i = idx / F1; j = idx - i * F1; }
-    int a = min(i, j), b = max(i, j);
-    // entry (a,b) lives in tile (a/8, b/8) which is stored iff b/8 >= a/8 -- always true
-    double s = 0.0;
-    for (int c = 0; c < nparts; ++c) s += partial[(size_t)c * FP * FP + a * FP + b];
-    gram[idx] = s;
-  }
+  const int idx = blockIdx.x;
+  int i, j;
+  if (idx == F * F1) { i = F; j = F; } else { i = idx / F1; j = idx - i * F1; }
+  const int a = min(i, j), b = max(i, j);
+  // entry (a,b) lives in tile (a/8, b/8) which is stored iff b/8 >= a/8 -- always true
+  const double* src = partial + (size_t)a * FP + b;
+  double s = 0.0;
+  for (int c = threadIdx.x; c < nparts; c += 64) s += src[(size_t)c * FP * FP];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) sw[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) gram[idx] = sw[0] + sw[1];
 }
 
 // -------------------------------------------------------------------- solve
@@ -580,7 +585,7 @@ int mjrl_linbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, co
   int rc = mjrl_check_launch("linbase_gram");
   if (rc) return rc;
   int total = F * F1 + 1;
-  linbase_gram_reduce_kernel<<<(total + 127) / 128, 128, 0, s>>>(partial, grid, F, FP, gram);
+  linbase_gram_reduce_kernel<<<total, 64, 0, s>>>(partial, grid, F, FP, gram);
   return mjrl_check_launch("linbase_gram_reduce");
 }
 

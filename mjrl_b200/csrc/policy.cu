@@ -716,13 +716,23 @@ namespace pol {
 // out[i] = sum_c partials[c][i] in fp64.  FVP: the log_std block [ols, d) is
 // count * h(sigma_j) * vec_j with h = 4 s (2 s - eps)/(2 s + eps)^2, s = sigma^2, eps = 1e-8
 // (second derivative of the KL expression of gaussian_mlp.py:137-139 at new == old).
-__global__ void reduce_partials_kernel(const float* __restrict__ partials, int nparts, int dstride,
-                                       int d, double* __restrict__ out, int ols, double count,
-                                       const float* __restrict__ params, const float* __restrict__ vec,
-                                       const int32_t* __restrict__ stop_flag) {
+__global__ void __launch_bounds__(256)
+reduce_partials_kernel(const float* __restrict__ partials, int nparts, int dstride,
+                       int d, double* __restrict__ out, int ols, double count,
+                       const float* __restrict__ params, const float* __restrict__ vec,
+                       const int32_t* __restrict__ stop_flag) {
+  // block = 32 outputs x 8 slices of the partials; slices are combined in a fixed order
+  __shared__ double sacc[8][33];
   if (stop_flag && *stop_flag) return;
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= d) return;
+  const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + x;
+  double acc = 0.0;
+  const bool net = i < d && !(vec && i >= ols);
+  if (net)
+    for (int c = y; c < nparts; c += 8) acc += (double)partials[(size_t)c * dstride + i];
+  sacc[y][x] = acc;
+  __syncthreads();
+  if (y != 0 || i >= d) return;
   if (vec && i >= ols) {
     const double ls = (double)params[i];
     const double s = exp(2.0 * ls), eps = 1e-8;
@@ -730,9 +740,10 @@ __global__ void reduce_partials_kernel(const float* __restrict__ partials, int n
     out[i] = count * h * (double)vec[i];
     return;
   }
-  double acc = 0.0;
-  for (int c = 0; c < nparts; ++c) acc += (double)partials[(size_t)c * dstride + i];
-  out[i] = acc;
+  double tot = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) tot += sacc[k][x];
+  out[i] = tot;
 }
 
 __global__ void reduce_scalars_kernel(const double* __restrict__ sp, int nparts, double* __restrict__ out,
@@ -1193,33 +1204,74 @@ cg_init_kernel(mjrl_cg_state st, long long d, const double* __restrict__ b, doub
   }
 }
 
-// cg_solve.py:10-20 with z = z_sum*inv_count + damping*p (npg_cg.py:74)
+// cg_solve.py:10-20 with z = z_sum*inv_count + damping*p (npg_cg.py:74).
+// REGS: every thread keeps its <= CG_E elements of p, z, x, r in registers, so the four vectors are
+// read once (all loads in flight together) instead of once per pass; same arithmetic and order.
+constexpr int CG_E = 8;
+template <bool REGS>
 __global__ void __launch_bounds__(CG_THREADS)
 cg_update_kernel(mjrl_cg_state st, long long d, double inv_count, double damping, double tol) {
   __shared__ double red[32];
   if (st.flags[0]) return;
   const double rdotr = st.scal[0];
   double pz = 0.0;
-  for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
-    const double p = st.p[i];
-    const double z = fma(st.z[i], inv_count, damping * p);
-    st.z[i] = z;
-    pz = fma(p, z, pz);
+  double rp[REGS ? CG_E : 1], rz[REGS ? CG_E : 1], rx[REGS ? CG_E : 1], rr[REGS ? CG_E : 1];
+  if (REGS) {
+#pragma unroll
+    for (int k = 0; k < CG_E; ++k) {
+      const long long i = threadIdx.x + (long long)k * CG_THREADS;
+      const bool in = i < d;
+      rp[k] = in ? st.p[i] : 0.0; rz[k] = in ? st.z[i] : 0.0;
+      rx[k] = in ? st.x[i] : 0.0; rr[k] = in ? st.r[i] : 0.0;
+    }
+#pragma unroll
+    for (int k = 0; k < CG_E; ++k) {
+      rz[k] = fma(rz[k], inv_count, damping * rp[k]);
+      pz = fma(rp[k], rz[k], pz);
+    }
+  } else {
+    for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
+      const double p = st.p[i];
+      const double z = fma(st.z[i], inv_count, damping * p);
+      st.z[i] = z;
+      pz = fma(p, z, pz);
+    }
   }
   pz = cta_sum_bcast(pz, red);
   const double v = rdotr / pz;
   double nrr = 0.0;
-  for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
-    st.x[i] = fma(v, st.p[i], st.x[i]);
-    const double r = fma(-v, st.z[i], st.r[i]);
-    st.r[i] = r;
-    nrr = fma(r, r, nrr);
+  if (REGS) {
+#pragma unroll
+    for (int k = 0; k < CG_E; ++k) {
+      rx[k] = fma(v, rp[k], rx[k]);
+      rr[k] = fma(-v, rz[k], rr[k]);
+      nrr = fma(rr[k], rr[k], nrr);
+    }
+  } else {
+    for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
+      st.x[i] = fma(v, st.p[i], st.x[i]);
+      const double r = fma(-v, st.z[i], st.r[i]);
+      st.r[i] = r;
+      nrr = fma(r, r, nrr);
+    }
   }
   nrr = cta_sum_bcast(nrr, red);
   const double mu = nrr / rdotr;
-  for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
-    const double p = fma(mu, st.p[i], st.r[i]);
-    st.p[i] = p; st.p32[i] = (float)p;
+  if (REGS) {
+#pragma unroll
+    for (int k = 0; k < CG_E; ++k) {
+      const long long i = threadIdx.x + (long long)k * CG_THREADS;
+      if (i < d) {
+        const double p = fma(mu, rp[k], rr[k]);
+        st.z[i] = rz[k]; st.x[i] = rx[k]; st.r[i] = rr[k];
+        st.p[i] = p; st.p32[i] = (float)p;
+      }
+    }
+  } else {
+    for (long long i = threadIdx.x; i < d; i += CG_THREADS) {
+      const double p = fma(mu, st.p[i], st.r[i]);
+      st.p[i] = p; st.p32[i] = (float)p;
+    }
   }
   if (threadIdx.x == 0) {
     st.scal[0] = nrr; st.scal[1] = pz; st.scal[2] = v; st.scal[3] = mu;
@@ -1388,7 +1440,7 @@ int mjrl_policy_grad_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const f
   rc = launch_any<M_GRAD>(ctx, a, &grid, s);
   if (rc) return rc;
   const Flat F(desc->n, desc->m, desc->h1, desc->h2);
-  reduce_partials_kernel<<<(F.d + 127) / 128, 128, 0, s>>>(a.partials, grid, a.dstride, F.d, grad_sum,
+  reduce_partials_kernel<<<(F.d + 31) / 32, 256, 0, s>>>(a.partials, grid, a.dstride, F.d, grad_sum,
                                                             F.ols, 0.0, nullptr, nullptr, nullptr);
   if (surr_sum) reduce_scalars_kernel<<<1, 32, 0, s>>>(a.spartials, grid, surr_sum, 1, nullptr);
   return mjrl_check_launch("policy_grad reduce");
@@ -1426,7 +1478,7 @@ int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const fl
   rc = launch_any<M_FVP>(ctx, a, &grid, s);
   if (rc) return rc;
   const Flat F(desc->n, desc->m, desc->h1, desc->h2);
-  reduce_partials_kernel<<<(F.d + 127) / 128, 128, 0, s>>>(a.partials, grid, a.dstride, F.d, fvp_sum,
+  reduce_partials_kernel<<<(F.d + 31) / 32, 256, 0, s>>>(a.partials, grid, a.dstride, F.d, fvp_sum,
                                                             F.ols, (double)N, params, vec, stop_flag);
   return mjrl_check_launch("policy_fvp reduce");
 }
@@ -1443,7 +1495,10 @@ int mjrl_cg_init(mjrl_ctx* ctx, const mjrl_cg_state* st, int64_t d, const double
 int mjrl_cg_update(mjrl_ctx* ctx, const mjrl_cg_state* st, int64_t d, double inv_count, double damping,
                    double residual_tol, void* stream) {
   MJRL_REQUIRE(ctx && st && d > 0, MJRL_E_ARG, "cg_update: bad argument");
-  cg_update_kernel<<<1, CG_THREADS, 0, (cudaStream_t)stream>>>(*st, d, inv_count, damping, residual_tol);
+  if (d <= (int64_t)CG_E * CG_THREADS)
+    cg_update_kernel<true><<<1, CG_THREADS, 0, (cudaStream_t)stream>>>(*st, d, inv_count, damping, residual_tol);
+  else
+    cg_update_kernel<false><<<1, CG_THREADS, 0, (cudaStream_t)stream>>>(*st, d, inv_count, damping, residual_tol);
   return mjrl_check_launch("cg_update");
 }
 
