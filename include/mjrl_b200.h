@@ -100,6 +100,16 @@ int mjrl_linbase_solve(mjrl_ctx* ctx, const double* gram, int32_t F, double reg_
                        const double* coeffs_prev, double* coeffs, double* info4,
                        void* stream);
 
+/* ---- QuadraticBaseline: mjrl/baselines/quadratic_baseline.py ------------------------------ */
+/* Features per timestep (:10-37): [o (n), o_i*o_j for i <= j row-major (n(n+1)/2), 1, al, al^2,
+ * al^3, al^4], o = clip(obs,-10,10)/10, al = t_in_path/1000; F = n + n(n+1)/2 + 5 (n <= 16).
+ * gram: same layout as mjrl_linbase_gram with this F; solve it with mjrl_linbase_solve(F)
+ * (:51-58 is the same ridge + NaN ladder).  predict (:66-68): pred[t] = features(t) . coeffs. */
+int mjrl_quadbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, const int32_t* path_offsets,
+                       int32_t P, int64_t N, int32_t n, double* gram, void* stream);
+int mjrl_quadbase_predict(mjrl_ctx* ctx, const float* obs, const int32_t* path_offsets, int32_t P,
+                          int64_t N, int32_t n, const double* coeffs, double* pred, void* stream);
+
 /* ---- (b) MLPBaseline: mjrl/baselines/mlp_baseline.py --------------------------------- */
 /* (n+4)-128-128-1 ReLU value net, fp32 (:24-28).  Flat parameter vector in torch
  * `model.parameters()` order: fc_0.weight [128][n+4] | fc_0.bias | fc_1.weight [128][128] |

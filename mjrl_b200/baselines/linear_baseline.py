@@ -17,6 +17,12 @@ from ..batch import PathBatch, batch_for
 
 
 class LinearBaseline:
+    _gram_fn, _predict_fn = "mjrl_linbase_gram", "mjrl_linbase_predict"
+
+    @staticmethod
+    def _num_feat(n):
+        return n + 4
+
     def __init__(self, env_spec, reg_coeff=1e-5):
         self.n = env_spec.observation_dim
         self._reg_coeff = reg_coeff
@@ -34,7 +40,7 @@ class LinearBaseline:
 
     def predict_batch(self, batch: PathBatch):
         out = batch.alloc_f64()
-        batch.ctx.call("mjrl_linbase_predict", ptr(batch.obs), ptr(batch.offsets), c_int(batch.P),
+        batch.ctx.call(self._predict_fn, ptr(batch.obs), ptr(batch.offsets), c_int(batch.P),
                        c_i64(batch.N), c_int(batch.n), ptr(self._coeffs_on(batch.device)),
                        ptr(out), stream_ptr())
         return out
@@ -44,9 +50,9 @@ class LinearBaseline:
         when asked.  With sync=False the coefficients stay on the device until `coeffs` is read."""
         if batch.returns is None:
             batch.returns = batch.gather("returns")
-        F = batch.n + 4
+        F = self._num_feat(batch.n)
         gram = torch.empty(F * (F + 1) + 1, dtype=torch.float64, device=batch.device)
-        batch.ctx.call("mjrl_linbase_gram", ptr(batch.obs), ptr(batch.returns), ptr(batch.offsets),
+        batch.ctx.call(self._gram_fn, ptr(batch.obs), ptr(batch.returns), ptr(batch.offsets),
                        c_int(batch.P), c_i64(batch.N), c_int(batch.n), ptr(gram), stream_ptr())
         if allreduce is None and dist is not None and dist.world > 1:
             allreduce = dist.allreduce

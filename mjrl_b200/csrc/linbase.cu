@@ -126,6 +126,50 @@ linbase_predict_kernel(const float* __restrict__ obs, const int32_t* __restrict_
   }
 }
 
+// QuadraticBaseline predict (quadratic_baseline.py:66-68): one thread per timestep; its o row is
+// widened once into shared memory, then linear + upper-triangle products + bias + time powers.
+constexpr int QPRED_TS = 128;
+__global__ void __launch_bounds__(QPRED_TS)
+quadbase_predict_kernel(const float* __restrict__ obs, const int32_t* __restrict__ off, int P,
+                        int64_t N, int n, int F, const double* __restrict__ coeffs,
+                        double* __restrict__ pred) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* sc = reinterpret_cast<double*>(smem_raw);            // [F]
+  double* so = sc + ((F + 1) & ~1);                            // [QPRED_TS][n | 1]
+  const int ns = n | 1, tid = threadIdx.x;
+  for (int k = tid; k < F; k += QPRED_TS) sc[k] = coeffs[k];
+  const int64_t ntiles = (N + QPRED_TS - 1) / QPRED_TS;
+  const double inv = (double)P / (double)N;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t t0 = tile * QPRED_TS;
+    const int rows = (int)min((int64_t)QPRED_TS, N - t0);
+    __syncthreads();
+    const TilePath tp = tile_path(off, P, t0, inv);
+    stream_rows<QPRED_TS>(obs + t0 * n, rows * n, n, tid, [&](int r, int c, float v) {
+      so[r * ns + c] = (double)fminf(fmaxf(v, -10.f), 10.f) / 10.0;
+    });
+    __syncthreads();
+    if (tid < rows) {
+      const int64_t t = t0 + tid;
+      const double* o = so + tid * ns;
+      double acc = 0.0;
+      for (int k = 0; k < n; ++k) acc = fma(o[k], sc[k], acc);
+      int qq = n;
+      for (int i = 0; i < n; ++i) {
+        const double oi = o[i];
+        for (int j = i; j < n; ++j, ++qq) acc = fma(oi * o[j], sc[qq], acc);
+      }
+      const double al = (double)t_in_path(off, P, tp, t) / 1000.0, al2 = al * al;
+      acc += sc[qq];
+      acc = fma(al, sc[qq + 1], acc);
+      acc = fma(al2, sc[qq + 2], acc);
+      acc = fma(al2 * al, sc[qq + 3], acc);
+      acc = fma(al2 * al2, sc[qq + 4], acc);
+      pred[t] = acc;
+    }
+  }
+}
+
 __global__ void fill_zero_kernel(double* __restrict__ x, int64_t N) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -177,6 +221,44 @@ __device__ __forceinline__ void gram_stage_tile(const float* __restrict__ obs,
   stream_rows<GRAM_THREADS>(obs + t0 * n, rows * n, n, tid, [&](int r, int c, float v) {
     feat[r * FS + c] = (double)fminf(fmaxf(v, -10.f), 10.f);
   });
+}
+
+// QuadraticBaseline features (quadratic_baseline.py:10-37): [o (n) | o_i o_j, i <= j row-major (Q) | 1 |
+// al, al^2, al^3, al^4 | y | zero padding], o = clip(obs,-10,10)/10.  `pairs` = the (i | j << 8) table
+// of the Q products in shared memory.  Contains a CTA barrier: the products read o of other threads.
+__device__ __forceinline__ void gram_stage_tile_quad(const float* __restrict__ obs,
+                                                     const double* __restrict__ ret,
+                                                     const int32_t* __restrict__ off, int P, double inv,
+                                                     int64_t t0, int rows, int n, int Q, int TS, int FP8,
+                                                     int FS, const int* __restrict__ pairs,
+                                                     double* __restrict__ feat, int tid) {
+  const int c1 = n + Q;          // column of the constant 1
+  const int F1 = c1 + 6;         // 1, four powers of al, y
+  const TilePath tp = tile_path(off, P, t0, inv);
+  for (int r = tid; r < TS; r += GRAM_THREADS) {
+    double* row = feat + r * FS;
+    if (r < rows) {
+      const int64_t t = t0 + r;
+      const double y = ldg_stream(ret + t);
+      const double al = (double)t_in_path(off, P, tp, t) / 1000.0;
+      const double al2 = al * al;
+      row[c1] = 1.0; row[c1 + 1] = al; row[c1 + 2] = al2; row[c1 + 3] = al2 * al; row[c1 + 4] = al2 * al2;
+      row[c1 + 5] = y;
+      for (int c = F1; c < FP8; ++c) row[c] = 0.0;
+    } else {
+      for (int c = 0; c < FP8; ++c) row[c] = 0.0;  // zero rows contribute nothing
+    }
+  }
+  stream_rows<GRAM_THREADS>(obs + t0 * n, rows * n, n, tid, [&](int r, int c, float v) {
+    feat[r * FS + c] = (double)fminf(fmaxf(v, -10.f), 10.f) / 10.0;
+  });
+  __syncthreads();
+  for (int idx = tid; idx < rows * Q; idx += GRAM_THREADS) {
+    const int r = idx / Q, qq = idx - r * Q;
+    const int pr = pairs[qq];
+    const double* row = feat + r * FS;
+    feat[r * FS + n + qq] = row[pr & 255] * row[pr >> 8];
+  }
 }
 
 // SPLIT variant (n <= 19).  The obs slab of a tile arrives by one bulk copy (TMA), double-buffered,
@@ -315,8 +397,17 @@ template <int MAXT>
 __global__ void __launch_bounds__(GRAM_THREADS)
 linbase_gram_tiles_kernel(const float* __restrict__ obs, const double* __restrict__ ret,
                           const int32_t* __restrict__ off, int P, int64_t N, int n, int TS, int FS,
-                          int nside, int ntri, double* __restrict__ partial) {
+                          int nside, int ntri, int Q /* > 0: quadratic features */,
+                          double* __restrict__ partial) {
   extern __shared__ unsigned char smem_raw[];
+  __shared__ int pairs[160];
+  if (Q > 0) {  // (i, j) of product q, i <= j row-major
+    for (int qq = threadIdx.x; qq < Q; qq += GRAM_THREADS) {
+      int i = 0, rem = qq, rowlen = n;
+      while (rem >= rowlen) { rem -= rowlen; ++i; --rowlen; }
+      pairs[qq] = i | ((i + rem) << 8);
+    }
+  }
   const int FP8 = 8 * nside;
   double* feat = reinterpret_cast<double*>(smem_raw);  // [TS][FS]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -347,7 +438,10 @@ linbase_gram_tiles_kernel(const float* __restrict__ obs, const double* __restric
     const int64_t t0 = tile * TS;
     const int rows = (int)min((int64_t)TS, N - t0);
     __syncthreads();
-    gram_stage_tile(obs, ret, off, P, (double)P / (double)N, t0, rows, n, TS, FP8, FS, feat, tid);
+    if (Q > 0)
+      gram_stage_tile_quad(obs, ret, off, P, (double)P / (double)N, t0, rows, n, Q, TS, FP8, FS, pairs, feat, tid);
+    else
+      gram_stage_tile(obs, ret, off, P, (double)P / (double)N, t0, rows, n, TS, FP8, FS, feat, tid);
     __syncthreads();
     for (int qd = 0; qd < nq; ++qd) {
       const double* fr = feat + (4 * qd + q) * FS + g;
@@ -515,15 +609,18 @@ int mjrl_linbase_predict(mjrl_ctx* ctx, const float* obs, const int32_t* off, in
   return mjrl_check_launch("linbase_predict");
 }
 
-int mjrl_linbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, const int32_t* off,
-                      int32_t P, int64_t N, int32_t n, double* gram, void* stream) {
+// Q = 0: LinearBaseline features (F = n + 4); Q = n(n+1)/2: QuadraticBaseline (F = n + Q + 5)
+static int gram_common(mjrl_ctx* ctx, const float* obs, const double* returns, const int32_t* off,
+                       int32_t P, int64_t N, int32_t n, int Q, double* gram, void* stream) {
   MJRL_REQUIRE(ctx && obs && returns && off && gram && N > 0 && n > 0 && P > 0, MJRL_E_ARG,
-               "linbase_gram: bad argument");
-  const int F = n + 4, F1 = F + 1, FP = (F1 + 7) & ~7;
+               "baseline gram: bad argument");
+  MJRL_REQUIRE(Q <= 160 && n < 256, MJRL_E_SHAPE, "quadbase_gram: obs_dim %d too large", n);
+  const int F = Q > 0 ? n + Q + 5 : n + 4, F1 = F + 1, FP = (F1 + 7) & ~7;
   const int nside = FP / 8, ntri = nside * (nside + 1) / 2;
   const int per = (ntri + GRAM_WARPS - 1) / GRAM_WARPS;
-  MJRL_REQUIRE(nside <= 3 || per <= 32, MJRL_E_SHAPE,
-               "linbase_gram: n=%d gives %d Gram tiles (> %d)", n, ntri, 32 * GRAM_WARPS);
+  const bool split = Q == 0 && nside <= 3;
+  MJRL_REQUIRE(split || per <= 32, MJRL_E_SHAPE,
+               "baseline gram: n=%d gives %d Gram tiles (> %d)", n, ntri, 32 * GRAM_WARPS);
   int FS = FP;  // row stride in doubles, = 4 (mod 16): the fragment loads hit 16 distinct bank pairs
   while ((FS & 15) != 4) ++FS;
   const int TS = FS <= 24 ? 256 : (FS <= 52 ? 128 : 64);
@@ -532,16 +629,16 @@ int mjrl_linbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, co
   // writes and the fragment reads are both conflict-free; 18 when two 8-wide blocks live there:
   // 2-way); reused for the warp partials
   const int EXS = (nside - n / 8) == 1 ? 9 : 18;
-  if (nside <= 3) {
+  if (split) {
     smem = (size_t)2 * TS * n * sizeof(float) + sizeof(double) * (size_t)TS * EXS;
     size_t smem_red = sizeof(double) * (size_t)GRAM_WARPS * ntri * 64;
     if (smem_red > smem) smem = smem_red;
   }
   MJRL_REQUIRE(smem <= (size_t)ctx->max_smem_optin, MJRL_E_SHAPE, "linbase_gram: smem %zu", smem);
   const void* kern = nullptr;
-  if (nside == 1) kern = (const void*)linbase_gram_split_kernel<1>;
-  else if (nside == 2) kern = (const void*)linbase_gram_split_kernel<2>;
-  else if (nside == 3) kern = (const void*)linbase_gram_split_kernel<3>;
+  if (split && nside == 1) kern = (const void*)linbase_gram_split_kernel<1>;
+  else if (split && nside == 2) kern = (const void*)linbase_gram_split_kernel<2>;
+  else if (split && nside == 3) kern = (const void*)linbase_gram_split_kernel<3>;
   else if (per <= 4) kern = (const void*)linbase_gram_tiles_kernel<4>;
   else if (per <= 8) kern = (const void*)linbase_gram_tiles_kernel<8>;
   else if (per <= 16) kern = (const void*)linbase_gram_tiles_kernel<16>;
@@ -550,7 +647,7 @@ int mjrl_linbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, co
   int per_sm = 1;  // persistent grid = exactly the resident CTAs
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, GRAM_THREADS, smem);
   per_sm = per_sm < 1 ? 1 : per_sm;
-  if (nside > 3 && per_sm > 2) per_sm = 2;  // bounds the scratch of the per-CTA partials
+  if (!split && per_sm > 2) per_sm = 2;  // bounds the scratch of the per-CTA partials
   int64_t ntiles = (N + TS - 1) / TS;
   int grid = (int)(ntiles < (int64_t)ctx->sm_count * per_sm ? ntiles : (int64_t)ctx->sm_count * per_sm);
   double* partial = (double*)mjrl_scratch2(ctx, sizeof(double) * (size_t)grid * FP * FP);
@@ -571,11 +668,11 @@ int mjrl_linbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, co
       cudaFuncSetAttribute(linbase_gram_tiles_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                            (int)smem);                                                              \
     linbase_gram_tiles_kernel<MT><<<grid, GRAM_THREADS, smem, s>>>(obs, returns, off, P, N, n, TS, FS, \
-                                                                   nside, ntri, partial);           \
+                                                                   nside, ntri, Q, partial);        \
   } while (0)
-  if (nside == 1) GRAM_SPLIT(1);
-  else if (nside == 2) GRAM_SPLIT(2);
-  else if (nside == 3) GRAM_SPLIT(3);
+  if (split && nside == 1) GRAM_SPLIT(1);
+  else if (split && nside == 2) GRAM_SPLIT(2);
+  else if (split && nside == 3) GRAM_SPLIT(3);
   else if (per <= 4) GRAM_TILES(4);
   else if (per <= 8) GRAM_TILES(8);
   else if (per <= 16) GRAM_TILES(16);
@@ -587,6 +684,37 @@ int mjrl_linbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, co
   int total = F * F1 + 1;
   linbase_gram_reduce_kernel<<<total, 64, 0, s>>>(partial, grid, F, FP, gram);
   return mjrl_check_launch("linbase_gram_reduce");
+}
+
+int mjrl_linbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, const int32_t* off,
+                      int32_t P, int64_t N, int32_t n, double* gram, void* stream) {
+  return gram_common(ctx, obs, returns, off, P, N, n, 0, gram, stream);
+}
+
+int mjrl_quadbase_gram(mjrl_ctx* ctx, const float* obs, const double* returns, const int32_t* off,
+                       int32_t P, int64_t N, int32_t n, double* gram, void* stream) {
+  MJRL_REQUIRE(n > 0 && n <= 16, MJRL_E_SHAPE,
+               "quadbase_gram: obs_dim %d > 16 (n + n(n+1)/2 + 5 features exceed the solve kernel)", n);
+  return gram_common(ctx, obs, returns, off, P, N, n, n * (n + 1) / 2, gram, stream);
+}
+
+int mjrl_quadbase_predict(mjrl_ctx* ctx, const float* obs, const int32_t* off, int32_t P, int64_t N,
+                          int32_t n, const double* coeffs, double* pred, void* stream) {
+  MJRL_REQUIRE(ctx && N >= 0 && n > 0 && n <= 16 && P >= 0, MJRL_E_ARG, "quadbase_predict: bad ctx/N/n/P");
+  if (N == 0) return 0;
+  MJRL_REQUIRE(pred, MJRL_E_ARG, "quadbase_predict: null pred");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!coeffs) {  // never fit: zeros (quadratic_baseline.py:66-67)
+    fill_zero_kernel<<<ctx->sm_count * 4, 256, 0, s>>>(pred, N);
+    return mjrl_check_launch("quadbase_predict(zero)");
+  }
+  MJRL_REQUIRE(obs && off, MJRL_E_ARG, "quadbase_predict: null pointer");
+  const int F = n + n * (n + 1) / 2 + 5;
+  const size_t smem = sizeof(double) * (((F + 1) & ~1) + (size_t)QPRED_TS * (n | 1));
+  int64_t ntiles = (N + QPRED_TS - 1) / QPRED_TS;
+  int grid = (int)(ntiles < (int64_t)ctx->sm_count * 8 ? ntiles : (int64_t)ctx->sm_count * 8);
+  quadbase_predict_kernel<<<grid, QPRED_TS, smem, s>>>(obs, off, P, N, n, F, coeffs, pred);
+  return mjrl_check_launch("quadbase_predict");
 }
 
 int mjrl_linbase_solve(mjrl_ctx* ctx, const double* gram, int32_t F, double reg_coeff,

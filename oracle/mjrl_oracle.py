@@ -132,6 +132,63 @@ class LinearBaseline:
         return linear_features(path).dot(self._coeffs)
 
 
+def quadratic_features(paths):
+    """[o (n), o_i*o_j for i <= j row-major (n(n+1)/2), 1, al, al^2, al^3, al^4] with
+    o = clip(obs,-10,10)/10, al = t/1000.  mjrl/baselines/quadratic_baseline.py:10-37."""
+    o = np.concatenate([p["observations"] for p in paths])
+    o = np.clip(o, -10, 10) / 10.0
+    if o.ndim > 2:
+        o = o.reshape(o.shape[0], -1)
+    N, n = o.shape
+    F = np.ones((N, int(n + n * (n + 1) / 2 + 1 + 4)))
+    F[:, :n] = o
+    k = n
+    for i in range(n):
+        for j in range(i, n):
+            F[:, k] = o[:, i] * o[:, j]
+            k += 1
+    row = 0
+    for p in paths:
+        T = len(p["rewards"])
+        al = np.arange(T) / 1000.0
+        for j in range(4):
+            F[row:row + T, -4 + j] = al ** (j + 1)
+        row += T
+    return F
+
+
+class QuadraticBaseline:
+    """Ridge regression on `quadratic_features`; mjrl/baselines/quadratic_baseline.py:4-68
+    (same normal-equation lstsq and NaN ladder as LinearBaseline, :51-58)."""
+
+    def __init__(self, env_spec=None, reg_coeff=1e-5, obs_dim=None):
+        self._reg_coeff = reg_coeff
+        self._coeffs = None
+
+    def fit(self, paths, return_errors=False):
+        X = quadratic_features(paths)
+        y = np.concatenate([p["returns"] for p in paths])
+        if return_errors:  # :45-48
+            pred = X.dot(self._coeffs) if self._coeffs is not None else np.zeros(y.shape)
+            err_before = np.sum((y - pred) ** 2) / np.sum(y ** 2)
+        lam = copy.deepcopy(self._reg_coeff)
+        for _ in range(10):  # :51-58
+            self._coeffs = np.linalg.lstsq(
+                X.T.dot(X) + lam * np.identity(X.shape[1]), X.T.dot(y), rcond=None)[0]
+            if not np.any(np.isnan(self._coeffs)):
+                break
+            lam *= 10
+        if return_errors:  # :60-64
+            pred = X.dot(self._coeffs)
+            err_after = np.sum((y - pred) ** 2) / np.sum(y ** 2)
+            return err_before, err_after
+
+    def predict(self, path):
+        if self._coeffs is None:  # :66-68
+            return np.zeros(len(path["rewards"]))
+        return quadratic_features([path]).dot(self._coeffs)
+
+
 def mlp_baseline_features(paths):
     """[clip(obs,-10,10)/10, al, al^2, al^3, al^4], no bias column.
 

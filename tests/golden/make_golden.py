@@ -210,6 +210,34 @@ def run_mlpbase_case(R, name, n, horizon, N, seed, epochs, reg_coef):
     print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
 
 
+def run_quadbase_case(R, name, n, horizon, N, seed):
+    """QuadraticBaseline (quadratic_baseline.py): features, first fit (zero predictions before),
+    second fit on a second batch (non-trivial error_before), predictions."""
+    from mjrl_b200.utils import synthetic as syn
+    import mjrl.baselines.quadratic_baseline as qb
+    spec = R.EnvSpec(n, 3, horizon, 1)
+    zero = np.zeros(n * 4 + 4 + 4 * 4 + 4 + 4 * 3 + 3 + 3, dtype=np.float32)
+    out = dict(n=n, horizon=horizon, N=N, seed=seed, numpy_version=np.__version__)
+    base = qb.QuadraticBaseline(spec)
+    for k in (0, 1):
+        b = syn.make_flat_batch(N, n, 3, horizon, seed + k, zero, (4, 4))
+        paths = syn.flat_to_paths(b)
+        R.ps.compute_returns(paths, 0.995)
+        pre = "b%d_" % k
+        out[pre + "observations"] = b["observations"]; out[pre + "rewards"] = b["rewards"]
+        out[pre + "path_offsets"] = b["path_offsets"]; out[pre + "terminated"] = b["terminated"]
+        out[pre + "returns"] = np.concatenate([p["returns"] for p in paths])
+        if k == 0:
+            out["features_head"] = base._features(paths[:2])
+        out[pre + "pred_before"] = np.concatenate([base.predict(p) for p in paths])
+        out[pre + "errors"] = np.asarray(base.fit(paths, return_errors=True), dtype=np.float64)
+        out[pre + "coeffs"] = np.asarray(base._coeffs, dtype=np.float64)
+        out[pre + "pred_after"] = np.concatenate([base.predict(p) for p in paths])
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
+
+
 def run_ppo_case(R, name, n, m, hidden, horizon, N, seed, mid, epochs):
     """PPO (ppo_clip.py): full train_from_paths of the live reference, with the minibatch rows it
     drew from numpy's global stream (np.random.choice, :89) recorded."""
@@ -256,6 +284,10 @@ if __name__ == "__main__":
         run_ppo_case(R, "ppo_hopper_mid", 11, 3, (64, 64), 100, 640, 8000, True, 2)
         run_ppo_case(R, "ppo_linear", 6, 2, (), 25, 320, 8001, False, 3)
         sys.exit(0)
+    if "--quadbase-only" in sys.argv:
+        run_quadbase_case(R, "quadbase_pointmass", 6, 25, 1000, 9000)
+        run_quadbase_case(R, "quadbase_hopper", 11, 200, 3000, 9001)
+        sys.exit(0)
     if "--mlpbase-only" in sys.argv:
         run_mlpbase_case(R, "mlpbase_1step", 11, 60, 150, 7000, 1, 0.0)
         run_mlpbase_case(R, "mlpbase_hopper", 11, 200, 1500, 7001, 2, 1e-3)
@@ -271,3 +303,5 @@ if __name__ == "__main__":
     run_mlpbase_case(R, "mlpbase_hopper", 11, 200, 1500, 7001, 2, 1e-3)
     run_ppo_case(R, "ppo_hopper_mid", 11, 3, (64, 64), 100, 640, 8000, True, 2)
     run_ppo_case(R, "ppo_linear", 6, 2, (), 25, 320, 8001, False, 3)
+    run_quadbase_case(R, "quadbase_pointmass", 6, 25, 1000, 9000)
+    run_quadbase_case(R, "quadbase_hopper", 11, 200, 3000, 9001)
