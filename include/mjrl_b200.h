@@ -194,7 +194,8 @@ int mjrl_policy_fvp(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* pa
  * iteration, npg_cg.py:103-106) only `vec` changes, so tanh layers need computing once.
  * cache: device fp32 [mjrl_policy_fvp_cache_count(...)] (0 = this shape has no cached variant: pass
  * cache_mode 0).  cache_mode 1 = compute and fill, 2 = use (caller guarantees params/obs/N are
- * those of the filling call), 0 = plain mjrl_policy_fvp.  Results are bit-identical in all modes. */
+ * those of the filling call), 0 = plain mjrl_policy_fvp.  Modes 0 and 1 give identical bits; mode 2 reads
+ * back the same activations and is deterministic, with its own fixed summation order (~1e-7 relative). */
 int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N);
 /* mjrl_policy_grad that also fills that cache (flat_vpg runs at the parameters the CG solve that
  * follows it uses, npg_cg.py:96-106): fvp_cache as above or NULL. */

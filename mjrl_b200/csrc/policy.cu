@@ -18,34 +18,6 @@
 
 namespace pol {
 
-enum Mode { M_FWD = 0, M_EVAL = 1, M_GRAD = 2, M_FVP = 3 };
-
-struct Args {
-  const float* params;
-  const float* vec;
-  const float* obs;
-  const float* act;
-  const float* w;
-  const float* old_ll;
-  const float* old_mean;
-  const float* old_log_std;
-  float* mean_out;
-  float* ll_out;
-  const float* in_shift;
-  const float* in_scale;
-  const float* out_shift;
-  const float* out_scale;
-  float* partials;    // [grid][dstride]
-  double* spartials;  // [grid][2]
-  const int32_t* stop_flag;
-  long long* phase_cycles;  // debug: [grid][8] cycles per phase (P0,P1,P2,P3a,P3b,P4,P5,P6+loop)
-  long long N;
-  int n, m, h1, h2, dstride;
-  int prefetch;   // 1: double-buffered obs/act staging (Layout::XR/AR present)
-  float* cache;   // FVP rows kernel: forward activations in fragment order (fill or use), may be null
-  int cache_mode; // 0 none, 1 fill, 2 use
-};
-
 // Shared-memory carve-up (offsets in floats), identical on host and device.
 struct Layout {
   int TS, LDH, LDW, NP, LDX, MP, LDM;
@@ -872,6 +844,14 @@ inline int launch_fvp_rows(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s
   if (!a.partials) return MJRL_E_STATE;
   const bool use = a.cache && a.cache_mode == 2;
   if (a.cache_mode != 1 && !use) a.cache = nullptr;
+  if (use) {   // warp-specialised variant of the cached product (fvp_ws.cu): opt-in, MJRL_B200_FVP_WS=1
+    // (measured 0.794 ms against 0.775 ms for the half-CTA kernel on the Hopper shape: DESIGN.md 3.1)
+    static const bool ws_on = getenv("MJRL_B200_FVP_WS") && getenv("MJRL_B200_FVP_WS")[0] == '1';
+    if (ws_on) {
+      const int rc = launch_fvp_ws(ctx, a, grid, s);
+      if (rc >= 0) return rc;
+    }
+  }
 #define ROWS_CASE(H, K)                                                                     \
   if (HP == H && NPK == K)                                                                  \
     return use ? launch_rows_one<H, K, true>(ctx, a, grid, smem, s)                         \

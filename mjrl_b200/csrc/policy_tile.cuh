@@ -310,4 +310,36 @@ __device__ __forceinline__ void mma_wgrad(float (&acc)[NFR][4], const float* __r
     for (int e = 0; e < 4; ++e) acc[j][e] += odd[j][e];
 }
 
+// ---- arguments shared by every policy kernel (policy.cu, fvp_rows.cuh, pol_rows.cuh, fvp_ws.cu) ----
+enum Mode { M_FWD = 0, M_EVAL = 1, M_GRAD = 2, M_FVP = 3 };
+
+struct Args {
+  const float* params;
+  const float* vec;
+  const float* obs;
+  const float* act;
+  const float* w;
+  const float* old_ll;
+  const float* old_mean;
+  const float* old_log_std;
+  float* mean_out;
+  float* ll_out;
+  const float* in_shift;
+  const float* in_scale;
+  const float* out_shift;
+  const float* out_scale;
+  float* partials;    // [grid][dstride]
+  double* spartials;  // [grid][2]
+  const int32_t* stop_flag;
+  long long* phase_cycles;  // debug: [grid][8] cycles per phase (P0,P1,P2,P3a,P3b,P4,P5,P6+loop)
+  long long N;
+  int n, m, h1, h2, dstride;
+  int prefetch;   // 1: double-buffered obs/act staging (Layout::XR/AR present)
+  float* cache;   // FVP rows kernel: forward activations in fragment order (fill or use), may be null
+  int cache_mode; // 0 none, 1 fill, 2 use
+};
+
+// warp-specialised cached FVP (fvp_ws.cu): returns -1 when it does not take the shape
+int launch_fvp_ws(mjrl_ctx* ctx, const Args& a, int grid, cudaStream_t s);
+
 }  // namespace pol

@@ -187,7 +187,7 @@ def test_batched_actions_philox():
 def test_fvp_variants_agree_and_cache_is_bit_exact(n, m, hidden, N):
     """FVP kernel variants over shapes that take the rows-in-registers kernel (hidden 64 / 32 / mixed,
     ragged N, several obs widths) against the oracle's fp64 Gauss-Newton product, and the activation
-    cache: fill / use must reproduce the plain call bit for bit."""
+    cache: filling must not change the product, using it must agree to fp32 rounding and be deterministic."""
     import torch
     from mjrl_b200.policies.gaussian_mlp import MLP
     from mjrl_b200.utils.gym_env import EnvSpec
@@ -209,9 +209,42 @@ def test_fvp_variants_agree_and_cache_is_bit_exact(n, m, hidden, N):
         eng.cg_flags.zero_()
         eng.fvp(params, obs, vec, out, cache_mode=mode)
         outs.append(out.cpu().numpy())
-    for o in outs[1:]:
-        np.testing.assert_array_equal(o, outs[0])
+    np.testing.assert_array_equal(outs[1], outs[0])        # filling the cache does not change the product
+    np.testing.assert_array_equal(outs[3], outs[2])        # the cached product is deterministic
+    # cached variant: same activations bit for bit, its own (fixed) summation order
+    assert rel_l2(outs[2], outs[0]) < 2e-6
     # fp64 truth: sum_t J^T diag(2/(2 sigma^2 + 1e-8)) J v on the network block, N h(sigma) v on log_std
     tp = O.TruthPolicy(O.GaussianPolicy(n, m, hidden, flat.copy()))
     truth = N * tp.fvp(obs.cpu().numpy(), vec.cpu().numpy().astype(np.float64))
     assert rel_l2(outs[0], truth) < 1e-5
+
+
+def test_warp_specialised_fvp_variant_in_subprocess():
+    """MJRL_B200_FVP_WS=1 selects the warp-specialised cached FVP kernel (csrc/fvp_ws.cu; the switch is
+    read once per process, hence the subprocess): same result as the default kernel to fp32 rounding."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, %r)
+from mjrl_b200.policies.gaussian_mlp import MLP
+from mjrl_b200.utils.gym_env import EnvSpec
+from mjrl_b200.algos.engine import UpdateEngine
+rng = np.random.default_rng(3)
+pol = MLP(EnvSpec(11, 3, 100, 1), hidden_sizes=(64, 64), seed=5)
+flat = pol.get_param_values(); flat = flat + 0.3 * rng.standard_normal(flat.shape).astype(np.float32)
+pol.set_param_values(flat.copy(), True, True)
+eng = UpdateEngine(pol); dev = eng.device
+obs = torch.from_numpy(rng.standard_normal((1500, 11)).astype(np.float32)).to(dev)
+vec = torch.from_numpy(rng.standard_normal(flat.shape[0]).astype(np.float32) * 0.1).to(dev)
+outs = []
+for mode in (1, 2, 2):
+    out = torch.zeros(flat.shape[0], dtype=torch.float64, device=dev)
+    eng.cg_flags.zero_(); eng.fvp(eng.dv.params("new"), obs, vec, out, cache_mode=mode); outs.append(out.cpu().numpy())
+rel = np.linalg.norm(outs[1] - outs[0]) / np.linalg.norm(outs[0])
+assert np.array_equal(outs[1], outs[2]) and rel < 2e-6, rel
+print("WS_OK %%.2e" %% rel)
+""" % root
+    env = dict(os.environ, MJRL_B200_FVP_WS="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "WS_OK" in r.stdout, r.stdout + r.stderr
