@@ -243,6 +243,28 @@ int mjrl_policy_act(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* pa
                     const float* obs, int64_t B, uint64_t seed, uint64_t offset, float* act_out,
                     float* mean_out, void* stream);
 
+/* ---- lock-step rollout (north_star (e)) ---------------------------------
+ * One simulator step of B environment slots, replacing B calls of policy.get_action inside the
+ * rollout loop (mjrl/samplers/base_sampler.py:64-66, evaluation_sampler.py:57-58):
+ *   mean = policy(obs); act = sample ? mean + exp(log_std)*eps : mean.
+ * eps = noise[b][j] when `noise` is given (host-generated, e.g. the reference's per-episode
+ * np.random stream of base_sampler.py:47-50), else Philox4x32-10 keyed by seeds[b] (the
+ * episode's seed) with counter (tsteps[b], j/4): a function of (episode, step, component) only.
+ * When dst_rows[b] >= 0 the slot's observation and action rows are also written to
+ * obs_store[dst_rows[b]] / act_store[dst_rows[b]] (device-resident timestep store; either may
+ * be NULL).  All pointers are device pointers; seeds/tsteps may be NULL when noise is given or
+ * sample == 0. */
+int mjrl_rollout_act(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                     const float* obs, int32_t B, const uint64_t* seeds, const int32_t* tsteps,
+                     const float* noise, int32_t sample, const int64_t* dst_rows,
+                     float* obs_store, float* act_store, float* act_out, float* mean_out,
+                     void* stream);
+/* dst[r][0:width] = src[src_rows[r]][0:width], r < rows: squeezes the padded [episode][T] store
+ * into the flat path-major buffer the update kernels take (the np.concatenate of
+ * npg_cg.py:87-89 over paths of unequal length). */
+int mjrl_rows_gather_f32(mjrl_ctx* ctx, const float* src, const int64_t* src_rows, int64_t rows,
+                         int32_t width, float* dst, void* stream);
+
 /* ---- PPO minibatch epochs: mjrl/algos/ppo_clip.py:47-54,85-101 ------------------------- */
 /* dst[b] = src[idx[b]] for rows of `width` floats (a with-replacement minibatch, :89-92). */
 int mjrl_gather_rows_f32(mjrl_ctx* ctx, const float* src, const int32_t* idx, int32_t B, int32_t width,

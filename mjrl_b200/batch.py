@@ -99,6 +99,28 @@ class PathBatch:
                            count=len(paths))
         return cls(obs, act, rew, off, term, device=device, paths=paths)
 
+    @classmethod
+    def from_device(cls, obs_dev, act_dev, rew, path_offsets, terminated, paths=None):
+        """Batch whose observation / action rows are already resident (filed there step by step by
+        the lock-step sampler, samplers/lockstep.py): only the reward column is uploaded."""
+        self = cls.__new__(cls)
+        self.device = obs_dev.device
+        self.ctx = _lib.context(self.device.index)
+        self.paths = paths
+        off = np.ascontiguousarray(np.asarray(path_offsets), dtype=np.int32)
+        self.P, self.N, self.h_offsets = int(off.shape[0] - 1), int(off[-1]), off
+        self.n, self.m = int(obs_dev.shape[1]), int(act_dev.shape[1])
+        if obs_dev.shape[0] != self.N or act_dev.shape[0] != self.N:
+            raise ValueError("device rows do not match the path offsets")
+        self.offsets = torch.from_numpy(off).to(self.device)
+        term8 = np.ascontiguousarray(np.asarray(terminated), dtype=np.uint8)
+        self.terminated = torch.from_numpy(term8).to(self.device)
+        self.obs, self.act = obs_dev, act_dev
+        self.rew = self._upload_f64(rew)
+        self.returns = self.baseline = self.adv = None
+        self.h2d_bytes = self._nbytes(self.rew) + off.nbytes + self.P
+        return self
+
     # ---- results back into the path dicts (reference contract: fp64 numpy [T]) --------
     def scatter(self, key, tensor):
         if self.paths is None:
@@ -127,6 +149,9 @@ def _signature(paths):
 def batch_for(paths, device=None):
     """PathBatch of `paths`, built once per list (1-entry cache keyed on object identity) so
     compute_returns -> compute_advantages -> train_from_paths -> fit share one upload."""
+    resident = getattr(paths, "batch", None)     # lock-step rollouts arrive already filed on the device
+    if resident is not None and resident.P == len(paths):
+        return resident
     key = _signature(paths)
     if _cache["key"] == key:
         return _cache["batch"]

@@ -278,11 +278,44 @@ def run_ppo_case(R, name, n, m, hidden, horizon, N, seed, mid, epochs):
     print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
 
 
+def run_rollout_case(R, name, hidden, N, pegasus_seed):
+    """The reference's own rollout loops (mjrl/samplers/base_sampler.py:10-88,
+    evaluation_sampler.py:11-85) on tests/stub_env.StubEnv with a reference policy."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import stub_env
+    import mjrl.samplers.base_sampler as bs
+    import mjrl.samplers.evaluation_sampler as es
+    env = stub_env.make_stub()
+    pol, init = build_ref_policy(R, env.n, env.m, hidden, seed=77)
+    rng = np.random.default_rng(pegasus_seed)
+    flat = init + 0.2 * rng.standard_normal(init.shape)
+    flat[-env.m:] = -0.7
+    pol.set_param_values(flat.copy(), set_new=True, set_old=True)
+    out = dict(hidden=np.asarray(hidden, dtype=np.int64), flat=pol.get_param_values(), N=N,
+               pegasus_seed=pegasus_seed, horizon=env.horizon)
+    for tag, paths in (("s", bs.do_rollout(N, pol, T=1e6, env=stub_env.make_stub(), pegasus_seed=pegasus_seed)),
+                       ("e", es.do_evaluation_rollout(N, pol, T=1e6, env=stub_env.make_stub(),
+                                                      pegasus_seed=pegasus_seed))):
+        out[tag + "_lens"] = np.asarray([len(q["rewards"]) for q in paths])
+        out[tag + "_terminated"] = np.asarray([bool(q["terminated"]) for q in paths])
+        for key in ("observations", "actions", "rewards"):
+            out[tag + "_" + key] = np.concatenate([q[key] for q in paths])
+        out[tag + "_mean"] = np.concatenate([q["agent_infos"]["mean"] for q in paths])
+        out[tag + "_info_t"] = np.concatenate([q["env_infos"]["t"] for q in paths])
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024), "lens", out["s_lens"])
+
+
 if __name__ == "__main__":
     R = import_reference()
     if "--ppo-only" in sys.argv:
         run_ppo_case(R, "ppo_hopper_mid", 11, 3, (64, 64), 100, 640, 8000, True, 2)
         run_ppo_case(R, "ppo_linear", 6, 2, (), 25, 320, 8001, False, 3)
+        sys.exit(0)
+    if "--rollout-only" in sys.argv:
+        run_rollout_case(R, "rollout_stub_mlp", (32, 32), 12, 500)
+        run_rollout_case(R, "rollout_stub_linear", (), 6, 600)
         sys.exit(0)
     if "--quadbase-only" in sys.argv:
         run_quadbase_case(R, "quadbase_pointmass", 6, 25, 1000, 9000)
@@ -305,3 +338,5 @@ if __name__ == "__main__":
     run_ppo_case(R, "ppo_linear", 6, 2, (), 25, 320, 8001, False, 3)
     run_quadbase_case(R, "quadbase_pointmass", 6, 25, 1000, 9000)
     run_quadbase_case(R, "quadbase_hopper", 11, 200, 3000, 9001)
+    run_rollout_case(R, "rollout_stub_mlp", (32, 32), 12, 500)
+    run_rollout_case(R, "rollout_stub_linear", (), 6, 600)
