@@ -280,6 +280,21 @@ int mjrl_adam_step(mjrl_ctx* ctx, int64_t d, float* params, const double* grad_s
                    float* adam_m, float* adam_v, int64_t step, double lr, double beta1, double beta2,
                    double eps, double weight_decay, void* stream);
 
+/* ---- Behaviour cloning: mjrl/algos/behavior_cloning.py:43-68, behavior_cloning_2.py:56-77 -- */
+/* `steps` serial Adam steps on the flat policy vector.  Step s gathers rows idx[s*B .. s*B+B) of
+ * obs/act (np.random.choice minibatch, :56 / :66), forms grad_sum[d] = sum_t w_t dLL_t/dtheta at the
+ * CURRENT params (LR = 1) and applies mjrl_adam_step with g = grad_scale*grad_sum to the first d_opt
+ * parameters (d for behavior_cloning.py, loss -mean LL: grad_scale = -1/B; d - m for
+ * behavior_cloning_2.py, whose MSE loss is the log_std = 0 likelihood: grad_scale = -2/(B*m) on a
+ * working vector with a zeroed log_std block).  Adam step numbers are step0+1 .. step0+steps.
+ * Scratch (device): mb_obs [B,n], mb_act [B,m], mb_w [B] (the weights, ones for BC), grad_sum fp64 [d].
+ * No host synchronisation inside. */
+int mjrl_policy_adam_chain(mjrl_ctx* ctx, const mjrl_policy_desc* desc, float* params, const float* obs,
+                           const float* act, const int32_t* idx, int32_t steps, int32_t B, int64_t d_opt,
+                           double grad_scale, float* adam_m, float* adam_v, int64_t step0, double lr,
+                           double beta1, double beta2, double eps, double weight_decay, float* mb_obs,
+                           float* mb_act, const float* mb_w, double* grad_sum, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -42,6 +42,28 @@ def _digest(path):
     return h.hexdigest()
 
 
+def _deps(path, seen=None):
+    """Transitive closure of the quoted #includes of a source file (paths resolved relative to it)."""
+    import re
+    seen = set() if seen is None else seen
+    path = os.path.normpath(path)
+    if path in seen or not os.path.exists(path):
+        return seen
+    seen.add(path)
+    for inc in re.findall(r'^\s*#\s*include\s+"([^"]+)"', open(path).read(), flags=re.M):
+        _deps(os.path.join(os.path.dirname(path), inc), seen)
+    return seen
+
+
+def _obj_digest(src):
+    h = hashlib.sha1()
+    for f in sorted(_deps(os.path.join(CSRC, src))):
+        h.update(f.encode())
+        h.update(open(f, "rb").read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
 def build(force=False, verbose=False):
     os.makedirs(BUILD, exist_ok=True)
     stamp = os.path.join(BUILD, "stamp")
@@ -53,6 +75,9 @@ def build(force=False, verbose=False):
 
     def compile_one(src):
         obj = os.path.join(BUILD, src[:-3] + ".o")
+        ostamp, odig = obj + ".stamp", _obj_digest(src)
+        if not force and os.path.exists(obj) and os.path.exists(ostamp) and open(ostamp).read() == odig:
+            return obj          # this object's own sources and headers are unchanged
         cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log = os.path.join(BUILD, src[:-3] + ".ptxas.log")
@@ -61,6 +86,7 @@ def build(force=False, verbose=False):
             raise RuntimeError("nvcc failed for %s:\n%s" % (src, r.stderr[-6000:]))
         if verbose:
             sys.stderr.write(r.stderr)
+        open(ostamp, "w").write(odig)
         return obj
 
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:

@@ -83,4 +83,33 @@ int mjrl_adam_step(mjrl_ctx* ctx, int64_t d, float* params, const double* grad_s
   return mjrl_check_launch("adam_kernel");
 }
 
+// Behaviour cloning (mjrl/algos/behavior_cloning.py:52-61, behavior_cloning_2.py:62-71): a serial chain of
+// Adam steps on with-replacement minibatches.  Host loop over the step kernels: no host work, no
+// synchronisation between steps, so the chain runs at launch rate.
+int mjrl_policy_adam_chain(mjrl_ctx* ctx, const mjrl_policy_desc* desc, float* params, const float* obs,
+                           const float* act, const int32_t* idx, int32_t steps, int32_t B, int64_t d_opt,
+                           double grad_scale, float* adam_m, float* adam_v, int64_t step0, double lr,
+                           double beta1, double beta2, double eps, double weight_decay, float* mb_obs,
+                           float* mb_act, const float* mb_w, double* grad_sum, void* stream) {
+  MJRL_REQUIRE(ctx && desc && params && obs && act && idx && adam_m && adam_v && mb_obs && mb_act && mb_w &&
+                   grad_sum && steps >= 0 && B > 0 && d_opt > 0 && step0 >= 0,
+               MJRL_E_ARG, "policy_adam_chain: bad argument");
+  const int64_t d = mjrl_policy_param_count(desc);
+  MJRL_REQUIRE(d > 0 && d_opt <= d, MJRL_E_SHAPE, "policy_adam_chain: d_opt exceeds the parameter count");
+  for (int32_t s = 0; s < steps; ++s) {
+    const int32_t* rows = idx + (int64_t)s * B;
+    int rc = mjrl_gather_rows_f32(ctx, obs, rows, B, desc->n, mb_obs, stream);
+    if (rc) return rc;
+    rc = mjrl_gather_rows_f32(ctx, act, rows, B, desc->m, mb_act, stream);
+    if (rc) return rc;
+    rc = mjrl_policy_grad(ctx, desc, params, mb_obs, mb_act, mb_w, nullptr, B, grad_sum, nullptr, nullptr,
+                          nullptr, stream);
+    if (rc) return rc;
+    rc = mjrl_adam_step(ctx, d_opt, params, grad_sum, grad_scale, adam_m, adam_v, step0 + s + 1, lr, beta1,
+                        beta2, eps, weight_decay, stream);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
 }  // extern "C"

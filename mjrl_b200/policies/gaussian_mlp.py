@@ -111,6 +111,10 @@ class _GaussianPolicyBase:
     def __getstate__(self):
         d = dict(self.__dict__)
         d["_dev"] = None
+        # pickle / deepcopy give every tensor of the reference object its own storage again (each
+        # torch.from_numpy view of gaussian_mlp.py:66-88 has its own Storage object), so a copy or a
+        # checkpoint of an aliased policy is NOT aliased (pinned by tests/golden/stock_policy_mlp.pickle)
+        d["_old_aliases_new"] = False
         return d
 
     # ---- queries -------------------------------------------------------------------------

@@ -682,6 +682,77 @@ def ppo_update(pol, paths, state=None, clip_coef=0.2, epochs=10, mb_size=64, lea
     return out
 
 
+def bc_transformations(expert_paths):
+    """mjrl/algos/behavior_cloning.py:25-29 (same lines in behavior_cloning_2.py): fp64 column
+    mean / std of the expert observations and actions, used as the policy's in/out transforms."""
+    observations = np.concatenate([p["observations"] for p in expert_paths])
+    actions = np.concatenate([p["actions"] for p in expert_paths])
+    return dict(in_shift=np.mean(observations, axis=0), in_scale=np.std(observations, axis=0),
+                out_shift=np.mean(actions, axis=0), out_scale=np.std(actions, axis=0))
+
+
+class BCState:
+    """What BC.__init__ does to the policy and the optimizer it builds once
+    (behavior_cloning.py:24-36; behavior_cloning_2.py:24-45).  mode "mle" = behavior_cloning.py
+    (Adam over trainable_params, loss -mean LL); mode "mse" = behavior_cloning_2.py (log_std set
+    to log(out_scale + 1e-12) through set_param_values, Adam over the NETWORK only, MSE loss)."""
+
+    def __init__(self, pol, expert_paths, mode="mle", lr=1e-3):
+        assert mode in ("mle", "mse")
+        self.pol, self.mode = pol, mode
+        tr = bc_transformations(expert_paths)
+        for k, v in tr.items():   # MuNet.set_transformations gaussian_mlp.py:159-174: fp32 cast
+            setattr(pol, k, torch.from_numpy(np.float32(v)))
+        if mode == "mse":
+            params = pol.get_param_values()
+            params[-pol.m:] = np.log(tr["out_scale"] + 1e-12)
+            pol.set_param_values(params)
+        self.optimizer = torch.optim.Adam(pol.new if mode == "mle" else pol.new[:-1], lr=lr)
+
+
+def bc_loss(pol, obs, act, mode):
+    """behavior_cloning.py:38-41 (-mean LL of the new parameters) / behavior_cloning_2.py:50-54
+    (torch MSELoss between model(obs) and the expert actions, both cast to fp32)."""
+    if mode == "mle":
+        return -torch.mean(pol.dist_info(obs, act, "new")[0])
+    o = torch.from_numpy(obs).float()
+    a = torch.from_numpy(act).float()
+    return torch.nn.functional.mse_loss(pol.mean(o, pol.new), a)
+
+
+def bc_train(state, expert_paths, epochs=5, mb_size=64, choice_source=None):
+    """BC.train, behavior_cloning.py:43-68 / behavior_cloning_2.py:56-77: per epoch one full-data
+    loss (logged), then int(N/mb) Adam steps on with-replacement minibatches drawn by
+    np.random.choice from the GLOBAL stream; finally set_param_values(new, True, True)."""
+    pol, mode = state.pol, state.mode
+    obs = np.concatenate([p["observations"] for p in expert_paths])
+    act = np.concatenate([p["actions"] for p in expert_paths])
+    choice = choice_source or (lambda n, k: np.random.choice(n, size=k))
+    num_samples = obs.shape[0]
+    losses = []
+    for _ in range(epochs):
+        losses.append(_scalar(bc_loss(pol, obs, act, mode)))
+        for _mb in range(int(num_samples / mb_size)):
+            idx = choice(num_samples, mb_size)
+            state.optimizer.zero_grad()
+            loss = bc_loss(pol, obs[idx], act[idx], mode)
+            loss.backward()
+            state.optimizer.step()
+    params_after_opt = pol.get_param_values()
+    # set_param_values re-creates the tensor list here (the reference re-points .data of the same
+    # leaves): keep the optimizer on the live tensors, moments carried over by position
+    old_leaves = state.optimizer.param_groups[0]["params"]
+    st = [state.optimizer.state.get(p, None) for p in old_leaves]
+    pol.set_param_values(params_after_opt, set_new=True, set_old=True)
+    leaves = pol.new if mode == "mle" else pol.new[:-1]
+    state.optimizer = torch.optim.Adam(leaves, lr=state.optimizer.param_groups[0]["lr"])
+    for p, s_ in zip(leaves, st):
+        if s_ is not None:
+            state.optimizer.state[p] = s_
+    losses.append(_scalar(bc_loss(pol, obs, act, mode)))
+    return {"losses": np.asarray(losses), "new_params": pol.get_param_values()}
+
+
 def full_npg_iteration(pol, baseline, paths, gamma, gae_lambda, **npg_kw):
     """What BatchREINFORCE.train_step does after sampling, batch_reinforce.py:86-101:
     returns, advantages (with the PREVIOUS fit), policy update, then baseline.fit."""

@@ -278,6 +278,92 @@ def run_ppo_case(R, name, n, m, hidden, horizon, N, seed, mid, epochs):
     print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024))
 
 
+def run_bc_case(R, name, n, m, hidden, horizon, N, seed, mode, epochs):
+    """Behaviour cloning: the live reference's BC class (behavior_cloning.py = "mle",
+    behavior_cloning_2.py = "mse") trained twice on synthetic expert paths, minibatch rows from
+    numpy's global stream (np.random.choice, :56 / :66) recorded."""
+    import torch
+    from mjrl_b200.utils import synthetic as syn
+    import importlib
+    mod = importlib.import_module("mjrl.algos.behavior_cloning" + ("" if mode == "mle" else "_2"))
+    pol, init = build_ref_policy(R, n, m, hidden, seed=123)
+    # expert data: actions of a DIFFERENT (perturbed) policy so the loss has something to fit
+    expert_flat, _ = syn.mid_training_variant(init, n, m, seed)
+    b = syn.make_flat_batch(N, n, m, horizon, seed, expert_flat, hidden, None)
+    paths = syn.flat_to_paths(b)
+    out = dict(n=n, m=m, hidden=np.asarray(hidden, dtype=np.int64), horizon=horizon, N=N, seed=seed,
+               epochs=epochs, mode=mode, init_params=init, numpy_version=np.__version__,
+               torch_version=torch.__version__)
+    out.update(b)
+    steps = epochs * int(N / 64)
+    np.random.seed(seed + 9)
+    out["minibatches"] = np.stack([np.random.choice(N, size=64) for _ in range(2 * steps)])
+    agent = mod.BC(paths, pol, epochs=epochs, batch_size=64, lr=1e-3)
+    out["params_after_init"] = pol.get_param_values()
+    for k in ("in_shift", "in_scale", "out_shift", "out_scale"):
+        out["tr_" + k] = getattr(pol.model, k).data.numpy().copy()
+    np.random.seed(seed + 9)
+    agent.train()
+    out["bc_new_params"] = pol.get_param_values()
+    out["bc_losses"] = np.asarray(agent.logger.log["loss"], dtype=np.float64)
+    agent.train()            # Adam state persists in agent.optimizer
+    out["bc_new_params_2"] = pol.get_param_values()
+    out["bc_losses_2"] = np.asarray(agent.logger.log["loss"], dtype=np.float64)[len(out["bc_losses"]):]
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, "%.1f KB" % (os.path.getsize(path) / 1024), "losses", out["bc_losses"])
+
+
+def run_checkpoint_case(R):
+    """Checkpoints exactly as train_agent.py:61-66 writes them: pickle.dump of the live reference's
+    policy / baseline objects, plus the values a loader must reproduce from them."""
+    import pickle
+    import torch
+    from mjrl_b200.utils import synthetic as syn
+    out = dict(numpy_version=np.__version__, torch_version=torch.__version__)
+    rng = np.random.default_rng(77)
+    # MLP policy, mid-training parameters set through set_param_values (float32 -> new/old alias, F14)
+    n, m, hidden = 11, 3, (64, 64)
+    pol, init = build_ref_policy(R, n, m, hidden, seed=123)
+    flat, tr = syn.mid_training_variant(init, n, m, 4242)
+    pol, _ = build_ref_policy(R, n, m, hidden, seed=123, flat=flat, transforms=tr)
+    pickle.dump(pol, open(os.path.join(HERE, "stock_policy_mlp.pickle"), "wb"))
+    obs = rng.standard_normal((40, n)) * 3
+    act = rng.standard_normal((40, m))
+    out.update(mlp_params=pol.get_param_values(), mlp_obs=obs, mlp_act=act,
+               mlp_ll=pol.log_likelihood(obs, act), mlp_mean=pol.new_dist_info(obs, act)[1].data.numpy())
+    # LinearPolicy straight from its constructor (new/old NOT aliased)
+    lp, linit = build_ref_policy(R, 6, 2, (), seed=5)
+    pickle.dump(lp, open(os.path.join(HERE, "stock_policy_linear.pickle"), "wb"))
+    out.update(lin_params=linit)
+    # LinearBaseline after one fit
+    spec = R.EnvSpec(n, m, 100, 1)
+    b = syn.make_flat_batch(1500, n, m, 100, 4243, flat, hidden, tr)
+    paths = syn.flat_to_paths(b)
+    R.ps.compute_returns(paths, 0.995)
+    lb = R.lb.LinearBaseline(spec)
+    lb.fit(paths)
+    pickle.dump(lb, open(os.path.join(HERE, "stock_baseline_linear.pickle"), "wb"))
+    out.update({"b_" + k: v for k, v in b.items()})
+    out.update(returns=np.concatenate([p["returns"] for p in paths]), lb_coeffs=lb._coeffs,
+               lb_pred=np.concatenate([lb.predict(p) for p in paths]))
+    # MLPBaseline after one fit (Adam state inside .optimizer), and what a SECOND fit then gives
+    torch.manual_seed(11)
+    mb = R.mb.MLPBaseline(spec, reg_coef=1e-3, batch_size=64, epochs=1)
+    np.random.seed(12)
+    mb.fit(paths)
+    pickle.dump(mb, open(os.path.join(HERE, "stock_baseline_mlp.pickle"), "wb"))
+    flatp = lambda: np.concatenate([p.data.numpy().ravel() for p in mb.model.parameters()]).astype(np.float32)
+    out.update(mb_params=flatp(), mb_pred=np.concatenate([mb.predict(p) for p in paths]))
+    np.random.seed(13)
+    mb.fit(paths)
+    out.update(mb_params_2=flatp())
+    path = os.path.join(HERE, "stock_checkpoints.npz")
+    np.savez_compressed(path, **out)
+    for f in ("stock_policy_mlp", "stock_policy_linear", "stock_baseline_linear", "stock_baseline_mlp"):
+        print(f, "%.1f KB" % (os.path.getsize(os.path.join(HERE, f + ".pickle")) / 1024))
+
+
 def run_rollout_case(R, name, hidden, N, pegasus_seed):
     """The reference's own rollout loops (mjrl/samplers/base_sampler.py:10-88,
     evaluation_sampler.py:11-85) on tests/stub_env.StubEnv with a reference policy."""
@@ -309,6 +395,14 @@ def run_rollout_case(R, name, hidden, N, pegasus_seed):
 
 if __name__ == "__main__":
     R = import_reference()
+    if "--bc-only" in sys.argv:
+        run_bc_case(R, "bc_mle_hopper", 11, 3, (64, 64), 100, 640, 8100, "mle", 2)
+        run_bc_case(R, "bc_mse_adroit", 45, 24, (32, 32), 50, 512, 8101, "mse", 2)
+        run_bc_case(R, "bc_mle_linear", 6, 2, (), 25, 320, 8102, "mle", 3)
+        sys.exit(0)
+    if "--checkpoint-only" in sys.argv:
+        run_checkpoint_case(R)
+        sys.exit(0)
     if "--ppo-only" in sys.argv:
         run_ppo_case(R, "ppo_hopper_mid", 11, 3, (64, 64), 100, 640, 8000, True, 2)
         run_ppo_case(R, "ppo_linear", 6, 2, (), 25, 320, 8001, False, 3)
