@@ -402,6 +402,10 @@ def run_b200(args):
                                       if use_mlp else "LinearBaseline", n, m,
                                       N, len(off) - 1, GAMMA, LAM, CG_ITERS, DAMPING),
                        "parallelism": "dp%d (whole paths per GPU)" % world,
+                       "exchange": ("none (1 GPU)" if world == 1 else
+                                    "peer-memory kernels over NVLink, CG update fused with its all-reduce (csrc/peer.cu)"
+                                    if agent._engine().dist.peer is not None else
+                                    "NCCL all-reduces (%s)" % agent._engine().dist.peer_note),
                        "l2": "256 MB buffer written between timed steps (outside the event brackets)",
                        "policy_reset_each_step": True},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,

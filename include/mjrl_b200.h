@@ -295,6 +295,39 @@ int mjrl_policy_adam_chain(mjrl_ctx* ctx, const mjrl_policy_desc* desc, float* p
                            double beta1, double beta2, double eps, double weight_decay, float* mb_obs,
                            float* mb_act, const float* mb_w, double* grad_sum, void* stream);
 
+/* ---- (e) multi-GPU: small fp64 sum all-reduces over NVLink peer memory ---------------------
+ * Replaces the collectives SURVEY 8(e) lists (gradient, each Fisher-vector product, Gram, moments,
+ * surrogate/KL sums; <= 107 KB each, latency bound) by ONE single-CTA kernel per exchange that
+ * signals the peers, pulls their contributions over NVLink and adds them in rank order (all ranks
+ * get bit-identical sums); mjrl_cg_update_peer fuses that exchange into the CG update
+ * (cg_solve.py:10-20), so a CG iteration is: product kernel -> partial reduce -> this kernel.
+ * One process per GPU: every rank creates its block, the 64-byte handles are exchanged by the host
+ * (torch.distributed all_gather), every rank connects.  `epoch` is a host counter starting at 1 that
+ * ALL ranks advance by one per exchange, in the same order.  A peer that does not arrive within the
+ * timeout (default 20 s) sets the error word read by mjrl_peer_status instead of hanging the GPU. */
+typedef struct mjrl_peer mjrl_peer;
+int mjrl_peer_handle_bytes(void);
+int mjrl_peer_create(mjrl_ctx* ctx, int32_t rank, int32_t world, int64_t max_count, mjrl_peer** out,
+                     void* handle_out);
+/* handles: world * mjrl_peer_handle_bytes() bytes in rank order (own entry ignored) */
+int mjrl_peer_connect(mjrl_peer* peer, const void* handles);
+/* same-process variant (ranks that share an address space, e.g. tests): bases[r] = mjrl_peer_base of rank r */
+int mjrl_peer_connect_ptrs(mjrl_peer* peer, void* const* bases);
+void* mjrl_peer_base(mjrl_peer* peer);
+/* device pointer of the local contribution slot of `epoch`: producers may write there directly */
+double* mjrl_peer_slot(mjrl_peer* peer, int64_t epoch);
+int mjrl_peer_set_timeout(mjrl_peer* peer, double seconds);
+/* dst[0..count) = sum over ranks of their src[0..count); src == NULL: already in mjrl_peer_slot(epoch).
+ * dst may alias src. */
+int mjrl_peer_allreduce_f64(mjrl_ctx* ctx, mjrl_peer* peer, const double* src, double* dst, int64_t count,
+                            int64_t epoch, void* stream);
+/* mjrl_cg_update with z_sum = sum over ranks of mjrl_peer_slot(epoch)[0..d) */
+int mjrl_cg_update_peer(mjrl_ctx* ctx, mjrl_peer* peer, const mjrl_cg_state* state, int64_t d,
+                        double inv_count, double damping, double residual_tol, int64_t epoch, void* stream);
+/* synchronous: *err_out = 1 when some wait timed out since creation */
+int mjrl_peer_status(mjrl_peer* peer, int32_t* err_out);
+int mjrl_peer_destroy(mjrl_peer* peer);
+
 #ifdef __cplusplus
 }
 #endif

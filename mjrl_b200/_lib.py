@@ -39,6 +39,8 @@ def load():
         fn = getattr(lib, name)  # raises AttributeError if a declared symbol is not exported
         if name.endswith("_count"):   # size queries return int64, not a status
             fn.restype = ctypes.c_int64
+        elif name in ("mjrl_peer_slot", "mjrl_peer_base"):   # device pointers
+            fn.restype = ctypes.c_void_p
         elif name != "mjrl_last_error":
             fn.restype = ctypes.c_int
     _lib = lib
@@ -62,6 +64,8 @@ def ptr(t):
         return c_void_p(0)
     if isinstance(t, int):
         return c_void_p(t)
+    if isinstance(t, ctypes.c_void_p):
+        return t
     return c_void_p(t.data_ptr())
 
 

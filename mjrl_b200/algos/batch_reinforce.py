@@ -169,6 +169,7 @@ class BatchREINFORCE:
         host = torch.cat([out, eng.grad[d:d + 1] / N_glob]).cpu().numpy()
         t_gLL = timer.time() - ts
         new_params = new_dev.cpu().numpy()
+        eng.dist.check()     # multi-GPU: a peer exchange that timed out invalidates the update
         surr_after, kl_dist, surr_before = float(host[0]), float(host[1]), float(host[2])
         self.policy.set_param_values(new_params, set_new=True, set_old=True)
         base_stats = self._finish_stats(stats, paths)

@@ -20,8 +20,16 @@ from .._lib import CGState, c_double, c_float, c_i64, c_int, c_void_p, ptr, stre
 
 
 class Dist:
-    """Thin wrapper over torch.distributed: sum all-reduce on device tensors; identity when
-    the process group is absent (single GPU)."""
+    """Sum all-reduce of small device tensors across the ranks of a torch.distributed group; identity
+    when the process group is absent (single GPU).
+
+    Data path (world > 1, CUDA): the peer-memory exchange kernels of csrc/peer.cu (`enable_peer`),
+    i.e. one single-CTA kernel per all-reduce over NVLink-mapped blocks, and the CG update fused with
+    its all-reduce; NCCL carries the tensors the peer block does not take (not fp64, or longer than the
+    block) and everything when MJRL_B200_PEER=0 or the box cannot map peer memory."""
+
+    peer = None
+    peer_note = "not tried"
 
     def __init__(self, group=None):
         import torch.distributed as td
@@ -30,12 +38,40 @@ class Dist:
         self.world = self.td.get_world_size(group) if self.td else 1
         self.rank = self.td.get_rank(group) if self.td else 0
         self.calls = 0
+        self.peer = None
+        self.peer_note = "not tried"
+
+    def enable_peer(self, ctx, max_count):
+        """Set up the peer-memory path once (collective: every rank of the group calls it)."""
+        from .. import peer as _peer
+        if self.peer is not None or self.td is None or self.world == 1 or self.peer_note != "not tried":
+            return self.peer
+        mode = _peer.mode()
+        if mode in ("0", "off", "nccl") or self.td.get_backend(self.group) != "nccl":
+            self.peer_note = "disabled"
+            return None
+        self.peer, why = _peer.connect_process_group(ctx, self.td, self.group, max_count)
+        self.peer_note = "active" if self.peer is not None else "unavailable: " + why
+        if self.peer is None and mode in ("1", "on", "required"):
+            raise _lib.MjrlError("MJRL_B200_PEER=1 but the peer-memory path is " + self.peer_note)
+        if self.peer is None and self.rank == 0:
+            import warnings
+            warnings.warn("mjrl_b200: peer-memory exchange " + self.peer_note + "; using NCCL all-reduces")
+        return self.peer
 
     def allreduce(self, t):
         if self.td is not None and self.world > 1:
-            self.td.all_reduce(t, op=self.td.ReduceOp.SUM, group=self.group)
+            if self.peer is not None and self.peer.takes(t):
+                self.peer.allreduce(t)
+            else:
+                self.td.all_reduce(t, op=self.td.ReduceOp.SUM, group=self.group)
             self.calls += 1
         return t
+
+    def check(self):
+        """After a host synchronisation: raise if a peer exchange timed out."""
+        if self.peer is not None:
+            self.peer.check()
 
     def global_count(self, n_local, device=None):
         """Sum of per-rank sample counts as a host float.  Shards are whole paths, so ranks
@@ -56,6 +92,8 @@ class UpdateEngine:
         self.device = self.dv.device
         self.dist = dist or Dist()
         d = self.dv.d
+        if self.dist.world > 1:
+            self.dist.enable_peer(self.ctx, d + 1)
         dev = self.device
         f64 = lambda k: torch.zeros(k, dtype=torch.float64, device=dev)
         self.grad = f64(d + 1)              # [gradient sum | surrogate sum] packed for one all-reduce
@@ -168,12 +206,23 @@ class UpdateEngine:
                 mode = 2      # filled by the gradient pass (or the first product) at these tensors
             else:
                 mode = 1
-            self.fvp(params, o, self.cg_p32, self.cg_z, cache_mode=mode)
+            peer = self.dist.peer if self.dist.world > 1 else None
+            if peer is not None:
+                # the product's partial reduce writes straight into this rank's exchange slot; the
+                # all-reduce over NVLink peer memory happens inside the CG update kernel
+                epoch, slot = peer.next_slot()
+                self.fvp(params, o, self.cg_p32, slot, cache_mode=mode)
+            else:
+                self.fvp(params, o, self.cg_p32, self.cg_z, cache_mode=mode)
             if mode == 1 and self._cache is not None:
                 self._cache_key = self._key(params, o)
-            self.dist.allreduce(self.cg_z)
-            self.ctx.call("mjrl_cg_update", ctypes.byref(self.cg), c_i64(d), c_double(1.0 / cnt),
-                          c_double(damping), c_double(tol), stream_ptr())
+            if peer is not None:
+                peer.cg_update(self.cg, d, 1.0 / cnt, damping, tol, epoch)
+                self.dist.calls += 1
+            else:
+                self.dist.allreduce(self.cg_z)
+                self.ctx.call("mjrl_cg_update", ctypes.byref(self.cg), c_i64(d), c_double(1.0 / cnt),
+                              c_double(damping), c_double(tol), stream_ptr())
             self.launches += 1
             if trace is not None:
                 trace.append(self.cg_x.cpu().numpy().copy())

@@ -90,6 +90,7 @@ class NPG(BatchREINFORCE):
         sb = eng.grad[d:d + 1] / st["N_glob"] if surr_before_dev is None else surr_before_dev
         host = torch.cat([out, sb, eng.scal4]).cpu().numpy()   # the update's single sync point
         new_params = new_dev.cpu().numpy()
+        eng.dist.check()     # multi-GPU: a peer exchange that timed out invalidates the update
         surr_after, kl_dist, surr_before = float(host[0]), float(host[1]), float(host[2])
         alpha, n_step_size = float(host[3]), float(host[5])
         self.policy.set_param_values(new_params, set_new=True, set_old=True)

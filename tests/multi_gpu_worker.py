@@ -40,7 +40,13 @@ def run(world_mode):
         ag.dist.group = None
     drop_cache()
     ag.train_step(len(paths), gamma=g["gamma"], gae_lambda=g["gae_lambda"], paths=paths)
+    global PEER_NOTE
+    if world_mode:
+        PEER_NOTE = "%s, %d exchanges" % (ag.dist.peer_note, ag.dist.peer.exchanges if ag.dist.peer else 0)
     return pol.get_param_values().astype(np.float64) - g["params"], np.asarray(base._coeffs), g
+
+
+PEER_NOTE = "-"
 
 
 def run_mlpbase(world_mode, rank, world):
@@ -79,8 +85,8 @@ if __name__ == "__main__":
         mlp_same = steps_multi == steps_one and np.array_equal(mlp_multi, mlp_one)
         errs_ok = all(abs(a - b) < 1e-9 * max(1.0, abs(b)) for a, b in zip(errs_multi, errs_one))
         ok = r_step < 1e-4 and r_coef < 1e-6 and mlp_same and errs_ok
-        print("MULTI_%s world=%d step_rel=%.3e coef_rel=%.3e mlpbase_bitexact=%s (%d steps) errs_ok=%s"
-              % ("OK" if ok else "FAIL", world, r_step, r_coef, mlp_same, steps_multi, errs_ok))
+        print("MULTI_%s world=%d step_rel=%.3e coef_rel=%.3e mlpbase_bitexact=%s (%d steps) errs_ok=%s peer=[%s]"
+              % ("OK" if ok else "FAIL", world, r_step, r_coef, mlp_same, steps_multi, errs_ok, PEER_NOTE))
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
