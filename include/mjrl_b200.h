@@ -197,6 +197,16 @@ int mjrl_policy_fvp(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* pa
  * those of the filling call), 0 = plain mjrl_policy_fvp.  Modes 0 and 1 give identical bits; mode 2 reads
  * back the same activations and is deterministic, with its own fixed summation order (~1e-7 relative). */
 int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N);
+/* Jacobian-cached product (act_dim <= 4, csrc/fvp_jac.cu): the m rows G1_j = d mu_j / d z1 of every
+ * timestep do not depend on `vec` either, so with them cached next to h1, h2 the product needs neither
+ * the tangent propagation nor the backward data products (43 % fewer MMAs, m*H*4 more bytes per
+ * timestep).  mjrl_policy_fvp_jac_ok: 1 when the shape has this variant (mjrl_policy_fvp_cache_count
+ * then includes the rows).  mjrl_policy_fvp_jac_fill computes the rows from an ALREADY FILLED h1|h2
+ * cache (cache_mode 1 product or mjrl_policy_grad_cached at the same params / obs / N); products then
+ * pass cache_mode 3.  Same result as modes 0-2 up to fp32 summation order (~1e-6 relative). */
+int mjrl_policy_fvp_jac_ok(mjrl_ctx* ctx, const mjrl_policy_desc* desc);
+int mjrl_policy_fvp_jac_fill(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params, int64_t N,
+                             float* cache, void* stream);
 /* mjrl_policy_grad that also fills that cache (flat_vpg runs at the parameters the CG solve that
  * follows it uses, npg_cg.py:96-106): fvp_cache as above or NULL. */
 int mjrl_policy_grad_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,

@@ -111,6 +111,8 @@ class UpdateEngine:
         self.launches = 0  # kernels launched by this engine (bench's gpu_launches)
         self._cache = None  # forward activations shared by the FVPs of one CG solve
         self._cache_key = None
+        self._jac_key = None  # (params, obs) the Jacobian rows G1 of the cache were filled for
+        self._jac_ok = None
 
     # ------------------------------------------------------------------ building blocks
     def whiten(self, adv64, eps=1e-6, scale=1.0, N_global=None):
@@ -169,6 +171,20 @@ class UpdateEngine:
                       c_int(cache_mode), stream_ptr())
         self.launches += 2
 
+    def _jac_prepare(self, params, obs):
+        """With the h1|h2 cache valid for (params, obs): make the Jacobian rows valid too (one fill pass
+        per CG solve).  False when this policy shape has no Jacobian-cached product."""
+        if self._jac_ok is None:
+            self._jac_ok = bool(_lib.load().mjrl_policy_fvp_jac_ok(self.ctx.h, self.dv.desc_ref()))
+        if not self._jac_ok or self._cache is None:
+            return False
+        key = self._key(params, obs)
+        if self._jac_key != key:
+            self.ctx.call("mjrl_policy_fvp_jac_fill", self.dv.desc_ref(), ptr(params), c_i64(obs.shape[0]),
+                          ptr(self._cache), stream_ptr())
+            self._jac_key = key
+        return True
+
     @staticmethod
     def _key(params, obs):
         """Identity + in-place-modification counters of the tensors a cache was filled from."""
@@ -203,7 +219,9 @@ class UpdateEngine:
             if subsample is not None:
                 mode = 0
             elif self._cache_key is not None and self._cache_key == self._key(params, o):
-                mode = 2      # filled by the gradient pass (or the first product) at these tensors
+                # h1|h2 filled by the gradient pass (or the first product) at these tensors; small action
+                # dimensions also cache the output-Jacobian rows and run the cheaper product (fvp_jac.cu)
+                mode = 3 if self._jac_prepare(params, o) else 2
             else:
                 mode = 1
             peer = self.dist.peer if self.dist.world > 1 else None

@@ -1414,7 +1414,30 @@ int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc,
   size_t smem;
   if (!rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem)) return 0;
   const int64_t ntiles = (N + rows::TSR - 1) / rows::TSR;
-  return ntiles * rows::TSR * 2 * HP;   // h1 and h2 of every (padded) timestep
+  int64_t cnt = ntiles * rows::TSR * 2 * HP;   // h1 and h2 of every (padded) timestep
+  if (jac_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, nullptr, nullptr, nullptr))
+    cnt += jac_cache_floats(desc->m, desc->h1, desc->h2, N);   // + the m Jacobian rows G1 (fvp_jac.cu)
+  return cnt;
+}
+
+int mjrl_policy_fvp_jac_ok(mjrl_ctx* ctx, const mjrl_policy_desc* desc) {
+  if (!ctx || !desc) return 0;
+  int HP, NPK;
+  size_t smem;
+  return rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem) &&
+         jac_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, nullptr, nullptr, nullptr) ? 1 : 0;
+}
+
+int mjrl_policy_fvp_jac_fill(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params, int64_t N,
+                             float* cache, void* stream) {
+  int rc = check_desc(desc, "policy_fvp_jac_fill");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params && cache && N > 0, MJRL_E_ARG, "policy_fvp_jac_fill: bad argument");
+  MJRL_REQUIRE(mjrl_policy_fvp_jac_ok(ctx, desc), MJRL_E_SHAPE,
+               "policy_fvp_jac_fill: this policy shape has no Jacobian-cached product");
+  rc = launch_jac_fill(ctx, params, desc->n, desc->m, desc->h1, desc->h2, cache, N, (cudaStream_t)stream);
+  MJRL_REQUIRE(rc >= 0, MJRL_E_SHAPE, "policy_fvp_jac_fill: shape not taken");
+  return rc;
 }
 
 int mjrl_policy_fvp(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
@@ -1429,7 +1452,7 @@ int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const fl
   int rc = check_desc(desc, "policy_fvp");
   if (rc) return rc;
   MJRL_REQUIRE(ctx && params && obs && vec && fvp_sum && N > 0, MJRL_E_ARG, "policy_fvp: bad argument");
-  MJRL_REQUIRE(cache_mode >= 0 && cache_mode <= 2 && (cache_mode == 0 || cache), MJRL_E_ARG,
+  MJRL_REQUIRE(cache_mode >= 0 && cache_mode <= 3 && (cache_mode == 0 || cache), MJRL_E_ARG,
                "policy_fvp: cache_mode %d needs a cache buffer", cache_mode);
   Args a = {};
   fill_desc(a, desc);
@@ -1437,7 +1460,14 @@ int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const fl
   a.cache = cache; a.cache_mode = cache_mode;
   int grid;
   cudaStream_t s = (cudaStream_t)stream;
-  rc = launch_any<M_FVP>(ctx, a, &grid, s);
+  if (cache_mode == 3) {
+    MJRL_REQUIRE(mjrl_policy_fvp_jac_ok(ctx, desc), MJRL_E_SHAPE,
+                 "policy_fvp: cache_mode 3 needs a shape mjrl_policy_fvp_jac_ok accepts");
+    rc = launch_fvp_jac(ctx, a, &grid, s);
+    MJRL_REQUIRE(rc >= 0, MJRL_E_SHAPE, "policy_fvp: Jacobian-cached product does not take this shape");
+  } else {
+    rc = launch_any<M_FVP>(ctx, a, &grid, s);
+  }
   if (rc) return rc;
   const Flat F(desc->n, desc->m, desc->h1, desc->h2);
   reduce_partials_kernel<<<(F.d + 31) / 32, 256, 0, s>>>(a.partials, grid, a.dstride, F.d, fvp_sum,

@@ -336,10 +336,18 @@ struct Args {
   int n, m, h1, h2, dstride;
   int prefetch;   // 1: double-buffered obs/act staging (Layout::XR/AR present)
   float* cache;   // FVP rows kernel: forward activations in fragment order (fill or use), may be null
-  int cache_mode; // 0 none, 1 fill, 2 use
+  int cache_mode; // 0 none, 1 fill, 2 use, 3 use h1|h2 and the Jacobian rows G1 (fvp_jac.cu)
 };
 
 // warp-specialised cached FVP (fvp_ws.cu): returns -1 when it does not take the shape
 int launch_fvp_ws(mjrl_ctx* ctx, const Args& a, int grid, cudaStream_t s);
+
+// Jacobian-cached FVP (fvp_jac.cu), act_dim <= 4: shape test, extra cache floats after the h1|h2 region,
+// the fill pass and the product (-1 when the shape does not fit)
+bool jac_fits(const mjrl_ctx* ctx, int n, int m, int h1, int h2, int* HP_out, int* NPK_out, size_t* smem_out);
+long long jac_cache_floats(int m, int h1, int h2, long long N);
+int launch_fvp_jac(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s);
+int launch_jac_fill(mjrl_ctx* ctx, const float* params, int n, int m, int h1, int h2, float* cache, long long N,
+                    cudaStream_t s);
 
 }  // namespace pol

@@ -219,6 +219,73 @@ def test_fvp_variants_agree_and_cache_is_bit_exact(n, m, hidden, N):
     assert rel_l2(outs[0], truth) < 1e-5
 
 
+@pytest.mark.parametrize("n,m,hidden,N,mid", [(11, 3, (64, 64), 1000, False), (11, 3, (64, 64), 777, True),
+                                               (12, 4, (32, 32), 500, True), (8, 2, (64, 32), 129, False),
+                                               (3, 1, (16, 16), 64, False), (17, 4, (32, 32), 4097, True),
+                                               (14, 3, (64, 64), 2049, True)])
+def test_fvp_jacobian_cached_variant(n, m, hidden, N, mid):
+    """cache_mode 3 (csrc/fvp_jac.cu, act_dim <= 4): the rows G1 = d mu_j / d z1 are filled once from the
+    cached h1|h2, then the product runs without tangent / backward-data MMAs.  Same product as mode 0 to
+    fp32 rounding, deterministic, exact against the fp64 Gauss-Newton truth, several vectors per fill, with
+    in/out transforms, ragged N, mixed hidden sizes; act_dim > 4 has no such variant."""
+    import ctypes
+    import torch
+    from mjrl_b200 import _lib
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.algos.engine import UpdateEngine
+    from mjrl_b200.utils import synthetic as syn
+    from oracle import mjrl_oracle as O
+    rng = np.random.default_rng(n * 100 + N)
+    pol = MLP(EnvSpec(n, m, 100, 1), hidden_sizes=hidden, seed=5)
+    flat = pol.get_param_values()
+    tr = None
+    if mid:
+        flat, tr = syn.mid_training_variant(flat, n, m, 77)
+        pol.model.set_transformations(**tr); pol.old_model.set_transformations(**tr)
+    else:
+        flat = flat + 0.3 * rng.standard_normal(flat.shape).astype(np.float32)
+    pol.set_param_values(flat.copy(), True, True)
+    eng = UpdateEngine(pol)
+    dev = eng.device
+    assert _lib.load().mjrl_policy_fvp_jac_ok(eng.ctx.h, eng.dv.desc_ref()) == 1
+    obs = torch.from_numpy((3 * rng.standard_normal((N, n))).astype(np.float32)).to(dev)
+    params = eng.dv.params("new")
+    tp = O.TruthPolicy(O.GaussianPolicy(n, m, hidden, flat.copy(), **(tr or {})))
+
+    def product(vec, mode):
+        out = torch.zeros(flat.shape[0], dtype=torch.float64, device=dev)
+        eng.cg_flags.zero_()
+        eng.fvp(params, obs, vec, out, cache_mode=mode)
+        return out.cpu().numpy()
+
+    vecs = [torch.from_numpy(rng.standard_normal(flat.shape[0]).astype(np.float32) * s).to(dev) for s in (0.1, 3.0, 1e-3)]
+    ref0 = product(vecs[0], 1)                     # fills h1|h2
+    assert eng._jac_prepare(params, obs)           # fills G1 (once: the second call is a no-op)
+    assert eng._jac_prepare(params, obs)
+    for k, vec in enumerate(vecs):
+        ref = ref0 if k == 0 else product(vec, 2)
+        a, b = product(vec, 3), product(vec, 3)
+        np.testing.assert_array_equal(a, b)
+        assert rel_l2(a, ref) < 3e-6, (k, rel_l2(a, ref))
+        truth = N * tp.fvp(obs.cpu().numpy(), vec.cpu().numpy().astype(np.float64))
+        assert rel_l2(a, truth) < 1e-5, (k, rel_l2(a, truth))
+        # the log_std block is the closed form of the reduce kernel in every mode
+        np.testing.assert_array_equal(a[-m:], ref[-m:])
+
+
+def test_fvp_jacobian_variant_not_offered_for_wide_actions():
+    from mjrl_b200 import _lib
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.algos.engine import UpdateEngine
+    eng = UpdateEngine(MLP(EnvSpec(17, 6, 100, 1), hidden_sizes=(32, 32), seed=5))
+    assert _lib.load().mjrl_policy_fvp_jac_ok(eng.ctx.h, eng.dv.desc_ref()) == 0
+    import torch
+    obs = torch.zeros((64, 17), device=eng.device)
+    assert eng._jac_prepare(eng.dv.params("new"), obs) is False
+
+
 def test_warp_specialised_fvp_variant_in_subprocess():
     """MJRL_B200_FVP_WS=1 selects the warp-specialised cached FVP kernel (csrc/fvp_ws.cu; the switch is
     read once per process, hence the subprocess): same result as the default kernel to fp32 rounding."""
