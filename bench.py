@@ -327,14 +327,29 @@ def run_b200(args):
 
     fvp_fill_ms = time_fvp(1)          # computes the forward pass, fills the activation cache
     cached = hidden and eng._fvp_cache(N) is not None
-    fvp_ms = time_fvp(2) if cached else fvp_fill_ms   # the other 9 of 10 products of an update
+    fvp_rows_ms = time_fvp(2) if cached else fvp_fill_ms   # activation-cached product (fvp_rows.cuh)
+    # small action dimensions: Jacobian-cached product (csrc/fvp_jac.cu) = what the CG solve runs
+    jac = bool(cached and eng._jac_prepare(params, resident.obs))
+    jac_fill_ms = None
+    if jac:
+        fe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(5)]
+        for a, bq in fe:
+            eng._jac_key = None
+            a.record(); eng._jac_prepare(params, resident.obs); bq.record()
+        torch.cuda.synchronize()
+        jac_fill_ms = sorted(a.elapsed_time(bq) for a, bq in fe)[2]
+    fvp_ms = time_fvp(3) if jac else fvp_rows_ms
     hbm_peak, peak_src, sm_max = peaks()
     U = (n * hidden[0] + hidden[0] * hidden[1] + hidden[1] * m) if hidden else n * m
     # MACs per timestep: forward U, tangent U + (h1 h2 + h2 m), backward data h1 h2 + h2 m, weight grads U
     fill_flop = 2.0 * (5 * U - 2 * n * (hidden[0] if hidden else 0)) if hidden else 2.0 * 2 * U
-    fvp_flop = fill_flop - 2.0 * U if cached else fill_flop       # cached: the forward pass is read back
+    # `achieved` uses SURVEY 8(d)'s algorithmic figure of one product (forward + tangent + transpose =
+    # fill_flop); the kernels issue fewer: the activation cache reads the forward pass back (- 2U), the
+    # Jacobian cache also drops the tangent propagation and the backward data products (4U left)
+    fvp_flop = fill_flop
+    issued_flop = (4.0 * U if jac else fill_flop - 2.0 * U) if cached else fill_flop
     hp = (32 if max(hidden) <= 32 else 64) if hidden else 0
-    fvp_bytes = 4.0 * n + (4.0 * 2 * hp if cached else 0.0)       # obs (+ cached h1, h2)
+    fvp_bytes = 4.0 * n + (4.0 * 2 * hp if cached else 0.0) + (4.0 * m * hp if jac else 0.0)   # obs + caches
     ach = N * fvp_bytes / (fvp_ms * 1e-3) / 1e9
     fma_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12          # nominal fp32 FMA peak at max clock
     bf16_peak = None
@@ -346,31 +361,37 @@ def run_b200(args):
     tp = os.path.join(ROOT, "profiles", "r01_fvp_traffic.json")
     if os.path.exists(tp) and args.workload == "C3-hopper":
         tj = json.load(open(tp))
-        key = "dram_bytes_per_timestep_cached" if cached else "dram_bytes_per_timestep"
+        key = ("dram_bytes_per_timestep_jac" if jac else "dram_bytes_per_timestep_cached") if cached \
+            else "dram_bytes_per_timestep"
         if key in tj:
             traffic = float(tj[key]) * N
     ach_tf = N * fvp_flop / (fvp_ms * 1e-3) / 1e12
     roofline = {
-        "kernel": "fvp_rows_kernel<use cache> (analytic Fisher-vector product; %d of the %d products of an "
-                  "update, the first one also computes the forward pass and fills the cache)"
-                  % (CG_ITERS - 1, CG_ITERS) if cached else
+        "kernel": ("fvp_jac_kernel (analytic Fisher-vector product on cached activations and output-Jacobian "
+                   "rows; all %d products of an update, after one jac_fill_kernel pass)" % CG_ITERS) if jac else
+                  ("fvp_rows_kernel<use cache> (analytic Fisher-vector product; %d of the %d products of an "
+                   "update, the first one also computes the forward pass and fills the cache)"
+                   % (CG_ITERS - 1, CG_ITERS)) if cached else
                   "FVP kernel (analytic Fisher-vector product, %d per update)" % CG_ITERS,
         "bound": "tensor", "achieved": ach_tf, "peak": tensor_peak, "unit": "TFLOP/s",
         "frac": ach_tf / tensor_peak, "peak_source": tensor_src + ", dense bf16 burst",
         "traffic": traffic, "traffic_source": "ncu dram bytes of one launch (profiles/r01_fvp_traffic.json) scaled by N",
         "ms_per_launch": fvp_ms, "ms_per_launch_fill": fvp_fill_ms,
-        "algorithmic_flop_per_timestep": fvp_flop, "algorithmic_flop_per_timestep_fill": fill_flop,
+        "ms_per_launch_activation_cached": fvp_rows_ms, "ms_jac_fill": jac_fill_ms,
+        "algorithmic_flop_per_timestep": fvp_flop, "issued_flop_per_timestep": issued_flop,
         "algorithmic_bytes_per_timestep": fvp_bytes,
         "note": "compute bound (%.0f flop per byte, SURVEY F13/H3).  The pass must hold fp32 accuracy "
                 "(1e-4 parity gate, measured ~1e-6), so every algorithmic flop is 3 TF32 tensor flops "
                 "(a_hi*b_hi + a_hi*b_lo + a_lo*b_hi) on mma.sync m16n8k8 (tcgen05 has no fp32-accurate "
-                "kind and its per-instruction issue floor at N=64 gives no gain here, DESIGN.md); ncu "
-                "shows the tensor pipe 62%% busy (profiles/).  TF32 dense peak is half the bf16 peak "
-                "used as denominator.  fp32_fma and hbm give the other two rooflines."
+                "kind and its per-instruction issue floor at N=64 gives no gain here, DESIGN.md).  "
+                "`achieved` counts SURVEY 8(d)'s algorithmic flops of one product; the kernel issues "
+                "`issued_flop_per_timestep` of them (the caches replace the rest by HBM reads), which "
+                "`fp32_fma` and `tensor_flops_issued_tflops` are quoted on.  TF32 dense peak is half the "
+                "bf16 peak used as denominator.  ncu: profiles/r01d_jac_ncu_summary.txt."
                 % (fvp_flop / fvp_bytes),
-        "tensor_flops_issued_tflops": 3.0 * ach_tf,
-        "fp32_fma": {"achieved_tflops": ach_tf, "peak_tflops_nominal": fma_peak,
-                     "frac": ach_tf / fma_peak, "flop_per_timestep": fvp_flop},
+        "tensor_flops_issued_tflops": 3.0 * N * issued_flop / (fvp_ms * 1e-3) / 1e12,
+        "fp32_fma": {"achieved_tflops": N * issued_flop / (fvp_ms * 1e-3) / 1e12, "peak_tflops_nominal": fma_peak,
+                     "frac": N * issued_flop / (fvp_ms * 1e-3) / 1e12 / fma_peak, "flop_per_timestep": issued_flop},
         "hbm": {"achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak},
         "whole_update_hbm": {"bytes_per_timestep": 56 * n + 16 * m + 88,
                              "achieved": N * (56 * n + 16 * m + 88) / (ms_step * 1e-3) / 1e9,

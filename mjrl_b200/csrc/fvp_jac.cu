@@ -69,7 +69,8 @@ __host__ __device__ inline long long h_region_floats(long long ntiles, int HP) {
 // NH independent groups of 4 warps per CTA ("halves" in fvp_rows.cuh; here 2 or 3): with 3 the CTA has 12
 // warps of <= 168 registers, i.e. three instruction streams per SM sub-partition instead of two -- this
 // variant is bound by instruction issue latency, not by the tensor pipe (ncu: pipe 35 % busy with NH = 2).
-template <int HP, int NPK, int NH>
+// MK = static bound of the action dimension (3 or 4): sizes the register-resident rows.
+template <int HP, int NPK, int NH, int MK>
 __global__ void __launch_bounds__(NH * HTHREADS, 1) fvp_jac_kernel(const Args a) {
   constexpr int NTHREADS = NH * HTHREADS;   // shadows pol::NTHREADS
   constexpr int NF = HP / 8, MT = HP / 16;
@@ -271,7 +272,7 @@ __global__ void __launch_bounds__(NH * HTHREADS, 1) fvp_jac_kernel(const Args a)
       uu[1][0] = uu[1][1] = uu[1][2] = uu[1][3] = 0.f;
 #pragma unroll
       for (int ks = 0; ks < NF; ++ks) {
-        const float2 lo = ld_cache(cslot + (2 * (NF + ks)) * 32), hi = ld_cache(cslot + (2 * (NF + ks) + 1) * 32);
+        const float2 lo = ld_g(cslot + (2 * (NF + ks)) * 32), hi = ld_g(cslot + (2 * (NF + ks) + 1) * 32);   // re-read twice below
         Frag4 ah;
         Frag2 bv;
         split_a(ah, lo.x, lo.y, hi.x, hi.y);
@@ -285,32 +286,52 @@ __global__ void __launch_bounds__(NH * HTHREADS, 1) fvp_jac_kernel(const Args a)
       q3[0] = uu[0][0] + uu[1][0] + vj.x; q3[1] = uu[0][1] + uu[1][1] + vj.y;
       q3[2] = uu[0][2] + uu[1][2] + vj.x; q3[3] = uu[0][3] + uu[1][3] + vj.y;
     }
-    // ---- (J v)_j, u_j = fisher_j (J v)_j for both rows of this thread ----------------------------
-    float uA[MJ], uB[MJ];
-    const bool va = rA < rows, vb = rB < rows;
+    // ---- (J v)_j.  Layer-2 part first (it frees q2), then the layer-1 part, whose rows G1_j stay in
+    //      registers for gz1 below: every cached row is read from HBM exactly once per product -------
+    float pa[MK], pb[MK];
 #pragma unroll
-    for (int j = 0; j < MJ; ++j) {
-      uA[j] = 0.f; uB[j] = 0.f;
+    for (int j = 0; j < MK; ++j) {
+      pa[j] = 0.f; pb[j] = 0.f;
       if (j < m) {
-        float pa = 0.f, pb = 0.f;
 #pragma unroll
         for (int nf = 0; nf < NF; ++nf) {
           const float2 w = *reinterpret_cast<const float2*>(sW2 + j * HP + 8 * nf + 2 * c);
-          const float2 lo = ld_g(gslot + (size_t)(j * 2 * NF + 2 * nf) * 32);
-          const float2 hi = ld_g(gslot + (size_t)(j * 2 * NF + 2 * nf + 1) * 32);
-          pa = fmaf(w.x, q2[nf][0], pa); pa = fmaf(w.y, q2[nf][1], pa);
-          pb = fmaf(w.x, q2[nf][2], pb); pb = fmaf(w.y, q2[nf][3], pb);
-          pa = fmaf(lo.x, q1[nf][0], pa); pa = fmaf(lo.y, q1[nf][1], pa);
-          pb = fmaf(hi.x, q1[nf][2], pb); pb = fmaf(hi.y, q1[nf][3], pb);
+          pa[j] = fmaf(w.x, q2[nf][0], pa[j]); pa[j] = fmaf(w.y, q2[nf][1], pa[j]);
+          pb[j] = fmaf(w.x, q2[nf][2], pb[j]); pb[j] = fmaf(w.y, q2[nf][3], pb[j]);
         }
-        pa += __shfl_xor_sync(0xffffffffu, pa, 1); pb += __shfl_xor_sync(0xffffffffu, pb, 1);
-        pa += __shfl_xor_sync(0xffffffffu, pa, 2); pb += __shfl_xor_sync(0xffffffffu, pb, 2);
+      }
+    }
+    float gk[MK][NF][4];
+#pragma unroll
+    for (int j = 0; j < MK; ++j) {
+#pragma unroll
+      for (int nf = 0; nf < NF; ++nf) {
+        float2 lo = make_float2(0.f, 0.f), hi = make_float2(0.f, 0.f);
+        if (j < m) {
+          lo = ld_cache(gslot + (size_t)(j * 2 * NF + 2 * nf) * 32);
+          hi = ld_cache(gslot + (size_t)(j * 2 * NF + 2 * nf + 1) * 32);
+        }
+        gk[j][nf][0] = lo.x; gk[j][nf][1] = lo.y; gk[j][nf][2] = hi.x; gk[j][nf][3] = hi.y;
+        pa[j] = fmaf(lo.x, q1[nf][0], pa[j]); pa[j] = fmaf(lo.y, q1[nf][1], pa[j]);
+        pb[j] = fmaf(hi.x, q1[nf][2], pb[j]); pb[j] = fmaf(hi.y, q1[nf][3], pb[j]);
+      }
+    }
+    // u_j = fisher_j (J v)_j for both rows of this thread (zero past N)
+    float uA[MK], uB[MK];
+    const bool va = rA < rows, vb = rB < rows;
+#pragma unroll
+    for (int j = 0; j < MK; ++j) {
+      uA[j] = 0.f; uB[j] = 0.f;
+      if (j < m) {
+        float sa = pa[j], sb = pb[j];
+        sa += __shfl_xor_sync(0xffffffffu, sa, 1); sb += __shfl_xor_sync(0xffffffffu, sb, 1);
+        sa += __shfl_xor_sync(0xffffffffu, sa, 2); sb += __shfl_xor_sync(0xffffffffu, sb, 2);
         const int src = (lane & ~3) | (j >> 1);
         const float ya = __shfl_sync(0xffffffffu, q3[j & 1], src);
         const float yb = __shfl_sync(0xffffffffu, q3[2 + (j & 1)], src);
         const float fj = sm[L.fisher + j];
-        uA[j] = va ? fj * (pa + ya) : 0.f;
-        uB[j] = vb ? fj * (pb + yb) : 0.f;
+        uA[j] = va ? fj * (sa + ya) : 0.f;
+        uB[j] = vb ? fj * (sb + yb) : 0.f;
         if (c == 0) { sUT[j * LDT + rA] = uA[j]; sUT[j * LDT + rB] = uB[j]; }
       }
     }
@@ -318,19 +339,17 @@ __global__ void __launch_bounds__(NH * HTHREADS, 1) fvp_jac_kernel(const Args a)
     float gz[NF][4];
 #pragma unroll
     for (int nf = 0; nf < NF; ++nf) {
-      const float2 h2lo = ld_g(cslot + (2 * (NF + nf)) * 32), h2hi = ld_g(cslot + (2 * (NF + nf) + 1) * 32);   // L1 / L2 hit
+      const float2 h2lo = ld_g(cslot + (2 * (NF + nf)) * 32), h2hi = ld_g(cslot + (2 * (NF + nf) + 1) * 32);   // L1 hit
       float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
       gz[nf][0] = gz[nf][1] = gz[nf][2] = gz[nf][3] = 0.f;
 #pragma unroll
-      for (int j = 0; j < MJ; ++j)
+      for (int j = 0; j < MK; ++j)
         if (j < m) {
           const float2 w = *reinterpret_cast<const float2*>(sW2 + j * HP + 8 * nf + 2 * c);
-          const float2 lo = ld_g(gslot + (size_t)(j * 2 * NF + 2 * nf) * 32);
-          const float2 hi = ld_g(gslot + (size_t)(j * 2 * NF + 2 * nf + 1) * 32);
           s0 = fmaf(uA[j], w.x, s0); s1 = fmaf(uA[j], w.y, s1);
           s2 = fmaf(uB[j], w.x, s2); s3 = fmaf(uB[j], w.y, s3);
-          gz[nf][0] = fmaf(uA[j], lo.x, gz[nf][0]); gz[nf][1] = fmaf(uA[j], lo.y, gz[nf][1]);
-          gz[nf][2] = fmaf(uB[j], hi.x, gz[nf][2]); gz[nf][3] = fmaf(uB[j], hi.y, gz[nf][3]);
+          gz[nf][0] = fmaf(uA[j], gk[j][nf][0], gz[nf][0]); gz[nf][1] = fmaf(uA[j], gk[j][nf][1], gz[nf][1]);
+          gz[nf][2] = fmaf(uB[j], gk[j][nf][2], gz[nf][2]); gz[nf][3] = fmaf(uB[j], gk[j][nf][3], gz[nf][3]);
         }
       float* p0 = sPB + (8 * nf + 2 * c) * LDT;
       p0[rA] = s0 * (1.f - h2lo.x * h2lo.x); p0[LDT + rA] = s1 * (1.f - h2lo.y * h2lo.y);
@@ -484,7 +503,7 @@ __global__ void __launch_bounds__(256, 2) jac_fill_kernel(const float* __restric
                                                         int h2n, float* __restrict__ cache, long long ntiles) {
   constexpr int NF = HP / 8, LDW = HP + 8, PL1 = HP * LDW, G = 2;
   extern __shared__ __align__(16) float sm[];
-  float* sW1 = sm;                    // hi plane | lo plane
+  float* sW1 = sm;                    // W1 TRANSPOSED ([in][out]), tf32 hi plane | lo plane
   float* sW2 = sm + 2 * HP * LDW;     // [MJ][HP]
   const Flat F(n, m, h1n, h2n);
   const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, c = lane & 3, warp = tid >> 5;
@@ -494,7 +513,7 @@ __global__ void __launch_bounds__(256, 2) jac_fill_kernel(const float* __restric
     const int o = i / h1n, k = i - o * h1n;
     uint32_t hi, lo;
     split_tf32(__ldg(params + F.oW1 + i), hi, lo);
-    sW1[o * LDW + k] = __uint_as_float(hi); sW1[PL1 + o * LDW + k] = __uint_as_float(lo);
+    sW1[k * LDW + o] = __uint_as_float(hi); sW1[PL1 + k * LDW + o] = __uint_as_float(lo);   // W1^T [in][out]
   }
   for (int i = tid; i < m * h2n; i += 256) {
     const int j = i / h2n, k = i - j * h2n;
@@ -528,7 +547,7 @@ __global__ void __launch_bounds__(256, 2) jac_fill_kernel(const float* __restric
           Frag2 bw[G];
 #pragma unroll
           for (int i = 0; i < G; ++i)
-            load_b_rows(bw[i], sW1 + (8 * ks + 2 * c) * LDW + 8 * (n0 + i) + g, LDW, PL1);   // B[k = o][n = i] = W1[o][i]
+            load_b(bw[i], sW1 + (8 * (n0 + i) + g) * LDW + 8 * ks + 2 * c, PL1);   // B[k = o][n = i] = W1[o][i] = W1^T[i][o]: one 8-byte load
 #pragma unroll
           for (int term = 0; term < 3; ++term)
 #pragma unroll
@@ -573,9 +592,9 @@ long long jac_cache_floats(int m, int h1, int h2, long long N) {
   return ntiles * rows::TSR * (long long)m * HP;
 }
 
-template <int HP, int NPK, int NH>
+template <int HP, int NPK, int NH, int MK>
 static int launch_jac_one(const Args& a, int grid, size_t smem, cudaStream_t s) {
-  auto kern = jac::fvp_jac_kernel<HP, NPK, NH>;
+  auto kern = jac::fvp_jac_kernel<HP, NPK, NH, MK>;
   static size_t attr = 0;
   if (smem > attr) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -592,11 +611,9 @@ int launch_fvp_jac(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
   size_t smem;
   if (!a.cache || !jac_fits(ctx, a.n, a.m, a.h1, a.h2, &HP, &NPK, &smem)) return -1;
   const Flat F(a.n, a.m, a.h1, a.h2);
-  // two groups of 4 warps per CTA; MJRL_B200_FVP_JAC_NH=3 asks for three when their planes fit
-  static const int nh_env = getenv("MJRL_B200_FVP_JAC_NH") ? atoi(getenv("MJRL_B200_FVP_JAC_NH")) : 0;
-  const size_t smem3 = sizeof(float) * (size_t)jac::JLayout(HP, NPK, a.n, 3).total;
-  const int NH = (nh_env != 3 || smem3 + 64 > (size_t)ctx->max_smem_optin) ? 2 : 3;   // 3 is opt-in: measured slower
-  if (NH == 3) smem = smem3;
+  // two groups of 4 warps per CTA.  (Three groups -- 12 warps of 168 registers, 222 KB of shared memory --
+  // measured slower: 0.85 ms against 0.63 ms per product on the Hopper shape)
+  constexpr int NH = 2;
   const long long ntiles = (a.N + NH * rows::TSR - 1) / (NH * rows::TSR);
   int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
   if (grid < 1) grid = 1;
@@ -606,7 +623,7 @@ int launch_fvp_jac(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
   if (!a.partials) return MJRL_E_STATE;
 #define JAC_CASE(H, K)                                                           \
   if (HP == H && NPK == K)                                                       \
-    return NH == 3 ? launch_jac_one<H, K, 3>(a, grid, smem, s) : launch_jac_one<H, K, 2>(a, grid, smem, s)
+    return a.m <= 3 ? launch_jac_one<H, K, NH, 3>(a, grid, smem, s) : launch_jac_one<H, K, NH, 4>(a, grid, smem, s)
   JAC_CASE(64, 1); JAC_CASE(64, 2); JAC_CASE(64, 3);
   JAC_CASE(32, 1); JAC_CASE(32, 2); JAC_CASE(32, 3);
 #undef JAC_CASE
