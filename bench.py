@@ -274,6 +274,10 @@ def run_b200(args):
         reset()
         flush.zero_()
         torch.cuda.synchronize()
+        if world > 1:
+            # reset() and the L2 flush are outside the event brackets on every rank; without a common start a
+            # rank that finished them earlier would count its wait for the other ranks' host work as step time
+            td.barrier()
         ev[k][0].record()
         step_resident()
         ev[k][1].record()
