@@ -19,6 +19,11 @@ from .. import _lib
 from .._lib import CGState, c_double, c_float, c_i64, c_int, c_void_p, ptr, stream_ptr
 
 
+# Below this many local timesteps a CG solve is launch-latency sized and the extra fill pass of the
+# Jacobian-cached product does not pay (C2 swimmer, 10k timesteps: 1.26 ms with, 1.28 without).
+JAC_MIN_N = int(os.environ.get("MJRL_B200_FVP_JAC_MIN_N", "32768"))
+
+
 class Dist:
     """Sum all-reduce of small device tensors across the ranks of a torch.distributed group; identity
     when the process group is absent (single GPU).
@@ -221,7 +226,7 @@ class UpdateEngine:
             elif self._cache_key is not None and self._cache_key == self._key(params, o):
                 # h1|h2 filled by the gradient pass (or the first product) at these tensors; small action
                 # dimensions also cache the output-Jacobian rows and run the cheaper product (fvp_jac.cu)
-                mode = 3 if self._jac_prepare(params, o) else 2
+                mode = 3 if (o.shape[0] >= JAC_MIN_N and self._jac_prepare(params, o)) else 2
             else:
                 mode = 1
             peer = self.dist.peer if self.dist.world > 1 else None

@@ -70,9 +70,14 @@ def test_forward_surrogate_gradient_fvp(golden):
     assert rel_l2(pol.log_likelihood(obs, act), g["pert_LL"]) < 1e-5
 
 
-def test_npg_update_and_cg_protocol(golden):
+@pytest.mark.parametrize("jac_min_n", [0, 1 << 30])
+def test_npg_update_and_cg_protocol(golden, jac_min_n, monkeypatch):
+    """jac_min_n = 0: the CG solve runs the Jacobian-cached product (act_dim <= 4 shapes) whatever the batch
+    size; 1 << 30: the activation-cached one.  Both must pass the same gates."""
+    from mjrl_b200.algos import engine
     from mjrl_b200.algos.npg_cg import NPG
     from oracle import mjrl_oracle as O
+    monkeypatch.setattr(engine, "JAC_MIN_N", jac_min_n)
     g = golden
     p1 = prepared_paths(g)
     pol = make_policy(g)
