@@ -66,6 +66,12 @@ int mjrl_adv_plain(mjrl_ctx* ctx, const double* returns, const double* baseline,
 /* moments[0..3] = {N, sum x, sum (x-mean)^2, mean} in fp64, deterministic.  Used for
  * whitening (npg_cg.py:91) and normalize=True (process_samples.py:14-19,30-35). */
 int mjrl_moments(mjrl_ctx* ctx, const double* x, int64_t N, double* moments4, void* stream);
+/* The same in two calls for a path-sharded batch: stage 0 writes the LOCAL {N, sum} (and the local mean);
+ * the caller all-reduces moments4[0..1]; stage 1 sets moments4[3] = sum/N from them and writes the local
+ * centred sum of squares to moments4[2], which the caller all-reduces.  Without the all-reduces the two
+ * stages give mjrl_moments' bits. */
+int mjrl_moments_stage(mjrl_ctx* ctx, const double* x, int64_t N, double* moments4, int32_t stage,
+                       void* stream);
 /* x <- (x - mean)/(std + eps) in place (fp64), std = sqrt(moments[2]/N). */
 int mjrl_normalize_inplace(mjrl_ctx* ctx, double* x, int64_t N, const double* moments4,
                            double eps, void* stream);

@@ -128,14 +128,12 @@ class UpdateEngine:
             self.ctx.call("mjrl_moments", ptr(adv64), c_i64(N), ptr(self.mom), stream_ptr())
             self.launches += 4
         else:
-            # two-pass global moments: all-reduce (N, sum) then the centred sum of squares
-            part = torch.stack([torch.tensor(float(N), dtype=torch.float64, device=self.device),
-                                adv64.sum()])
-            self.dist.allreduce(part)
-            mean = part[1] / part[0]
-            ss = ((adv64 - mean) ** 2).sum().reshape(1)
-            self.dist.allreduce(ss)
-            self.mom.copy_(torch.stack([part[0], part[1], ss[0], mean]))
+            # two-pass global moments: all-reduce {N, sum}, then the centred sums of squares
+            self.ctx.call("mjrl_moments_stage", ptr(adv64), c_i64(N), ptr(self.mom), c_int(0), stream_ptr())
+            self.dist.allreduce(self.mom[0:2])
+            self.ctx.call("mjrl_moments_stage", ptr(adv64), c_i64(N), ptr(self.mom), c_int(1), stream_ptr())
+            self.dist.allreduce(self.mom[2:3])
+            self.launches += 5
         self.ctx.call("mjrl_whiten_f32", ptr(adv64), c_i64(N), ptr(self.mom), c_double(eps),
                       c_double(scale), ptr(w), stream_ptr())
         self.launches += 1

@@ -305,6 +305,29 @@ int mjrl_moments(mjrl_ctx* ctx, const double* x, int64_t N, double* mom, void* s
   return mjrl_check_launch("moments");
 }
 
+__global__ void moment_mean_kernel(double* __restrict__ mom) {
+  mom[3] = mom[0] > 0.0 ? mom[1] / mom[0] : 0.0;
+}
+
+// The two passes of mjrl_moments as separate calls, so that a path-sharded batch can all-reduce
+// {N, sum} between them and the centred squares afterwards (global moments of npg_cg.py:91).
+int mjrl_moments_stage(mjrl_ctx* ctx, const double* x, int64_t N, double* mom, int32_t stage, void* stream) {
+  MJRL_REQUIRE(ctx && x && mom && N > 0 && (stage == 0 || stage == 1), MJRL_E_ARG, "moments_stage: bad argument");
+  int grid = ew_grid(ctx, N, 256 * 8);
+  double* part = (double*)mjrl_scratch(ctx, sizeof(double) * grid);
+  if (!part) return MJRL_E_STATE;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (stage == 0) {
+    moment_partial_kernel<false><<<grid, 256, 0, s>>>(x, N, mom, part);
+    moment_final_kernel<false><<<1, 256, 0, s>>>(part, grid, N, mom);
+  } else {
+    moment_mean_kernel<<<1, 1, 0, s>>>(mom);   // mean of the (all-reduced) {N, sum}
+    moment_partial_kernel<true><<<grid, 256, 0, s>>>(x, N, mom, part);
+    moment_final_kernel<true><<<1, 256, 0, s>>>(part, grid, N, mom);
+  }
+  return mjrl_check_launch("moments_stage");
+}
+
 int mjrl_normalize_inplace(mjrl_ctx* ctx, double* x, int64_t N, const double* mom, double eps,
                            void* stream) {
   MJRL_REQUIRE(ctx && x && mom && N > 0, MJRL_E_ARG, "normalize: bad argument");

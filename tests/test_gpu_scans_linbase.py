@@ -209,3 +209,38 @@ def test_linbase_kernels_unaligned_obs_base():
     G = out["a"][0][:F * (F + 1)].reshape(F, F + 1)
     np.testing.assert_allclose(G[:, :F], X.T @ X, rtol=1e-10, atol=1e-8)
     np.testing.assert_allclose(G[:, F], X.T @ ret.cpu().numpy(), rtol=1e-10, atol=1e-8)
+
+
+def test_staged_moments_equal_single_call_and_combine_across_shards():
+    """mjrl_moments_stage (the sharded whitening of algos/engine.py): without all-reduces the two stages give
+    mjrl_moments' bits; with the {N, sum} and centred-square sums of two shards added between / after the
+    stages they give the moments of the concatenated batch (numpy mean / std of npg_cg.py:91)."""
+    import torch
+    from mjrl_b200 import _lib
+    from mjrl_b200._lib import c_i64, c_int, ptr, stream_ptr
+    ctx = _lib.context()
+    dev = torch.device("cuda", ctx.device)
+    rng = np.random.default_rng(12)
+    x = rng.standard_normal(70001) * 3.0 + 0.7
+    d_x = torch.from_numpy(x).to(dev)
+    one = torch.zeros(4, dtype=torch.float64, device=dev)
+    two = torch.zeros(4, dtype=torch.float64, device=dev)
+    ctx.call("mjrl_moments", ptr(d_x), c_i64(x.size), ptr(one), stream_ptr())
+    ctx.call("mjrl_moments_stage", ptr(d_x), c_i64(x.size), ptr(two), c_int(0), stream_ptr())
+    ctx.call("mjrl_moments_stage", ptr(d_x), c_i64(x.size), ptr(two), c_int(1), stream_ptr())
+    np.testing.assert_array_equal(one.cpu().numpy(), two.cpu().numpy())
+    # two shards of unequal size
+    cut = 26000
+    shards = [torch.from_numpy(x[:cut].copy()).to(dev), torch.from_numpy(x[cut:].copy()).to(dev)]
+    moms = [torch.zeros(4, dtype=torch.float64, device=dev) for _ in shards]
+    for s, m in zip(shards, moms):
+        ctx.call("mjrl_moments_stage", ptr(s), c_i64(s.numel()), ptr(m), c_int(0), stream_ptr())
+    tot = moms[0][0:2] + moms[1][0:2]                 # what Dist.allreduce does to the slice
+    for m in moms:
+        m[0:2] = tot
+    for s, m in zip(shards, moms):
+        ctx.call("mjrl_moments_stage", ptr(s), c_i64(s.numel()), ptr(m), c_int(1), stream_ptr())
+    ss = float((moms[0][2] + moms[1][2]).item())
+    N, mean = float(moms[0][0].item()), float(moms[0][3].item())
+    assert N == x.size and abs(mean - x.mean()) < 1e-13 * max(1.0, abs(x.mean()))
+    assert abs(np.sqrt(ss / N) - x.std()) < 1e-12 * x.std()
