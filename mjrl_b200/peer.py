@@ -105,6 +105,9 @@ def connect_process_group(ctx, td, group, max_count):
             pg.close()
         return None, why or "a peer rank could not map the blocks"
     td.barrier(group=group)      # every block is zeroed and mapped before the first flag is raised
+    # ranks run their host code independently between exchanges (data staging, Python jitter, 8 processes
+    # sharing the host cores): give a late peer a minute before declaring the update invalid
+    pg.set_timeout(float(os.environ.get("MJRL_B200_PEER_TIMEOUT", "60")))
     return pg, ""
 
 
