@@ -311,6 +311,42 @@ def run_b200(args):
     e2e = {"value": N * world / e2e_s, "unit": "timesteps/s", "ms_per_step": 1e3 * e2e_s,
            "h2d_bytes_per_step": int(b.h2d_bytes), "d2h_bytes_per_step": int(d2h)}
 
+    # ---- strong scaling (north_star: ONE batch of the named size sharded over the GPUs) -----------
+    # The headline `value` is weak scaling (the named batch per GPU).  Here the same N timesteps are split
+    # by whole paths over the ranks: N / world per GPU, same kernels, same exchanges.
+    strong = None
+    if world > 1 and not use_mlp:
+        Ns = N // world
+        sb_h = syn.make_flat_batch(Ns, n, m, horizon, 5000 + rank, flat0, hidden)
+        sbatch = PathBatch(pin(sb_h["observations"]), pin(sb_h["actions"]), pin(sb_h["rewards"]),
+                           sb_h["path_offsets"], sb_h["terminated"], device=local)
+
+        def step_strong():
+            sbatch.returns = sbatch.baseline = sbatch.adv = None
+            return agent.train_step(Ns, gamma=GAMMA, gae_lambda=LAM, paths=sbatch)
+
+        for _ in range(3):
+            reset(); step_strong()
+        barrier()
+        sev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+               for _ in range(args.steps)]
+        for k in range(args.steps):
+            reset()
+            flush.zero_()
+            torch.cuda.synchronize()
+            td.barrier()
+            sev[k][0].record()
+            step_strong()
+            sev[k][1].record()
+        barrier()
+        ts_ = torch.tensor([sum(a.elapsed_time(bq) for a, bq in sev)], dtype=torch.float64, device=dev)
+        td.all_reduce(ts_, op=td.ReduceOp.MAX)
+        s_ms = float(ts_.item()) / args.steps
+        strong = {"timesteps_total": Ns * world, "timesteps_per_gpu": Ns, "ms_per_step": s_ms,
+                  "value": Ns * world / (s_ms * 1e-3), "unit": "timesteps/s",
+                  "whole_update_hbm_frac": Ns * world * (56 * n + 16 * m + 88) / (s_ms * 1e-3) / 1e9 / (world * peaks()[0]),
+                  "note": "same update on ONE batch of the named size split over the ranks by whole paths"}
+
     # ---- roofline of the dominant kernel: the FVP pass (10 of them per update) -----------------
     eng = agent._engine()
     reset()
@@ -434,6 +470,7 @@ def run_b200(args):
                        "l2": "256 MB buffer written between timed steps (outside the event brackets)",
                        "policy_reset_each_step": True},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
+            **({"strong_scaling": strong} if strong else {}),
             "cpu_baseline": cb, "mlp_baseline": mlp_extra}))
     if world > 1:
         td.destroy_process_group()

@@ -340,6 +340,16 @@ int mjrl_peer_allreduce_f64(mjrl_ctx* ctx, mjrl_peer* peer, const double* src, d
 /* mjrl_cg_update with z_sum = sum over ranks of mjrl_peer_slot(epoch)[0..d) */
 int mjrl_cg_update_peer(mjrl_ctx* ctx, mjrl_peer* peer, const mjrl_cg_state* state, int64_t d,
                         double inv_count, double damping, double residual_tol, int64_t epoch, void* stream);
+/* cg_solve.py:3-22 in one call: mjrl_cg_init(b, b_scale), then `iters` x ( mjrl_policy_fvp_cached(vec =
+ * state->p32) -> mjrl_cg_update ), enqueued from C with no host work in between.  The first product uses
+ * cache_mode `mode_first`, the others `mode_rest`; jac_fill_after_first != 0 runs mjrl_policy_fvp_jac_fill
+ * after the first product (mode_first 1, mode_rest 3).  peer != NULL: the products write into the exchange
+ * slots of epochs epoch0+1 .. epoch0+iters and the updates are mjrl_cg_update_peer (the caller advances its
+ * epoch counter by `iters`); peer == NULL: single rank. */
+int mjrl_cg_solve(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params, const float* obs, int64_t N,
+                  const mjrl_cg_state* state, const double* b, double b_scale, int32_t iters, double inv_count,
+                  double damping, double residual_tol, float* cache, int32_t mode_first, int32_t mode_rest,
+                  int32_t jac_fill_after_first, mjrl_peer* peer, int64_t epoch0, void* stream);
 /* synchronous: *err_out = 1 when some wait timed out since creation */
 int mjrl_peer_status(mjrl_peer* peer, int32_t* err_out);
 int mjrl_peer_destroy(mjrl_peer* peer);

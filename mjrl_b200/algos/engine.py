@@ -211,6 +211,10 @@ class UpdateEngine:
                  subsample=None):
         """cg_solve.py:3-22 entirely on device; b = self.grad[:d]*g_scale.  Returns self.cg_x."""
         d = self.dv.d
+        peer = self.dist.peer if self.dist.world > 1 else None
+        if subsample is None and trace is None and (self.dist.world == 1 or peer is not None) \
+                and os.environ.get("MJRL_B200_CG_LOOP", "c") == "c":
+            return self._cg_solve_native(params, obs, g_scale, N_global, iters, damping, tol, peer)
         self.ctx.call("mjrl_cg_init", ctypes.byref(self.cg), c_i64(d), ptr(self.grad), c_double(g_scale),
                       stream_ptr())
         self.launches += 1
@@ -247,6 +251,41 @@ class UpdateEngine:
             self.launches += 1
             if trace is not None:
                 trace.append(self.cg_x.cpu().numpy().copy())
+        return self.cg_x
+
+    def _cg_solve_native(self, params, obs, g_scale, N_global, iters, damping, tol, peer):
+        """The same solve through ONE C-ABI call (`mjrl_cg_solve`): the host loop over product / update
+        launches runs in C, which matters when the batch is small enough for the update to be bound by the
+        rate at which Python can enqueue kernels (small configs, strong scaling)."""
+        N = obs.shape[0]
+        key = self._key(params, obs)
+        cache = self._fvp_cache(N)
+        fill_jac = 0
+        if cache is None:
+            first = rest = 0
+        elif self._cache_key is not None and self._cache_key == key:
+            first = rest = 3 if (N >= JAC_MIN_N and self._jac_prepare(params, obs)) else 2
+        else:
+            first, rest = 1, 2
+            if N >= JAC_MIN_N and iters > 1:
+                if self._jac_ok is None:
+                    self._jac_ok = bool(_lib.load().mjrl_policy_fvp_jac_ok(self.ctx.h, self.dv.desc_ref()))
+                if self._jac_ok:
+                    rest, fill_jac = 3, 1
+                    self._jac_key = key
+            self._cache_key = key
+        epoch0 = 0
+        if peer is not None:
+            epoch0 = peer.epoch
+            peer.epoch += iters
+            peer.exchanges += iters
+            self.dist.calls += iters
+        self.ctx.call("mjrl_cg_solve", self.dv.desc_ref(), ptr(params), ptr(obs), c_i64(N), ctypes.byref(self.cg),
+                      ptr(self.grad), c_double(g_scale), c_int(iters), c_double(1.0 / N_global),
+                      c_double(damping), c_double(tol), ptr(cache), c_int(first), c_int(rest), c_int(fill_jac),
+                      peer.h if peer is not None else c_void_p(0), c_i64(epoch0), stream_ptr())
+        self.launches += 1 + 3 * iters + fill_jac
+        self.ctx.launches += 3 * iters + fill_jac     # ctx.call counted one
         return self.cg_x
 
     def step(self, curr, g_scale, delta, const_alpha=None, alpha_scale=1.0):

@@ -318,6 +318,36 @@ int mjrl_cg_update_peer(mjrl_ctx* ctx, mjrl_peer* p, const mjrl_cg_state* st, in
   return mjrl_check_launch("cg_update_peer");
 }
 
+// cg_solve.py:3-22 as ONE host call: cg_init, then `iters` x (product -> partial reduce -> CG update [fused with
+// the peer all-reduce]) enqueued back to back from C.  A Python caller pays one ctypes transition instead of
+// 2 * iters + 1: at small batches (and under strong scaling) the update is bound by how fast the host can enqueue.
+int mjrl_cg_solve(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params, const float* obs, int64_t N,
+                  const mjrl_cg_state* st, const double* b, double b_scale, int32_t iters, double inv_count,
+                  double damping, double residual_tol, float* cache, int32_t mode_first, int32_t mode_rest,
+                  int32_t jac_fill_after_first, mjrl_peer* peer, int64_t epoch0, void* stream) {
+  MJRL_REQUIRE(ctx && desc && params && obs && st && b && N > 0 && iters >= 0, MJRL_E_ARG, "cg_solve: bad argument");
+  MJRL_REQUIRE(peer == nullptr || (peer->connected && epoch0 >= 0), MJRL_E_ARG, "cg_solve: peer not connected");
+  const int64_t d = mjrl_policy_param_count(desc);
+  MJRL_REQUIRE(d > 0, MJRL_E_SHAPE, "cg_solve: bad policy description");
+  int rc = mjrl_cg_init(ctx, st, d, b, b_scale, stream);
+  if (rc) return rc;
+  for (int32_t k = 0; k < iters; ++k) {
+    const int64_t epoch = epoch0 + k + 1;
+    double* out = peer ? mjrl_peer_slot(peer, epoch) : st->z;
+    rc = mjrl_policy_fvp_cached(ctx, desc, params, obs, N, st->p32, out, st->flags, cache,
+                                k == 0 ? mode_first : mode_rest, stream);
+    if (rc) return rc;
+    if (k == 0 && jac_fill_after_first) {
+      rc = mjrl_policy_fvp_jac_fill(ctx, desc, params, N, cache, stream);
+      if (rc) return rc;
+    }
+    rc = peer ? mjrl_cg_update_peer(ctx, peer, st, d, inv_count, damping, residual_tol, epoch, stream)
+              : mjrl_cg_update(ctx, st, d, inv_count, damping, residual_tol, stream);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
 int mjrl_peer_status(mjrl_peer* p, int32_t* err_out) {
   MJRL_REQUIRE(p && err_out, MJRL_E_ARG, "peer_status: bad argument");
   cudaSetDevice(p->device);
