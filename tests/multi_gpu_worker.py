@@ -49,6 +49,40 @@ def run(world_mode):
 PEER_NOTE = "-"
 
 
+def run_trpo_dapg(world_mode):
+    """TRPO (line search: one exchange per trial) and DAPG (demo term on top of the sharded gradient) under
+    the same sharding: updated parameters and the backtrack count must not depend on the rank count."""
+    from mjrl_b200.algos.trpo import TRPO
+    from mjrl_b200.algos.dapg import DAPG
+    g = load_golden("c3_hopper_mid")
+    spec = EnvSpec(g["n"], g["m"], g["horizon"], 1)
+    out = {}
+    for name in ("trpo", "dapg"):
+        pol = MLP(spec, hidden_sizes=g["hidden"], seed=123)
+        pol.model.set_transformations(**g["transforms"]); pol.old_model.set_transformations(**g["transforms"])
+        pol.set_param_values(g["params"].copy())
+        base = LinearBaseline(spec)
+        base._coeffs = g["fit0_coeffs"].copy()
+        paths = syn.flat_to_paths(batch_of(g, "b1_"))
+        if name == "trpo":
+            ag = TRPO(None, pol, base, kl_dist=0.002, FIM_invert_args={"iters": 10, "damping": 1e-4})
+        else:
+            demos = syn.flat_to_paths(batch_of(g, "b1_"))[:3]      # replicated on every rank
+            ag = DAPG(None, pol, base, demo_paths=demos, kl_dist=0.01, lam_0=1.0, lam_1=0.95,
+                      FIM_invert_args={"iters": 10, "damping": 1e-4})
+        if world_mode:
+            ag.dist = Dist()
+            paths = shard_paths(paths, ag.dist.rank, ag.dist.world)
+        else:
+            ag.dist = Dist.__new__(Dist); ag.dist.td = None; ag.dist.world = 1; ag.dist.rank = 0; ag.dist.calls = 0
+            ag.dist.group = None
+        drop_cache()
+        ag.train_step(len(paths), gamma=g["gamma"], gae_lambda=g["gae_lambda"], paths=paths)
+        out[name] = (pol.get_param_values().astype(np.float64) - g["params"],
+                     len(ag.last_update.get("trials", [])) if name == "trpo" else 0)
+    return out
+
+
 def run_mlpbase(world_mode, rank, world):
     """MLPBaseline.fit is replicas-only: every rank gathers all rows and runs the same chain, so the
     result must equal (bit for bit) a single-GPU fit on the shards concatenated in rank order."""
@@ -78,13 +112,20 @@ if __name__ == "__main__":
     torch.cuda.set_device(local)
     step_multi, coef_multi, g = run(True)
     mlp_multi, errs_multi, steps_multi = run_mlpbase(True, rank, world)
+    td_multi = run_trpo_dapg(True)
     if rank == 0:
+        td_one = run_trpo_dapg(False)
+        r_trpo = rel_l2(td_multi["trpo"][0], td_one["trpo"][0])
+        r_dapg = rel_l2(td_multi["dapg"][0], td_one["dapg"][0])
+        td_ok = r_trpo < 1e-4 and r_dapg < 1e-4 and td_multi["trpo"][1] == td_one["trpo"][1]
+        print("TRPO_DAPG_%s trpo_rel=%.3e (%d trials) dapg_rel=%.3e" % ("OK" if td_ok else "FAIL", r_trpo,
+                                                                         td_multi["trpo"][1], r_dapg))
         step_one, coef_one, _ = run(False)
         mlp_one, errs_one, steps_one = run_mlpbase(False, rank, world)
         r_step, r_coef = rel_l2(step_multi, step_one), rel_l2(coef_multi, coef_one)
         mlp_same = steps_multi == steps_one and np.array_equal(mlp_multi, mlp_one)
         errs_ok = all(abs(a - b) < 1e-9 * max(1.0, abs(b)) for a, b in zip(errs_multi, errs_one))
-        ok = r_step < 1e-4 and r_coef < 1e-6 and mlp_same and errs_ok
+        ok = r_step < 1e-4 and r_coef < 1e-6 and mlp_same and errs_ok and td_ok
         print("MULTI_%s world=%d step_rel=%.3e coef_rel=%.3e mlpbase_bitexact=%s (%d steps) errs_ok=%s peer=[%s]"
               % ("OK" if ok else "FAIL", world, r_step, r_coef, mlp_same, steps_multi, errs_ok, PEER_NOTE))
     if world > 1:
