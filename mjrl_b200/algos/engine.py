@@ -73,6 +73,29 @@ class Dist:
             self.calls += 1
         return t
 
+    def allgather_rows(self, t):
+        """Rows of a [N_r, C] device tensor of every rank, concatenated in rank order on every rank
+        (ranks own different row counts).  Used by the replicas-only serial chains (PPO minibatch epochs),
+        never by the sharded passes.  Returns (tensor [sum N_r, C], [N_r per rank])."""
+        if self.td is None or self.world == 1:
+            return t, [int(t.shape[0])]
+        n_local = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+        sizes = [torch.zeros_like(n_local) for _ in range(self.world)]
+        self.td.all_gather(sizes, n_local, group=self.group)
+        sizes = [int(v.item()) for v in sizes]
+        padded = torch.zeros((max(sizes),) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        padded[:t.shape[0]] = t
+        parts = [torch.empty_like(padded) for _ in range(self.world)]
+        self.td.all_gather(parts, padded, group=self.group)
+        return torch.cat([p[:k] for p, k in zip(parts, sizes)]), sizes
+
+    def broadcast0(self, t):
+        """Rank 0's tensor on every rank (in place)."""
+        if self.td is not None and self.world > 1:
+            src = self.td.get_global_rank(self.group, 0) if self.group is not None else 0
+            self.td.broadcast(t, src=src, group=self.group)
+        return t
+
     def check(self):
         """After a host synchronisation: raise if a peer exchange timed out."""
         if self.peer is not None:

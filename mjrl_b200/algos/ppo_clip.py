@@ -64,10 +64,10 @@ class PPO(BatchREINFORCE):
 
     def train_from_paths(self, paths, minibatches=None):
         eng, batch, w, stats = self._prepare(paths)
-        if eng.dist.world > 1:
-            raise NotImplementedError("PPO's minibatch chain is serial (replicas only); run it on one rank")
+        world = eng.dist.world
         d, m, n = eng.dv.d, eng.dv.m, eng.dv.n
         N = batch.N
+        N_glob = self._global_n(eng, batch) if world > 1 else float(N)
         ctx, dev = eng.ctx, eng.device
         ts = timer.time()
         p_old = eng.dv.params("old")
@@ -78,10 +78,31 @@ class PPO(BatchREINFORCE):
         p_old_eff = p_old.clone()
         old_ll, old_mean = eng.old_cache(p_old, batch.obs, batch.act)
         surr_before_dev = eng.evaluate(params, batch.obs, batch.act, w, old_ll, old_mean, p_old[d - m:],
-                                       float(N))[0:1].clone()
-        idx = self.minibatch_indices(N) if minibatches is None else np.asarray(minibatches, dtype=np.int32)
-        B = idx.shape[1] if idx.size else self.mb_size
-        d_idx = torch.from_numpy(np.ascontiguousarray(idx)).to(dev)
+                                       N_glob)[0:1].clone()
+        # The minibatch chain samples the GLOBAL batch (ppo_clip.py:89) and is serial: with several ranks it
+        # runs as REPLICAS -- every rank gathers all rows (rank order), rank 0 draws the minibatches, and
+        # every rank runs the identical deterministic chain; the full-batch passes stay sharded.
+        c_obs, c_act, c_w, c_oll, Nc = batch.obs, batch.act, w, old_ll, N
+        if world > 1:
+            packed, sizes = eng.dist.allgather_rows(
+                torch.cat([batch.obs, batch.act, w[:, None], old_ll[:, None]], dim=1))
+            Nc = int(sum(sizes))
+            c_obs, c_act = packed[:, :n].contiguous(), packed[:, n:n + m].contiguous()
+            c_w, c_oll = packed[:, n + m].contiguous(), packed[:, n + m + 1].contiguous()
+        if minibatches is not None:
+            idx = np.asarray(minibatches, dtype=np.int32)
+            d_idx = torch.from_numpy(np.ascontiguousarray(idx)).to(dev)
+        else:
+            steps = self.epochs * int(Nc / self.mb_size)
+            if world == 1 or eng.dist.rank == 0:
+                idx = self.minibatch_indices(Nc)
+                d_idx = torch.from_numpy(np.ascontiguousarray(idx)).to(dev)
+            else:
+                d_idx = torch.empty((steps, self.mb_size), dtype=torch.int32, device=dev)
+            if world > 1 and steps > 0:
+                eng.dist.broadcast0(d_idx)
+            idx = d_idx      # only its shape is used below
+        B = idx.shape[1] if idx.shape[0] else self.mb_size
         am, av = self._adam(eng)
         f32 = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
         mb_obs, mb_act, mb_adv, mb_oll, mb_ll, mb_w = f32(B, n), f32(B, m), f32(B), f32(B), f32(B), f32(B)
@@ -89,15 +110,15 @@ class PPO(BatchREINFORCE):
         st = stream_ptr()
         for s in range(idx.shape[0]):
             rows = ptr(d_idx[s])
-            ctx.call("mjrl_gather_rows_f32", ptr(batch.obs), rows, c_int(B), c_int(n), ptr(mb_obs), st)
-            ctx.call("mjrl_gather_rows_f32", ptr(batch.act), rows, c_int(B), c_int(m), ptr(mb_act), st)
-            ctx.call("mjrl_gather_rows_f32", ptr(w), rows, c_int(B), c_int(1), ptr(mb_adv), st)
+            ctx.call("mjrl_gather_rows_f32", ptr(c_obs), rows, c_int(B), c_int(n), ptr(mb_obs), st)
+            ctx.call("mjrl_gather_rows_f32", ptr(c_act), rows, c_int(B), c_int(m), ptr(mb_act), st)
+            ctx.call("mjrl_gather_rows_f32", ptr(c_w), rows, c_int(B), c_int(1), ptr(mb_adv), st)
             if aliased:
                 p_old_eff[:d - m].copy_(params[:d - m])
                 ctx.call("mjrl_policy_forward", eng.dv.desc_ref(), ptr(p_old_eff), ptr(mb_obs), ptr(mb_act),
                          c_i64(B), ptr(None), ptr(mb_oll), st)
             else:
-                ctx.call("mjrl_gather_rows_f32", ptr(old_ll), rows, c_int(B), c_int(1), ptr(mb_oll), st)
+                ctx.call("mjrl_gather_rows_f32", ptr(c_oll), rows, c_int(B), c_int(1), ptr(mb_oll), st)
             ctx.call("mjrl_policy_forward", eng.dv.desc_ref(), ptr(params), ptr(mb_obs), ptr(mb_act),
                      c_i64(B), ptr(None), ptr(mb_ll), st)
             ctx.call("mjrl_ppo_clip_weights", ptr(mb_ll), ptr(mb_oll), ptr(mb_adv), c_int(B),
@@ -112,9 +133,10 @@ class PPO(BatchREINFORCE):
         if aliased:
             p_old_eff[:d - m].copy_(params[:d - m])
             old_ll, old_mean = eng.old_cache(p_old_eff, batch.obs, batch.act)
-        out = eng.evaluate(params, batch.obs, batch.act, w, old_ll, old_mean, p_old[d - m:], float(N))
+        out = eng.evaluate(params, batch.obs, batch.act, w, old_ll, old_mean, p_old[d - m:], N_glob)
         host = torch.cat([out, surr_before_dev]).cpu().numpy()
         params_after_opt = params.cpu().numpy()
+        eng.dist.check()
         surr_after, kl_dist, surr_before = float(host[0]), float(host[1]), float(host[2])
         self.policy.set_param_values(params_after_opt, set_new=True, set_old=True)
         t_opt = timer.time() - ts

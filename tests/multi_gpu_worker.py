@@ -83,6 +83,34 @@ def run_trpo_dapg(world_mode):
     return out
 
 
+def run_ppo(world_mode, rank, world):
+    """PPO: the minibatch chain is replicas-only (every rank gathers all rows in rank order, rank 0 draws the
+    minibatches), the full-batch passes are sharded.  Must equal a single-GPU run on the shards concatenated
+    in rank order with the same numpy seed, up to the summation order of the whitening moments."""
+    from mjrl_b200.algos.ppo_clip import PPO
+    g = load_golden("c3_hopper_mid")
+    spec = EnvSpec(g["n"], g["m"], g["horizon"], 1)
+    pol = MLP(spec, hidden_sizes=g["hidden"], seed=123)
+    pol.model.set_transformations(**g["transforms"]); pol.old_model.set_transformations(**g["transforms"])
+    pol.set_param_values(g["params"].copy())
+    base = LinearBaseline(spec)
+    base._coeffs = g["fit0_coeffs"].copy()
+    paths = syn.flat_to_paths(batch_of(g, "b1_"))
+    shards = [shard_paths(paths, r, world) for r in range(world)]
+    ag = PPO(None, pol, base, clip_coef=0.2, epochs=2, mb_size=64, learn_rate=3e-4)
+    np.random.seed(77)
+    if world_mode:
+        ag.dist = Dist()
+        mine = shards[rank]
+    else:
+        ag.dist = Dist.__new__(Dist); ag.dist.td = None; ag.dist.world = 1; ag.dist.rank = 0; ag.dist.calls = 0
+        ag.dist.group = None
+        mine = [p for sh in shards for p in sh]
+    drop_cache()
+    ag.train_step(len(mine), gamma=g["gamma"], gae_lambda=g["gae_lambda"], paths=mine)
+    return pol.get_param_values().astype(np.float64), ag.last_update
+
+
 def run_mlpbase(world_mode, rank, world):
     """MLPBaseline.fit is replicas-only: every rank gathers all rows and runs the same chain, so the
     result must equal (bit for bit) a single-GPU fit on the shards concatenated in rank order."""
@@ -113,7 +141,18 @@ if __name__ == "__main__":
     step_multi, coef_multi, g = run(True)
     mlp_multi, errs_multi, steps_multi = run_mlpbase(True, rank, world)
     td_multi = run_trpo_dapg(True)
+    ppo_multi, ppo_lu = run_ppo(True, rank, world)
+    # replicas: every rank must hold the same parameters bit for bit
+    gathered = [None] * world
+    torch.distributed.all_gather_object(gathered, ppo_multi.tobytes())
+    ppo_replicas_same = all(b == gathered[0] for b in gathered)
     if rank == 0:
+        ppo_one, ppo_lu1 = run_ppo(False, rank, world)
+        d_ppo = float(np.abs(ppo_multi - ppo_one).max())
+        ppo_ok = ppo_replicas_same and d_ppo < 2e-5 and ppo_lu["steps"] == ppo_lu1["steps"] and \
+            abs(ppo_lu["kl_dist"] - ppo_lu1["kl_dist"]) < 1e-5
+        print("PPO_%s max|dp|=%.3e steps=%d replicas_bitexact=%s" % ("OK" if ppo_ok else "FAIL", d_ppo,
+                                                                     ppo_lu["steps"], ppo_replicas_same))
         td_one = run_trpo_dapg(False)
         r_trpo = rel_l2(td_multi["trpo"][0], td_one["trpo"][0])
         r_dapg = rel_l2(td_multi["dapg"][0], td_one["dapg"][0])
@@ -125,7 +164,7 @@ if __name__ == "__main__":
         r_step, r_coef = rel_l2(step_multi, step_one), rel_l2(coef_multi, coef_one)
         mlp_same = steps_multi == steps_one and np.array_equal(mlp_multi, mlp_one)
         errs_ok = all(abs(a - b) < 1e-9 * max(1.0, abs(b)) for a, b in zip(errs_multi, errs_one))
-        ok = r_step < 1e-4 and r_coef < 1e-6 and mlp_same and errs_ok and td_ok
+        ok = r_step < 1e-4 and r_coef < 1e-6 and mlp_same and errs_ok and td_ok and ppo_ok
         print("MULTI_%s world=%d step_rel=%.3e coef_rel=%.3e mlpbase_bitexact=%s (%d steps) errs_ok=%s peer=[%s]"
               % ("OK" if ok else "FAIL", world, r_step, r_coef, mlp_same, steps_multi, errs_ok, PEER_NOTE))
     if world > 1:

@@ -60,9 +60,16 @@ def _worker(rank, world, port, q):
     dist.allreduce(gsum)
     fsum = torch.from_numpy(tp.fvp(obs, g["vpg_grad"]) * obs.shape[0])
     dist.allreduce(fsum)
+    # (4) replicas-only chains (PPO minibatch epochs): all rows in rank order on every rank, rank 0's schedule
+    rows, sizes = dist.allgather_rows(torch.from_numpy(np.c_[obs, act].astype(np.float32)))
+    sched = torch.arange(6, dtype=torch.int32) * (7 if rank == 0 else 1)
+    dist.broadcast0(sched)
     if rank == 0:
         q.put(dict(N=float(part[0]), mean=float(mean), std=std, gram=gram.numpy(), gsum=gsum.numpy(),
-                   fsum=fsum.numpy(), calls=dist.calls, n_mine=len(mine)))
+                   fsum=fsum.numpy(), calls=dist.calls, n_mine=len(mine), rows=rows.numpy(), sizes=sizes,
+                   sched=sched.numpy()))
+    else:
+        q.put(dict(rank=rank, rows_sum=float(rows.double().sum()), sched=sched.numpy()))
     td.barrier()
     td.destroy_process_group()
 
@@ -92,9 +99,11 @@ def test_two_rank_sums_match_single_process():
     port = _free_port()
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     [p.start() for p in procs]
-    res = q.get(timeout=240)
+    got = [q.get(timeout=240), q.get(timeout=240)]
     [p.join(60) for p in procs]
     assert all(p.exitcode == 0 for p in procs)
+    res = [r for r in got if "N" in r][0]
+    other = [r for r in got if "N" not in r][0]
     g = load_golden("c3_hopper_mid")
     paths = syn.flat_to_paths(batch_of(g, "b1_"))
     off = g["b1_path_offsets"]
@@ -111,3 +120,12 @@ def test_two_rank_sums_match_single_process():
     assert rel_l2(res["gsum"] / adv.size, g["vpg_grad"]) < 1e-5
     assert rel_l2(res["fsum"] / adv.size, g["hvp_of_grad_nodamp"]) < 1e-5
     assert res["calls"] == 5
+    # replicas-only chains: both ranks hold all rows, in rank order, and rank 0's schedule
+    from mjrl_b200.sharding import shard_paths
+    want = np.concatenate([np.c_[np.concatenate([p["observations"] for p in sh]),
+                                 np.concatenate([p["actions"] for p in sh])]
+                           for sh in (shard_paths(paths, r, 2) for r in range(2))]).astype(np.float32)
+    np.testing.assert_array_equal(res["rows"], want)
+    assert sum(res["sizes"]) == adv.size and abs(other["rows_sum"] - float(want.astype(np.float64).sum())) < 1e-6
+    np.testing.assert_array_equal(res["sched"], np.arange(6) * 7)
+    np.testing.assert_array_equal(other["sched"], np.arange(6) * 7)
