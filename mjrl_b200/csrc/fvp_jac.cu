@@ -265,6 +265,13 @@ __global__ void __launch_bounds__(NH * HTHREADS, 1) fvp_jac_kernel(const Args a)
           for (int i = 0; i < G; ++i) mma_term(q2[n0 + i], ah, bv[i], term);
       }
     }
+    // Jacobian rows of output 0 are requested before the head product: their latency hides behind its MMAs
+    float gk[MK][NF][4];
+#pragma unroll
+    for (int nf = 0; nf < NF; ++nf) {
+      const float2 lo = ld_cache(gslot + (size_t)(2 * nf) * 32), hi = ld_cache(gslot + (size_t)(2 * nf + 1) * 32);
+      gk[0][nf][0] = lo.x; gk[0][nf][1] = lo.y; gk[0][nf][2] = hi.x; gk[0][nf][3] = hi.y;
+    }
     // ---- h2 block by block: q3 = vb2 + H2 V2^T (rows g / g+8, columns j = 2c, 2c+1), and
     //      q2 <- (1 - h2^2) q2 so that <G2_j, q2> = sum_col W2[j][col] q2[col] --------------------------
     float q3[4];
@@ -303,19 +310,20 @@ __global__ void __launch_bounds__(NH * HTHREADS, 1) fvp_jac_kernel(const Args a)
         }
       }
     }
-    float gk[MK][NF][4];
 #pragma unroll
     for (int j = 0; j < MK; ++j) {
 #pragma unroll
       for (int nf = 0; nf < NF; ++nf) {
-        float2 lo = make_float2(0.f, 0.f), hi = make_float2(0.f, 0.f);
-        if (j < m) {
-          lo = ld_cache(gslot + (size_t)(j * 2 * NF + 2 * nf) * 32);
-          hi = ld_cache(gslot + (size_t)(j * 2 * NF + 2 * nf + 1) * 32);
+        if (j > 0) {
+          float2 lo = make_float2(0.f, 0.f), hi = make_float2(0.f, 0.f);
+          if (j < m) {
+            lo = ld_cache(gslot + (size_t)(j * 2 * NF + 2 * nf) * 32);
+            hi = ld_cache(gslot + (size_t)(j * 2 * NF + 2 * nf + 1) * 32);
+          }
+          gk[j][nf][0] = lo.x; gk[j][nf][1] = lo.y; gk[j][nf][2] = hi.x; gk[j][nf][3] = hi.y;
         }
-        gk[j][nf][0] = lo.x; gk[j][nf][1] = lo.y; gk[j][nf][2] = hi.x; gk[j][nf][3] = hi.y;
-        pa[j] = fmaf(lo.x, q1[nf][0], pa[j]); pa[j] = fmaf(lo.y, q1[nf][1], pa[j]);
-        pb[j] = fmaf(hi.x, q1[nf][2], pb[j]); pb[j] = fmaf(hi.y, q1[nf][3], pb[j]);
+        pa[j] = fmaf(gk[j][nf][0], q1[nf][0], pa[j]); pa[j] = fmaf(gk[j][nf][1], q1[nf][1], pa[j]);
+        pb[j] = fmaf(gk[j][nf][2], q1[nf][2], pb[j]); pb[j] = fmaf(gk[j][nf][3], q1[nf][3], pb[j]);
       }
     }
     // u_j = fisher_j (J v)_j for both rows of this thread (zero past N)
