@@ -141,6 +141,7 @@ class UpdateEngine:
         self._cache_key = None
         self._jac_key = None  # (params, obs) the Jacobian rows G1 of the cache were filled for
         self._jac_ok = None
+        self._held = None     # tensors of the current cache keys (see _hold)
 
     # ------------------------------------------------------------------ building blocks
     def whiten(self, adv64, eps=1e-6, scale=1.0, N_global=None):
@@ -180,7 +181,9 @@ class UpdateEngine:
         self.ctx.call("mjrl_policy_grad_cached", self.dv.desc_ref(), ptr(params), ptr(obs), ptr(act), ptr(w),
                       ptr(old_ll), c_i64(N), ptr(tgt), c_void_p(tgt.data_ptr() + 8 * d),
                       ptr(ll_out), ptr(mean_out), ptr(fcache), stream_ptr())
-        self._cache_key = self._key(params, obs) if fcache is not None else None
+        # the pass refilled h1|h2 for these tensors; Jacobian rows of any earlier policy / batch are stale
+        self._cache_key = self._hold(params, obs) if fcache is not None else None
+        self._jac_key = None
         self.launches += 3
         if accumulate:
             self.grad[:d] += tgt[:d]   # demo term: only the gradient, not the surrogate (dapg.py:93,98)
@@ -215,6 +218,14 @@ class UpdateEngine:
     def _key(params, obs):
         """Identity + in-place-modification counters of the tensors a cache was filled from."""
         return (params.data_ptr(), params._version, obs.data_ptr(), obs._version, obs.shape[0])
+
+    def _hold(self, params, obs):
+        """Key of a cache fill.  The engine keeps the two tensors alive while the key is: `dv.params()` builds a
+        fresh device tensor per update and the caching allocator would hand a freed one's address (and version
+        0) to the next, making a stale cache look current.  Every update's gradient pass refills h1|h2 and drops
+        the Jacobian key, so rows written through raw pointers into a reused obs store are covered as well."""
+        self._held = (params, obs)
+        return self._key(params, obs)
 
     def _fvp_cache(self, N):
         """Device buffer for the cached-activation FVP (None when the kernel variant that uses it
@@ -263,7 +274,8 @@ class UpdateEngine:
             else:
                 self.fvp(params, o, self.cg_p32, self.cg_z, cache_mode=mode)
             if mode == 1 and self._cache is not None:
-                self._cache_key = self._key(params, o)
+                self._cache_key = self._hold(params, o)
+                self._jac_key = None
             if peer is not None:
                 peer.cg_update(self.cg, d, 1.0 / cnt, damping, tol, epoch)
                 self.dist.calls += 1
@@ -290,6 +302,8 @@ class UpdateEngine:
             first = rest = 3 if (N >= JAC_MIN_N and self._jac_prepare(params, obs)) else 2
         else:
             first, rest = 1, 2
+            key = self._hold(params, obs)
+            self._jac_key = None
             if N >= JAC_MIN_N and iters > 1:
                 if self._jac_ok is None:
                     self._jac_ok = bool(_lib.load().mjrl_policy_fvp_jac_ok(self.ctx.h, self.dv.desc_ref()))

@@ -38,8 +38,10 @@ _TO_OURS = {v: k for k, v in _MODULES.items()}
 _CLASSES = {"MLP", "MuNet", "LinearPolicy", "LinearModel", "LinearBaseline", "QuadraticBaseline",
             "MLPBaseline", "EnvSpec"}
 # fields of the mirrors that stock objects do not have
-_PRIVATE = {"_dev", "_old_aliases_new", "hidden_sizes", "_dev_coeffs", "last_fit_info", "learn_rate",
+_PRIVATE = {"_dev", "_old_aliases_new", "_dev_coeffs", "last_fit_info", "learn_rate",
             "adam_betas", "adam_eps", "adam_step", "_host_m", "_host_v", "last_fit_steps"}
+# ... per class: stock MLP has no `hidden_sizes`, stock MuNet does (gaussian_mlp.py:153)
+_PRIVATE_OF = {"MLP": {"hidden_sizes"}, "LinearPolicy": {"hidden_sizes"}}
 
 
 # ------------------------------------------------------------------------------------ load
@@ -57,8 +59,10 @@ def _adopt_policy(p):
     d["_dev"] = None
     if "hidden_sizes" not in d:
         hs = getattr(p.model, "hidden_sizes", None)
+        if hs is None and hasattr(p.model, "fc1"):
+            hs = (p.model.fc0.out_features, p.model.fc1.out_features)
         if hs is not None:
-            d["hidden_sizes"] = tuple(hs)
+            d["hidden_sizes"] = tuple(int(h) for h in hs)
     if "_old_aliases_new" not in d:
         # tensors that shared storage when pickled still do after unpickling
         new0, old0 = p.trainable_params[0], p.old_params[0]
@@ -161,8 +165,9 @@ def _as_stock(obj, tokens):
     tokens.append(tok)
     state = obj.__getstate__() if hasattr(obj, "__getstate__") and not isinstance(obj, torch.nn.Module) \
         else dict(obj.__dict__)
-    state = {k: v for k, v in dict(state).items() if k not in _PRIVATE}
     name = ours.__name__
+    drop = _PRIVATE | _PRIVATE_OF.get(name, set())
+    state = {k: v for k, v in dict(state).items() if k not in drop}
     if name in ("MLP", "LinearPolicy"):
         state["model"] = _as_stock(obj.model, tokens)
         state["old_model"] = _as_stock(obj.old_model, tokens)

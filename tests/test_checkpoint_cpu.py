@@ -146,3 +146,19 @@ def test_stock_mjrl_loads_our_dumps(tmp_path):
     r = subprocess.run([sys.executable, "-c", _STOCK_SIDE, G("stock_checkpoints.npz"), str(tmp_path)],
                        capture_output=True, text=True, cwd=str(tmp_path), env=env, timeout=300)
     assert "STOCK-OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_dump_load_roundtrip_keeps_hidden_sizes():
+    """A mirror-built MLP with non-default widths survives dumps -> loads: stock MuNet stores `hidden_sizes`
+    (gaussian_mlp.py:153), stock MLP does not; the loader recovers the policy-level field from the net."""
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.utils.gym_env import EnvSpec
+    pol = MLP(EnvSpec(7, 2, 50, 1), hidden_sizes=(32, 16), seed=3)
+    back = ck.loads(ck.dumps(pol))
+    assert tuple(back.hidden_sizes) == (32, 16)
+    assert tuple(back.model.hidden_sizes) == (32, 16) and tuple(back.old_model.hidden_sizes) == (32, 16)
+    np.testing.assert_array_equal(back.get_param_values(), pol.get_param_values())
+    assert back.d == pol.d
+    # a stock-side pickle without the policy-level field and without MuNet.hidden_sizes still resolves
+    del back.__dict__["hidden_sizes"]; del back.model.__dict__["hidden_sizes"]
+    assert tuple(ck._adopt_policy(back).hidden_sizes) == (32, 16)

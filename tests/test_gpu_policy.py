@@ -320,3 +320,60 @@ print("WS_OK %%.2e" %% rel)
     env = dict(os.environ, MJRL_B200_FVP_WS="1")
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "WS_OK" in r.stdout, r.stdout + r.stderr
+
+
+def test_cg_solve_reference_signature_over_hvp_eval(golden):
+    """utils.cg_solve (mjrl/utils/cg_solve.py:3-22) with the operator npg_cg.py:122-124 builds:
+    `cg_solve(agent.build_Hvp_eval([obs, act], regu_coef), vpg_grad, x_0=vpg_grad.copy(), cg_iters=k)`
+    against the reference's iterates (k <= 5 within 1e-4; k = 10 by the H1 protocol)."""
+    from mjrl_b200.algos.npg_cg import NPG
+    from mjrl_b200.utils.cg_solve import cg_solve
+    from oracle import mjrl_oracle as O
+    g = golden
+    b1 = batch_of(g, "b1_")
+    obs, act = b1["observations"], b1["actions"]
+    ag = agent(NPG, g, make_policy(g))
+    hvp = ag.build_Hvp_eval([obs, act], regu_coef=1e-4)
+    grad = g["vpg_grad"]
+    for k in (1, 2, 3, 5):
+        x = cg_solve(hvp, grad, x_0=grad.copy(), cg_iters=k)
+        assert x.dtype == np.float32 and rel_l2(x, g["cg_k%d" % k]) < TOL, k
+    x10 = cg_solve(hvp, grad, x_0=grad.copy(), cg_iters=10)
+    opol = O.GaussianPolicy(g["n"], g["m"], g["hidden"], g["params"], **(g["transforms"] or {}))
+    tp = O.TruthPolicy(opol)
+    xs = O.truth_cg(tp, obs, tp.vpg(obs, act, g["b1_adv_white"]))
+    assert rel_l2(x10, xs) <= max(TOL, 1.05 * rel_l2(g["cg_k10"], xs))
+    # early exit: a huge tolerance stops after the first update, like the reference (:19-20)
+    np.testing.assert_array_equal(cg_solve(hvp, grad, cg_iters=10, residual_tol=1e30),
+                                  cg_solve(hvp, grad, cg_iters=1))
+
+
+@pytest.mark.parametrize("case", ["c3_hopper", "c2_swimmer"])
+def test_consecutive_updates_refresh_the_jacobian_cache(case, monkeypatch):
+    """Two train_from_paths calls on ONE agent over a caller-resident batch (same obs buffer, parameters
+    changed by the first update): the second solve must run on Jacobian rows of the CURRENT policy.  The
+    device parameter tensor of every update is a fresh allocation that the caching allocator places at
+    the address of the previous one, which once made the stale rows look current."""
+    from conftest import load_golden
+    from mjrl_b200.algos import engine
+    from mjrl_b200.algos.npg_cg import NPG
+    from oracle import mjrl_oracle as O
+    g = load_golden(case)
+    iters = 3            # k <= 3 iterates of the reference agree with any summation order to 3e-7 (SURVEY 8c)
+    finals = {}
+    for jac_min_n in (0, 1 << 30):
+        monkeypatch.setattr(engine, "JAC_MIN_N", jac_min_n)
+        p1 = prepared_paths(g)
+        pol = make_policy(g)
+        ag = agent(NPG, g, pol, normalized_step_size=0.01, FIM_invert_args={'iters': iters, 'damping': 1e-4})
+        ag.train_from_paths(p1)
+        mid = pol.get_param_values().copy()
+        ag.train_from_paths(p1)
+        finals[jac_min_n] = (mid, pol.get_param_values().copy())
+    opol = O.GaussianPolicy(g["n"], g["m"], g["hidden"], g["params"], **(g["transforms"] or {}))
+    p1 = prepared_paths(g)
+    o1 = O.npg_update(opol, p1, cg_iters=iters)["new_params"].copy()
+    o2 = O.npg_update(opol, p1, cg_iters=iters)["new_params"].copy()
+    for mid, fin in finals.values():
+        assert rel_l2(mid - g["params"], o1 - g["params"]) < TOL
+        assert rel_l2(fin.astype(np.float64) - mid, o2.astype(np.float64) - o1) < 10 * TOL
