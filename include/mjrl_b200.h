@@ -72,6 +72,18 @@ int mjrl_moments(mjrl_ctx* ctx, const double* x, int64_t N, double* moments4, vo
  * stages give mjrl_moments' bits. */
 int mjrl_moments_stage(mjrl_ctx* ctx, const double* x, int64_t N, double* moments4, int32_t stage,
                        void* stream);
+/* mjrl_moments for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels, same grid and therefore the same bits as mjrl_moments, but the per-CTA partial sums live in
+ * a file-scope `static __device__` array of 4,096 doubles (32 KB, held by every GPU that loads the library
+ * until the process exits) instead of the context's grow-on-demand scratch: the call path contains no
+ * cudaMalloc / cudaFree / allocating library routine.  Limit: N <= 8,388,608 (4,096 partial sums x 2,048
+ * elements per CTA slab); larger N returns MJRL_E_SHAPE with a message naming the limit.  The context's
+ * device must be the current device (MJRL_E_STATE otherwise).  All calls on a device share the one array:
+ * nothing in it needs clearing between calls (every pass overwrites the entries it reads), but two calls
+ * whose kernels overlap on the GPU (different streams, or concurrent graph branches) RACE on it -- serialise
+ * them on one stream. */
+int mjrl_moments_noalloc(mjrl_ctx* ctx, const double* x, int64_t N, double* moments4, void* stream);
 /* x <- (x - mean)/(std + eps) in place (fp64), std = sqrt(moments[2]/N). */
 int mjrl_normalize_inplace(mjrl_ctx* ctx, double* x, int64_t N, const double* moments4,
                            double eps, void* stream);

@@ -98,7 +98,7 @@ class Context:
 
 
 # kernels each entry point launches (csrc/*.cu), for the launch count bench.py reports
-KERNELS_PER_CALL = {"mjrl_moments": 4, "mjrl_path_return_stats": 2, "mjrl_linbase_gram": 2,
+KERNELS_PER_CALL = {"mjrl_moments": 4, "mjrl_moments_noalloc": 4, "mjrl_path_return_stats": 2, "mjrl_linbase_gram": 2,
                     "mjrl_quadbase_gram": 2,
                     "mjrl_policy_eval": 2, "mjrl_policy_grad": 3, "mjrl_policy_fvp": 2,
                     "mjrl_policy_fvp_cached": 2, "mjrl_policy_grad_cached": 3,

@@ -328,6 +328,53 @@ int mjrl_moments_stage(mjrl_ctx* ctx, const double* x, int64_t N, double* mom, i
   return mjrl_check_launch("moments_stage");
 }
 
+// ---- mjrl_moments without any allocation -------------------------------------------------------
+// Scratch of the allocation-free variant: the per-CTA partial sums of the two passes live in a
+// file-scope device array instead of the context's grow-on-demand block (no cudaMalloc on the
+// call path).  Every GPU that loads the library holds these 32 KB until the process exits.
+#define MJRL_NOALLOC_MAX_PARTS 4096
+#define MJRL_NOALLOC_SLAB 2048       /* elements per CTA slab below the grid cap (ew_grid(N, 256 * 8)) */
+#define MJRL_NOALLOC_MAX_DEVICES 64
+static __device__ __align__(256) double g_moments_partials[MJRL_NOALLOC_MAX_PARTS];
+// Device address of g_moments_partials per device.  In host code the array's NAME is only a host-side
+// stand-in for the symbol (passing it to a kernel hands over a host address), so the address is
+// looked up once per device with cudaGetSymbolAddress while that device is current.
+static double* g_moments_partials_dev[MJRL_NOALLOC_MAX_DEVICES];
+
+int mjrl_moments_noalloc(mjrl_ctx* ctx, const double* x, int64_t N, double* mom, void* stream) {
+  MJRL_REQUIRE(ctx && x && mom && N > 0, MJRL_E_ARG, "moments_noalloc: bad argument");
+  const int64_t max_n = (int64_t)MJRL_NOALLOC_MAX_PARTS * MJRL_NOALLOC_SLAB;
+  MJRL_REQUIRE(N <= max_n, MJRL_E_SHAPE,
+               "moments_noalloc: N = %lld exceeds the static scratch (at most %lld elements = %d partial sums "
+               "x %d elements per CTA); use mjrl_moments", (long long)N, (long long)max_n,
+               MJRL_NOALLOC_MAX_PARTS, MJRL_NOALLOC_SLAB);
+  const int grid = ew_grid(ctx, N, 256 * 8);   // the grid of mjrl_moments: same partials, same bits
+  MJRL_REQUIRE(grid <= MJRL_NOALLOC_MAX_PARTS, MJRL_E_SHAPE,
+               "moments_noalloc: %d CTAs exceed the %d static partial sums", grid, MJRL_NOALLOC_MAX_PARTS);
+  int cur = -1;
+  cudaError_t e = cudaGetDevice(&cur);
+  if (e != cudaSuccess) { mjrl_set_error("moments_noalloc: cudaGetDevice: %s", cudaGetErrorString(e)); return (int)e; }
+  MJRL_REQUIRE(cur == ctx->device, MJRL_E_STATE,
+               "moments_noalloc: device %d is current, the context belongs to device %d", cur, ctx->device);
+  MJRL_REQUIRE(cur >= 0 && cur < MJRL_NOALLOC_MAX_DEVICES, MJRL_E_STATE, "moments_noalloc: device index %d", cur);
+  double* part = g_moments_partials_dev[cur];
+  if (!part) {   // set-up, once per device, with that device current
+    e = cudaGetSymbolAddress((void**)&part, g_moments_partials);
+    if (e != cudaSuccess || !part) {
+      mjrl_set_error("moments_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : MJRL_E_STATE;
+    }
+    g_moments_partials_dev[cur] = part;
+  }
+  // Nothing to clear: each pass writes partials [0, grid) before its final kernel reads exactly those.
+  cudaStream_t s = (cudaStream_t)stream;
+  moment_partial_kernel<false><<<grid, 256, 0, s>>>(x, N, mom, part);
+  moment_final_kernel<false><<<1, 256, 0, s>>>(part, grid, N, mom);
+  moment_partial_kernel<true><<<grid, 256, 0, s>>>(x, N, mom, part);
+  moment_final_kernel<true><<<1, 256, 0, s>>>(part, grid, N, mom);
+  return mjrl_check_launch("moments_noalloc");
+}
+
 int mjrl_normalize_inplace(mjrl_ctx* ctx, double* x, int64_t N, const double* mom, double eps,
                            void* stream) {
   MJRL_REQUIRE(ctx && x && mom && N > 0, MJRL_E_ARG, "normalize: bad argument");
