@@ -225,6 +225,14 @@ int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc,
 int mjrl_policy_fvp_jac_ok(mjrl_ctx* ctx, const mjrl_policy_desc* desc);
 int mjrl_policy_fvp_jac_fill(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params, int64_t N,
                              float* cache, void* stream);
+/* Tensor-memory product (hidden 64 x 64, obs_dim <= 15, act_dim <= 8, csrc/fvp_tc.cu): the same Fisher-vector
+ * product on the 5th-generation tensor cores (tcgen05.mma kind::tf32 with hi/lo error compensation, accumulators
+ * and A operands in tensor memory).  It reads h1, h2 from a copy of the cache in its own tile order:
+ * mjrl_policy_fvp_tc_ok: 1 when the shape has this variant (mjrl_policy_fvp_cache_count then includes the
+ * copy).  mjrl_policy_fvp_tc_fill builds the copy from an ALREADY FILLED h1|h2 cache (once per CG solve, a pure
+ * relayout); products then pass cache_mode 4.  Same result as the other modes to fp32 rounding (~1e-6). */
+int mjrl_policy_fvp_tc_ok(mjrl_ctx* ctx, const mjrl_policy_desc* desc);
+int mjrl_policy_fvp_tc_fill(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N, float* cache, void* stream);
 /* mjrl_policy_grad that also fills that cache (flat_vpg runs at the parameters the CG solve that
  * follows it uses, npg_cg.py:96-106): fvp_cache as above or NULL. */
 int mjrl_policy_grad_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
@@ -355,7 +363,8 @@ int mjrl_cg_update_peer(mjrl_ctx* ctx, mjrl_peer* peer, const mjrl_cg_state* sta
 /* cg_solve.py:3-22 in one call: mjrl_cg_init(b, b_scale), then `iters` x ( mjrl_policy_fvp_cached(vec =
  * state->p32) -> mjrl_cg_update ), enqueued from C with no host work in between.  The first product uses
  * cache_mode `mode_first`, the others `mode_rest`; jac_fill_after_first != 0 runs mjrl_policy_fvp_jac_fill
- * after the first product (mode_first 1, mode_rest 3).  peer != NULL: the products write into the exchange
+ * after the first product (mode_first 1, mode_rest 3); jac_fill_after_first == 2 runs mjrl_policy_fvp_tc_fill
+ * there instead (mode_rest 4).  peer != NULL: the products write into the exchange
  * slots of epochs epoch0+1 .. epoch0+iters and the updates are mjrl_cg_update_peer (the caller advances its
  * epoch counter by `iters`); peer == NULL: single rank. */
 int mjrl_cg_solve(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params, const float* obs, int64_t N,

@@ -22,6 +22,8 @@ from .._lib import CGState, c_double, c_float, c_i64, c_int, c_void_p, ptr, stre
 # Below this many local timesteps a CG solve is launch-latency sized and the extra fill pass of the
 # Jacobian-cached product does not pay (C2 swimmer, 10k timesteps: 1.26 ms with, 1.28 without).
 JAC_MIN_N = int(os.environ.get("MJRL_B200_FVP_JAC_MIN_N", "32768"))
+# Same threshold for the tensor-memory product (csrc/fvp_tc.cu): it needs a relayout pass per solve.
+TC_MIN_N = int(os.environ.get("MJRL_B200_FVP_TC_MIN_N", "32768"))
 
 
 class Dist:
@@ -141,6 +143,8 @@ class UpdateEngine:
         self._cache_key = None
         self._jac_key = None  # (params, obs) the Jacobian rows G1 of the cache were filled for
         self._jac_ok = None
+        self._tc_key = None   # same for the tile-ordered copy the tensor-memory product reads
+        self._tc_ok = None
         self._held = None     # tensors of the current cache keys (see _hold)
 
     # ------------------------------------------------------------------ building blocks
@@ -184,6 +188,7 @@ class UpdateEngine:
         # the pass refilled h1|h2 for these tensors; Jacobian rows of any earlier policy / batch are stale
         self._cache_key = self._hold(params, obs) if fcache is not None else None
         self._jac_key = None
+        self._tc_key = None
         self.launches += 3
         if accumulate:
             self.grad[:d] += tgt[:d]   # demo term: only the gradient, not the surrogate (dapg.py:93,98)
@@ -213,6 +218,30 @@ class UpdateEngine:
                           ptr(self._cache), stream_ptr())
             self._jac_key = key
         return True
+
+    def _tc_prepare(self, params, obs):
+        """With the h1|h2 cache valid for (params, obs): make its tile-ordered copy for the tensor-memory product
+        (csrc/fvp_tc.cu) valid too -- one relayout pass per CG solve.  False when the shape has no such product."""
+        if self._tc_ok is None:
+            self._tc_ok = bool(_lib.load().mjrl_policy_fvp_tc_ok(self.ctx.h, self.dv.desc_ref()))
+        if not self._tc_ok or self._cache is None:
+            return False
+        key = self._key(params, obs)
+        if self._tc_key != key:
+            self.ctx.call("mjrl_policy_fvp_tc_fill", self.dv.desc_ref(), c_i64(obs.shape[0]), ptr(self._cache),
+                          stream_ptr())
+            self._tc_key = key
+        return True
+
+    def _cached_mode(self, params, obs):
+        """Product variant for a solve whose h1|h2 cache is valid: 4 = tensor-memory product (tcgen05), 3 =
+        Jacobian-cached rows kernel, 2 = activation-cached rows kernel."""
+        N = obs.shape[0]
+        if N >= TC_MIN_N and self._tc_prepare(params, obs):
+            return 4
+        if N >= JAC_MIN_N and self._jac_prepare(params, obs):
+            return 3
+        return 2
 
     @staticmethod
     def _key(params, obs):
@@ -262,7 +291,7 @@ class UpdateEngine:
             elif self._cache_key is not None and self._cache_key == self._key(params, o):
                 # h1|h2 filled by the gradient pass (or the first product) at these tensors; small action
                 # dimensions also cache the output-Jacobian rows and run the cheaper product (fvp_jac.cu)
-                mode = 3 if (o.shape[0] >= JAC_MIN_N and self._jac_prepare(params, o)) else 2
+                mode = self._cached_mode(params, o)
             else:
                 mode = 1
             peer = self.dist.peer if self.dist.world > 1 else None
@@ -276,6 +305,7 @@ class UpdateEngine:
             if mode == 1 and self._cache is not None:
                 self._cache_key = self._hold(params, o)
                 self._jac_key = None
+                self._tc_key = None
             if peer is not None:
                 peer.cg_update(self.cg, d, 1.0 / cnt, damping, tol, epoch)
                 self.dist.calls += 1
@@ -299,15 +329,21 @@ class UpdateEngine:
         if cache is None:
             first = rest = 0
         elif self._cache_key is not None and self._cache_key == key:
-            first = rest = 3 if (N >= JAC_MIN_N and self._jac_prepare(params, obs)) else 2
+            first = rest = self._cached_mode(params, obs)
         else:
             first, rest = 1, 2
             key = self._hold(params, obs)
             self._jac_key = None
-            if N >= JAC_MIN_N and iters > 1:
+            self._tc_key = None
+            if iters > 1:
+                if self._tc_ok is None:
+                    self._tc_ok = bool(_lib.load().mjrl_policy_fvp_tc_ok(self.ctx.h, self.dv.desc_ref()))
                 if self._jac_ok is None:
                     self._jac_ok = bool(_lib.load().mjrl_policy_fvp_jac_ok(self.ctx.h, self.dv.desc_ref()))
-                if self._jac_ok:
+                if self._tc_ok and N >= TC_MIN_N:
+                    rest, fill_jac = 4, 2        # relayout pass after the first (cache-filling) product
+                    self._tc_key = key
+                elif self._jac_ok and N >= JAC_MIN_N:
                     rest, fill_jac = 3, 1
                     self._jac_key = key
             self._cache_key = key
@@ -321,8 +357,8 @@ class UpdateEngine:
                       ptr(self.grad), c_double(g_scale), c_int(iters), c_double(1.0 / N_global),
                       c_double(damping), c_double(tol), ptr(cache), c_int(first), c_int(rest), c_int(fill_jac),
                       peer.h if peer is not None else c_void_p(0), c_i64(epoch0), stream_ptr())
-        self.launches += 1 + 3 * iters + fill_jac
-        self.ctx.launches += 3 * iters + fill_jac     # ctx.call counted one
+        self.launches += 1 + 3 * iters + (1 if fill_jac else 0)
+        self.ctx.launches += 3 * iters + (1 if fill_jac else 0)     # ctx.call counted one
         return self.cg_x
 
     def step(self, curr, g_scale, delta, const_alpha=None, alpha_scale=1.0):

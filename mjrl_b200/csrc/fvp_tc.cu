@@ -1,0 +1,764 @@
+// Fisher-vector product on the 5th-generation tensor cores (tcgen05.mma, accumulators and A operands in
+// tensor memory) -- replaces the double backprop of mjrl/algos/npg_cg.py:55-74 inside a CG solve, for the
+// two-hidden-layer tanh policy of mjrl/policies/gaussian_mlp.py:143-182 with 64 x 64 hidden units.
+//
+//   F v = sum_t J_t^T M J_t v,   J_t = d mu_t / d theta,   M = diag(out_scale^2 * 2 / (2 sigma^2 + 1e-8))
+//
+// computed per tile of 96 timesteps as a tangent pass followed by a backward pass, with h1, h2 of the (fixed)
+// policy read from the activation cache:
+//
+//   dz1 = x~ dW0^T (+db0)                      MMA-1   A = x~      (TMEM)  B = dW0  (smem, K-major)
+//   dh1 = (1 - h1^2) dz1                       E1      TMEM -> registers -> TMEM
+//   dz2 = h1 dW1^T + dh1 W1^T (+db1)           MMA-2   A = h1, dh1 (TMEM)  B = dW1, W1
+//   dh2 = (1 - h2^2) dz2;  dmu = h2 dW2^T + dh2 W2^T + db2;  u = M dmu;  gz2 = (u W2)(1 - h2^2)     E2 (CUDA cores)
+//   gh1 = gz2 W1                               MMA-5   A = gz2     (TMEM)  B = W1^T
+//   gz1 = gh1 (1 - h1^2)                       E3
+//   gW2 += h2^T u,  gW1 += gz2^T h1,  gW0 += gz1^T [x~ 1]          weight-gradient MMAs, A and B from smem,
+//                                                                   accumulators stay in TMEM for the whole kernel
+//
+// Precision: kind::tf32 with error compensation.  The tensor core truncates an fp32 operand to tf32, so the
+// "hi" plane of every operand is the RAW fp32 value and the "lo" plane is x - trunc(x): a*b = hi*hi + lo*hi +
+// hi*lo (+ lo*lo where it is free), 1e-6 relative (profiles/probes/umma2_probe.cu), i.e. fp32-class like the
+// reference.  Forward-type products issue the three terms into one accumulator; the weight gradients stack
+// [hi | lo] along M and along N, so ONE instruction per 8 timesteps yields all four blocks, summed at the end.
+//
+// Layouts (all measured in the probe): K-major operands use the 128-byte swizzle (16-byte atoms); MN-major
+// tf32 operands -- everything contracted over the timestep -- only exist with the 128-byte swizzle on 32-byte
+// atoms (SWIZZLE_128B_BASE32B), so the activation cache is stored in HBM in exactly that order and a tile
+// lands in shared memory by ONE linear bulk copy, ready to be a weight-gradient operand.
+//
+// Roles: warps 0-2 own the 96 rows (TMEM lanes 0-95: thread = timestep), warp 3 feeds the bulk copies and sums
+// the bias gradients, one elected lane of warp 4 issues every MMA.  All hand-offs are mbarriers.
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "policy_tile.cuh"
+
+namespace pol {
+namespace tc {
+
+constexpr int ROWS = 96;            // timesteps per tile (smem bound: four 24 KB planes next to 104 KB of weights)
+constexpr int H = 64;               // hidden width
+constexpr int KX = 16;              // padded width of [x~, 1]
+constexpr int MJ = 8;               // largest action dimension
+constexpr int NTHREADS = 160;
+constexpr int ETHREADS = ROWS;      // epilogue threads (warps 0-2)
+constexpr int KSTEPS = ROWS / 8;    // weight-gradient MMAs per product and tile
+
+// ---- shared memory map (bytes) -------------------------------------------------------------------------
+constexpr uint32_t PLANE = ROWS * 256;              // 96 rows x 64 fp32 = 2 blocks of [96][128 B]
+constexpr uint32_t BLK = ROWS * 128;                // one block of 32 columns
+constexpr uint32_t OFF_X = 0;                       // h1 (raw = hi)              } adjacent: [h1_hi | h1_lo] is one
+constexpr uint32_t OFF_W = OFF_X + PLANE;           // h1 lo                      } N = 128 MN-major operand
+constexpr uint32_t OFF_Y = OFF_W + PLANE;           // h2 -> gz2 hi -> gz1 hi     } adjacent: one M = 128 operand
+constexpr uint32_t OFF_Z = OFF_Y + PLANE;           // h2 lo -> gz2 lo -> gz1 lo  }
+constexpr uint32_t WPLANE = H * 256;                // [64 rows][64 K] K-major, 128 B swizzle: 2 blocks of [64][128 B]
+constexpr uint32_t OFF_DW1 = OFF_Z + PLANE;         // hi, lo
+constexpr uint32_t OFF_W1 = OFF_DW1 + 2 * WPLANE;
+constexpr uint32_t OFF_W1T = OFF_W1 + 2 * WPLANE;
+constexpr uint32_t W0PLANE = H * 64;                // [64 rows][16 K] K-major, 64 B swizzle
+constexpr uint32_t OFF_DW0 = OFF_W1T + 2 * WPLANE;  // hi, lo
+constexpr uint32_t XTPLANE = 3 * 32 * 128;          // [32 rows = x~ hi (16) | x~ lo (16)][96 t] K-major: 3 blocks of [32][128 B]
+constexpr uint32_t OFF_XT = OFF_DW0 + 2 * W0PLANE;
+constexpr uint32_t UTPLANE = 3 * 16 * 128;          // [16 rows = u hi (8) | u lo (8)][96 t]
+constexpr uint32_t OFF_UT = OFF_XT + XTPLANE;
+constexpr uint32_t OFF_VEC = OFF_UT + UTPLANE;      // fp32 vectors, see Vec
+constexpr uint32_t VEC_FLOATS = 2 * MJ * H + H + 3 * MJ + 2 * KX + ROWS * MJ;
+constexpr uint32_t OFF_BAR = OFF_VEC + 4 * VEC_FLOATS;
+constexpr int NBAR = 20;
+constexpr uint32_t SMEM_BYTES = OFF_BAR + 8 * NBAR + 16;
+constexpr uint32_t SMEM_ALLOC = SMEM_BYTES + 1024;  // the base is aligned up to 1024 in the kernel
+struct Vec {   // float offsets inside the vector block
+  static constexpr int W2 = 0;                 // [MJ][64]
+  static constexpr int DW2 = MJ * H;           // [MJ][64]
+  static constexpr int DB1 = 2 * MJ * H;       // [64]
+  static constexpr int DB2 = DB1 + H;          // [MJ]
+  static constexpr int FISHER = DB2 + MJ;      // [MJ]
+  static constexpr int PADV = FISHER + MJ;     // [MJ] spare
+  static constexpr int ISHIFT = PADV + MJ;     // [KX]
+  static constexpr int IRCP = ISHIFT + KX;     // [KX] 1/(in_scale + 1e-8)
+  static constexpr int UARR = IRCP + KX;       // [96][MJ] u of the tile (bias gradient gb2)
+};
+// barriers
+enum { B_H1 = 0, B_H2, B_E0, B_E1, B_E2A, B_E2B, B_E2C, B_E3, B_M1, B_M2A, B_M2B, B_GW2, B_M5, B_GW1, B_GW0, B_W3 };
+
+// ---- tensor memory map (columns) ------------------------------------------------------------------------
+constexpr uint32_t T_D1 = 0;        // dz1 -> dh1 hi (in place) -> gh1
+constexpr uint32_t T_LO1 = 64;      // x~ hi (64..79), x~ lo (80..95) -> dh1 lo (64..127)
+constexpr uint32_t T_D2 = 128;      // dz2
+constexpr uint32_t T_A1 = 192;      // h1 hi (192..255), h1 lo (256..319) -> gz2 hi, gz2 lo
+constexpr uint32_t T_ACC1 = 320;    // gW1: 128 lanes [gz2 hi | gz2 lo] x 128 columns [h1 hi | h1 lo]
+constexpr uint32_t T_ACC0 = 448;    // gW0: x 32 columns [x~ hi | x~ lo]
+constexpr uint32_t T_ACC2 = 480;    // gW2: 128 lanes [h2 hi | h2 lo] x 16 columns [u hi | u lo]
+constexpr uint32_t T_COLS = 512;
+
+// ---- PTX wrappers ----------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t elect_one() {
+  uint32_t pred = 0, laneid = 0;
+  asm volatile("{\n\t.reg .b32 %%rx;\n\t.reg .pred %%px;\n\telect.sync %%rx|%%px, %2;\n\t@%%px mov.s32 %1, 1;\n\tmov.s32 %0, %%rx;\n\t}\n"
+               : "+r"(laneid), "+r"(pred) : "r"(0xFFFFFFFFu));
+  return pred;
+}
+// layout: 1 = 128 B swizzle on 32 B atoms (MN-major tf32), 2 = 128 B swizzle, 4 = 64 B swizzle
+__device__ __forceinline__ uint64_t make_desc(uint32_t start, uint32_t lbo, uint32_t sbo, uint32_t layout) {
+  uint64_t d = (uint64_t)((start >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)layout << 61;
+  return d;
+}
+__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void mma_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t id, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
+               :: "r"(d), "l"(a), "l"(b), "r"(id), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void mma_ts(uint32_t d, uint32_t a, uint64_t b, uint32_t id, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}\n"
+               :: "r"(d), "r"(a), "l"(b), "r"(id), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+#define TC_R16(v, o) "=r"(v[o + 0]), "=r"(v[o + 1]), "=r"(v[o + 2]), "=r"(v[o + 3]), "=r"(v[o + 4]), "=r"(v[o + 5]), "=r"(v[o + 6]), "=r"(v[o + 7]), \
+                     "=r"(v[o + 8]), "=r"(v[o + 9]), "=r"(v[o + 10]), "=r"(v[o + 11]), "=r"(v[o + 12]), "=r"(v[o + 13]), "=r"(v[o + 14]), "=r"(v[o + 15])
+#define TC_I16(v, o) "r"(v[o + 0]), "r"(v[o + 1]), "r"(v[o + 2]), "r"(v[o + 3]), "r"(v[o + 4]), "r"(v[o + 5]), "r"(v[o + 6]), "r"(v[o + 7]), \
+                     "r"(v[o + 8]), "r"(v[o + 9]), "r"(v[o + 10]), "r"(v[o + 11]), "r"(v[o + 12]), "r"(v[o + 13]), "r"(v[o + 14]), "r"(v[o + 15])
+// 32x32b shape: lane L of warp w <-> TMEM lane 32 w + L; register j <-> column col0 + j
+__device__ __forceinline__ void tld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+               "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+               : TC_R16(v, 0), TC_R16(v, 16) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : TC_R16(v, 0) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tst32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+               "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+               :: "r"(taddr), TC_I16(v, 0), TC_I16(v, 16) : "memory");
+}
+__device__ __forceinline__ void tst16(uint32_t taddr, const uint32_t (&v)[16]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+               :: "r"(taddr), TC_I16(v, 0) : "memory");
+}
+// lo plane of the compensated product: x - trunc_tf32(x) (exact)
+__device__ __forceinline__ float lo_of(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+
+// ---- plane addressing ----------------------------------------------------------------------------------
+// MN-major planes ([96 rows = timesteps][64 columns]): 2 blocks of 32 columns, rows of 128 B, 32-byte atoms
+// swizzled by the row index mod 4.  A thread owns one row; `q` = 32-byte atom 0..7 of the 64 columns.
+__device__ __forceinline__ uint32_t mn_atom(int r, int q) {
+  return (uint32_t)(q >> 2) * BLK + (uint32_t)r * 128u + (uint32_t)(((q & 3) ^ (r & 3)) << 5);
+}
+// K-major plane, 128 B swizzle: [R rows][K columns], blocks of 32 columns
+__host__ __device__ inline uint32_t k128_off(int R, int r, int k) {
+  return (uint32_t)(k >> 5) * R * 128u + (uint32_t)r * 128u + (uint32_t)((((k & 31) >> 2) ^ (r & 7)) << 4) + (uint32_t)(k & 3) * 4u;
+}
+// K-major plane, 64 B swizzle: [R rows][16 columns]
+__host__ __device__ inline uint32_t k64_off(int r, int k) {
+  return (uint32_t)r * 64u + (uint32_t)((((k & 15) >> 2) ^ ((r >> 1) & 3)) << 4) + (uint32_t)(k & 3) * 4u;
+}
+
+struct TcArgs {
+  const float* params;
+  const float* vec;
+  const float* obs;
+  const float* cache;     // tc region: per tile [h1 plane | h2 plane] in shared-memory order
+  const float* in_shift;
+  const float* in_scale;
+  const float* out_scale;
+  float* partials;        // [grid][dstride]
+  const int32_t* stop_flag;
+  long long N;
+  int n, m, dstride;
+};
+
+__device__ __forceinline__ void load_row32(const unsigned char* plane, int r, int blk, float (&v)[32]) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float4* p = reinterpret_cast<const float4*>(plane + mn_atom(r, blk * 4 + q));
+    const float4 a = p[0], b = p[1];
+    v[8 * q + 0] = a.x; v[8 * q + 1] = a.y; v[8 * q + 2] = a.z; v[8 * q + 3] = a.w;
+    v[8 * q + 4] = b.x; v[8 * q + 5] = b.y; v[8 * q + 6] = b.z; v[8 * q + 7] = b.w;
+  }
+}
+__device__ __forceinline__ void store_row32(unsigned char* plane, int r, int blk, const float (&v)[32]) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float4* p = reinterpret_cast<float4*>(plane + mn_atom(r, blk * 4 + q));
+    p[0] = make_float4(v[8 * q + 0], v[8 * q + 1], v[8 * q + 2], v[8 * q + 3]);
+    p[1] = make_float4(v[8 * q + 4], v[8 * q + 5], v[8 * q + 6], v[8 * q + 7]);
+  }
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
+  extern __shared__ unsigned char smraw[];
+  __shared__ uint32_t tslot;
+  if (a.stop_flag && *a.stop_flag) return;
+  const uint32_t sraw = smem_u32(smraw);
+  const uint32_t sb = (sraw + 1023u) & ~1023u;
+  unsigned char* sm = smraw + (sb - sraw);
+  float* vecs = reinterpret_cast<float*>(sm + OFF_VEC);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + OFF_BAR);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n = a.n, m = a.m;
+  const Flat F(n, m, H, H);
+  const int ntiles = (int)((a.N + ROWS - 1) / ROWS);
+
+  // ---- one-time staging ---------------------------------------------------------------------------------
+  for (uint32_t i = tid; i < (OFF_VEC - OFF_DW1) / 16; i += NTHREADS)
+    reinterpret_cast<float4*>(sm + OFF_DW1)[i] = make_float4(0.f, 0.f, 0.f, 0.f);   // weights, x~^T, u^T planes
+  for (uint32_t i = tid; i < VEC_FLOATS; i += NTHREADS) vecs[i] = 0.f;
+  if (tid == 0) {
+    tma::mbar_init(&bar[B_H1], 1); tma::mbar_init(&bar[B_H2], 1);
+    for (int b = B_E0; b <= B_E3; ++b) tma::mbar_init(&bar[b], ETHREADS);
+    for (int b = B_M1; b <= B_GW0; ++b) tma::mbar_init(&bar[b], 1);
+    tma::mbar_init(&bar[B_W3], 32);
+    tma::mbar_init_fence();
+  }
+  if (warp == 4) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(smem_u32(&tslot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  __syncthreads();
+  {
+    const float* P = a.params; const float* V = a.vec;
+    auto put = [&](uint32_t plane_hi, uint32_t plane_bytes, uint32_t off, float w) {
+      *reinterpret_cast<float*>(sm + plane_hi + off) = w;                      // raw: the tensor core truncates
+      *reinterpret_cast<float*>(sm + plane_hi + plane_bytes + off) = lo_of(w);
+    };
+    for (int i = tid; i < H * H; i += NTHREADS) {
+      const int o = i >> 6, k = i & 63;
+      const float w = __ldg(P + F.oW1 + i);
+      put(OFF_W1, WPLANE, k128_off(H, o, k), w);            // B[N = o][K = i]: dh1 W1^T
+      put(OFF_W1T, WPLANE, k128_off(H, k, o), w);           // B[N = i][K = o]: gz2 W1
+      put(OFF_DW1, WPLANE, k128_off(H, o, k), __ldg(V + F.oW1 + i));
+    }
+    for (int i = tid; i < H * n; i += NTHREADS) {
+      const int o = i / n, k = i - o * n;
+      put(OFF_DW0, W0PLANE, k64_off(o, k), __ldg(V + F.oW0 + i));
+    }
+    for (int o = tid; o < H; o += NTHREADS) {
+      put(OFF_DW0, W0PLANE, k64_off(o, n), __ldg(V + F.ob0 + o));   // db0 rides on the ones column of x~
+      vecs[Vec::DB1 + o] = __ldg(V + F.ob1 + o);
+    }
+    for (int i = tid; i < m * H; i += NTHREADS) {
+      vecs[Vec::W2 + i] = __ldg(P + F.oW2 + i);
+      vecs[Vec::DW2 + i] = __ldg(V + F.oW2 + i);
+    }
+    for (int j = tid; j < m; j += NTHREADS) {
+      vecs[Vec::DB2 + j] = __ldg(V + F.ob2 + j);
+      const float sg = expf(__ldg(P + F.ols + j));
+      const float os = a.out_scale ? __ldg(a.out_scale + j) : 1.f;
+      // d^2 KL / d mu^2 = 2/(2 sigma^2 + 1e-8) (gaussian_mlp.py:137-138), chained through out_scale twice
+      vecs[Vec::FISHER + j] = os * os * (2.f / (2.f * sg * sg + 1e-8f));
+    }
+    for (int k = tid; k < n; k += NTHREADS) {
+      vecs[Vec::ISHIFT + k] = a.in_shift ? __ldg(a.in_shift + k) : 0.f;
+      vecs[Vec::IRCP + k] = 1.f / ((a.in_scale ? __ldg(a.in_scale + k) : 1.f) + 1e-8f);
+    }
+  }
+  fence_async();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tb = tslot;
+
+  const unsigned char* pX = sm + OFF_X; unsigned char* pW = sm + OFF_W;
+  unsigned char* pY = sm + OFF_Y; unsigned char* pZ = sm + OFF_Z;
+  const float* tile_base = a.cache;     // + tile * 2 * PLANE / 4
+
+  if (warp < 3) {
+    // =========================== epilogue warps: thread = timestep row ===================================
+    const int r = tid;
+    const uint32_t tl = tb + ((uint32_t)(32 * warp) << 16);   // this warp's lane quadrant
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const uint32_t ph = it & 1;
+      const long long t = (long long)tile * ROWS + r;
+      const bool valid = t < a.N;
+      // x~ of this row: [ (obs - shift) / (scale + 1e-8), 1, 0.. ]
+      float xs[KX];
+      auto load_x = [&]() {
+#pragma unroll
+        for (int k = 0; k < KX; ++k) {
+          float v = 0.f;
+          if (valid && k < n) v = (__ldg(a.obs + t * n + k) - vecs[Vec::ISHIFT + k]) * vecs[Vec::IRCP + k];
+          if (valid && k == n) v = 1.f;
+          xs[k] = v;
+        }
+      };
+      // ---- E0: x~ and h1 as tensor-memory A operands, h1 lo as a weight-gradient operand -----------------
+      load_x();
+      {
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int k = 0; k < KX; ++k) { hi[k] = __float_as_uint(xs[k]); lo[k] = __float_as_uint(lo_of(xs[k])); }
+        tst16(tl + T_LO1, hi);
+        tst16(tl + T_LO1 + 16, lo);
+      }
+      tma::mbar_wait(&bar[B_H1], ph);
+#pragma unroll
+      for (int blk = 0; blk < 2; ++blk) {
+        float h[32];
+        uint32_t u32[32];
+        load_row32(pX, r, blk, h);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) u32[i] = __float_as_uint(h[i]);
+        tst32(tl + T_A1 + 32 * blk, u32);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) { h[i] = lo_of(h[i]); u32[i] = __float_as_uint(h[i]); }
+        tst32(tl + T_A1 + 64 + 32 * blk, u32);
+        store_row32(pW, r, blk, h);
+      }
+      wait_st();
+      fence_async();
+      fence_before();
+      mbar_arrive(&bar[B_E0]);
+
+      // ---- E1: dh1 = (1 - h1^2) dz1, in place over dz1 (hi) and next to it (lo) ---------------------------
+      tma::mbar_wait(&bar[B_M1], ph);
+      fence_after();
+#pragma unroll
+      for (int blk = 0; blk < 2; ++blk) {
+        float h[32];
+        uint32_t d[32], l[32];
+        tld32(tl + T_D1 + 32 * blk, d);
+        load_row32(pX, r, blk, h);
+        wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float v = __uint_as_float(d[i]) * fmaf(-h[i], h[i], 1.f);
+          d[i] = __float_as_uint(v); l[i] = __float_as_uint(lo_of(v));
+        }
+        tst32(tl + T_D1 + 32 * blk, d);
+        tst32(tl + T_LO1 + 32 * blk, l);
+      }
+      wait_st();
+      fence_before();
+      mbar_arrive(&bar[B_E1]);
+
+      // ---- E2: head on the CUDA cores: dh2, dmu, u, gz2 ---------------------------------------------------
+      tma::mbar_wait(&bar[B_H2], ph);
+      tma::mbar_wait(&bar[B_M2B], ph);
+      fence_after();
+      float dmu[MJ];
+#pragma unroll
+      for (int j = 0; j < MJ; ++j) dmu[j] = 0.f;
+#pragma unroll
+      for (int blk = 0; blk < 2; ++blk) {
+        float h[32];
+        uint32_t d[32];
+        tld32(tl + T_D2 + 32 * blk, d);
+        load_row32(pY, r, blk, h);
+        wait_ld();
+        float dh[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          dh[i] = (__uint_as_float(d[i]) + vecs[Vec::DB1 + 32 * blk + i]) * fmaf(-h[i], h[i], 1.f);
+#pragma unroll
+        for (int j = 0; j < MJ; ++j) {
+          if (j < m) {
+            const float4* w2 = reinterpret_cast<const float4*>(vecs + Vec::W2 + j * H + 32 * blk);
+            const float4* v2 = reinterpret_cast<const float4*>(vecs + Vec::DW2 + j * H + 32 * blk);
+            float acc = dmu[j];
+#pragma unroll
+            for (int i4 = 0; i4 < 8; ++i4) {
+              const float4 w = w2[i4], v = v2[i4];
+              acc = fmaf(h[4 * i4 + 0], v.x, acc); acc = fmaf(dh[4 * i4 + 0], w.x, acc);
+              acc = fmaf(h[4 * i4 + 1], v.y, acc); acc = fmaf(dh[4 * i4 + 1], w.y, acc);
+              acc = fmaf(h[4 * i4 + 2], v.z, acc); acc = fmaf(dh[4 * i4 + 2], w.z, acc);
+              acc = fmaf(h[4 * i4 + 3], v.w, acc); acc = fmaf(dh[4 * i4 + 3], w.w, acc);
+            }
+            dmu[j] = acc;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) h[i] = lo_of(h[i]);
+        store_row32(pZ, r, blk, h);                      // h2 lo: weight-gradient operand of gW2
+      }
+      float u[MJ];
+#pragma unroll
+      for (int j = 0; j < MJ; ++j) {
+        u[j] = (valid && j < m) ? vecs[Vec::FISHER + j] * (dmu[j] + vecs[Vec::DB2 + j]) : 0.f;
+        // u^T planes, K-major over the timestep: rows j (hi) and 8 + j (lo), column r
+        *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, j, r)) = u[j];
+        *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, 8 + j, r)) = lo_of(u[j]);
+        vecs[Vec::UARR + r * MJ + j] = u[j];
+      }
+      fence_async();
+      mbar_arrive(&bar[B_E2A]);
+      // gz2 = (u W2) (1 - h2^2): A operand of MMA-5 now, weight-gradient operand once gW2 has read h2
+      float gz[64];
+#pragma unroll
+      for (int blk = 0; blk < 2; ++blk) {
+        float h[32];
+        load_row32(pY, r, blk, h);
+        uint32_t hi[32], lo[32];
+#pragma unroll
+        for (int i4 = 0; i4 < 8; ++i4) {
+          float g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f;
+#pragma unroll
+          for (int j = 0; j < MJ; ++j) {
+            if (j < m) {
+              const float4 w = *reinterpret_cast<const float4*>(vecs + Vec::W2 + j * H + 32 * blk + 4 * i4);
+              g0 = fmaf(u[j], w.x, g0); g1 = fmaf(u[j], w.y, g1); g2 = fmaf(u[j], w.z, g2); g3 = fmaf(u[j], w.w, g3);
+            }
+          }
+          gz[32 * blk + 4 * i4 + 0] = g0 * fmaf(-h[4 * i4 + 0], h[4 * i4 + 0], 1.f);
+          gz[32 * blk + 4 * i4 + 1] = g1 * fmaf(-h[4 * i4 + 1], h[4 * i4 + 1], 1.f);
+          gz[32 * blk + 4 * i4 + 2] = g2 * fmaf(-h[4 * i4 + 2], h[4 * i4 + 2], 1.f);
+          gz[32 * blk + 4 * i4 + 3] = g3 * fmaf(-h[4 * i4 + 3], h[4 * i4 + 3], 1.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) { hi[i] = __float_as_uint(gz[32 * blk + i]); lo[i] = __float_as_uint(lo_of(gz[32 * blk + i])); }
+        tst32(tl + T_A1 + 32 * blk, hi);
+        tst32(tl + T_A1 + 64 + 32 * blk, lo);
+      }
+      wait_st();
+      fence_before();
+      mbar_arrive(&bar[B_E2B]);
+      tma::mbar_wait(&bar[B_GW2], ph);                  // gW2 has read h2 hi | lo: the planes become gz2
+#pragma unroll
+      for (int blk = 0; blk < 2; ++blk) {
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = gz[32 * blk + i];
+        store_row32(pY, r, blk, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = lo_of(v[i]);
+        store_row32(pZ, r, blk, v);
+      }
+      fence_async();
+      mbar_arrive(&bar[B_E2C]);
+
+      // ---- E3: gz1 = gh1 (1 - h1^2); x~^T planes for gW0 -------------------------------------------------
+      tma::mbar_wait(&bar[B_M5], ph);
+      fence_after();
+#pragma unroll
+      for (int blk = 0; blk < 2; ++blk) {
+        float h[32];
+        uint32_t d[32];
+        tld32(tl + T_D1 + 32 * blk, d);
+        load_row32(pX, r, blk, h);
+        wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) gz[32 * blk + i] = valid ? __uint_as_float(d[i]) * fmaf(-h[i], h[i], 1.f) : 0.f;
+      }
+      fence_before();
+      tma::mbar_wait(&bar[B_GW1], ph);                  // gW1 has read gz2 and h1 (and every earlier MMA is done)
+      tma::mbar_wait(&bar[B_W3], ph);                   // warp 3 has summed gz2 for gb1
+#pragma unroll
+      for (int blk = 0; blk < 2; ++blk) {
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = gz[32 * blk + i];
+        store_row32(pY, r, blk, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = lo_of(v[i]);
+        store_row32(pZ, r, blk, v);
+      }
+#pragma unroll
+      for (int k = 0; k < KX; ++k) {
+        *reinterpret_cast<float*>(sm + OFF_XT + k128_off(32, k, r)) = xs[k];
+        *reinterpret_cast<float*>(sm + OFF_XT + k128_off(32, 16 + k, r)) = lo_of(xs[k]);
+      }
+      fence_async();
+      mbar_arrive(&bar[B_E3]);
+    }
+  } else if (warp == 3) {
+    // =========================== loader + bias gradients ==================================================
+    double gb1a = 0.0, gb1b = 0.0, gb2 = 0.0;
+    auto load_plane = [&](int tile, int which) {   // which 0: h1 -> X, 1: h2 -> Y
+      if (lane == 0) {
+        uint64_t* b = &bar[which ? B_H2 : B_H1];
+        tma::mbar_expect(b, PLANE);
+        tma::bulk_g2s(sm + (which ? OFF_Y : OFF_X), tile_base + (size_t)tile * (2 * PLANE / 4) + (which ? PLANE / 4 : 0), PLANE, b);
+      }
+    };
+    if ((int)blockIdx.x < ntiles) { load_plane(blockIdx.x, 0); load_plane(blockIdx.x, 1); }
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const uint32_t ph = it & 1;
+      tma::mbar_wait(&bar[B_E2C], ph);       // gz2 (hi = the full fp32 value) is in Y, u in UARR
+      {
+        const int c0 = 2 * lane, q = c0 >> 3;
+        double s0 = 0.0, s1 = 0.0;
+        float f0 = 0.f, f1 = 0.f;
+#pragma unroll 4
+        for (int rr = 0; rr < ROWS; ++rr) {
+          const float2 v = *reinterpret_cast<const float2*>(pY + mn_atom(rr, q) + (c0 & 7) * 4);
+          f0 += v.x; f1 += v.y;
+          if ((rr & 15) == 15) { s0 += (double)f0; s1 += (double)f1; f0 = 0.f; f1 = 0.f; }
+        }
+        gb1a += s0; gb1b += s1;
+        if (lane < MJ) {
+          float f = 0.f;
+          for (int rr = 0; rr < ROWS; ++rr) f += vecs[Vec::UARR + rr * MJ + lane];
+          gb2 += (double)f;
+        }
+      }
+      mbar_arrive(&bar[B_W3]);
+      const int next = tile + gridDim.x;
+      tma::mbar_wait(&bar[B_E3], ph);        // gW1 is done and every row thread has read its h1 row for the last time
+      if (next < ntiles) load_plane(next, 0);
+      tma::mbar_wait(&bar[B_GW0], ph);       // gz1 planes (Y, Z) are free
+      if (next < ntiles) load_plane(next, 1);
+    }
+    float* out = a.partials + (size_t)blockIdx.x * a.dstride;
+    out[F.ob1 + 2 * lane] = (float)gb1a;
+    out[F.ob1 + 2 * lane + 1] = (float)gb1b;
+    if (lane < m) out[F.ob2 + lane] = (float)gb2;
+  } else {
+    // =========================== MMA issuer (one elected lane of warp 4) ==================================
+    const uint32_t ID_FWD = idesc_tf32(128, 64, 0, 0);
+    const uint32_t ID_GW1 = idesc_tf32(128, 128, 1, 1);
+    const uint32_t ID_GW0 = idesc_tf32(128, 32, 1, 0);
+    const uint32_t ID_GW2 = idesc_tf32(128, 16, 1, 0);
+    // K-major weights: k-step ks covers columns 8 ks..: block ks/4, 32 bytes per step inside the 128-byte row
+    auto wdesc = [&](uint32_t off, int ks) {
+      return make_desc(sb + off + (uint32_t)(ks >> 2) * (H * 128u) + (uint32_t)(ks & 3) * 32u, 16u, 1024u, 2u);
+    };
+    auto w0desc = [&](uint32_t off, int ks) { return make_desc(sb + off + (uint32_t)ks * 32u, 16u, 512u, 4u); };
+    // MN-major planes: k-step = 8 rows = 1024 bytes; 32-column blocks BLK apart; 4-row atoms 512 bytes apart
+    auto mndesc = [&](uint32_t off, int ks) { return make_desc(sb + off + (uint32_t)ks * 1024u, BLK, 512u, 1u); };
+    // K-major planes over the timestep ([R rows][96 t]): block = 32 timesteps
+    auto ktdesc = [&](uint32_t off, int R, int ks) {
+      return make_desc(sb + off + (uint32_t)(ks >> 2) * (uint32_t)R * 128u + (uint32_t)(ks & 3) * 32u, 16u, 1024u, 2u);
+    };
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const uint32_t ph = it & 1;
+      const uint32_t first = it == 0 ? 0u : 1u;
+      tma::mbar_wait(&bar[B_E0], ph);
+      fence_after();
+      if (elect_one()) {
+        // MMA-1: dz1 = [x~ hi | lo] dW0^T     (K = 16)
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) {
+          mma_ts(tb + T_D1, tb + T_LO1 + 8 * ks, w0desc(OFF_DW0, ks), ID_FWD, ks > 0);
+          mma_ts(tb + T_D1, tb + T_LO1 + 16 + 8 * ks, w0desc(OFF_DW0, ks), ID_FWD, 1);
+          mma_ts(tb + T_D1, tb + T_LO1 + 8 * ks, w0desc(OFF_DW0 + W0PLANE, ks), ID_FWD, 1);
+        }
+        commit(&bar[B_M1]);
+        // MMA-2a: dz2 = h1 dW1^T
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          mma_ts(tb + T_D2, tb + T_A1 + 8 * ks, wdesc(OFF_DW1, ks), ID_FWD, ks > 0);
+          mma_ts(tb + T_D2, tb + T_A1 + 64 + 8 * ks, wdesc(OFF_DW1, ks), ID_FWD, 1);
+          mma_ts(tb + T_D2, tb + T_A1 + 8 * ks, wdesc(OFF_DW1 + WPLANE, ks), ID_FWD, 1);
+        }
+        commit(&bar[B_M2A]);
+      }
+      __syncwarp();
+      tma::mbar_wait(&bar[B_E1], ph);
+      fence_after();
+      if (elect_one()) {
+        // MMA-2b: dz2 += dh1 W1^T
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          mma_ts(tb + T_D2, tb + T_D1 + 8 * ks, wdesc(OFF_W1, ks), ID_FWD, 1);
+          mma_ts(tb + T_D2, tb + T_LO1 + 8 * ks, wdesc(OFF_W1, ks), ID_FWD, 1);
+          mma_ts(tb + T_D2, tb + T_D1 + 8 * ks, wdesc(OFF_W1 + WPLANE, ks), ID_FWD, 1);
+        }
+        commit(&bar[B_M2B]);
+      }
+      __syncwarp();
+      tma::mbar_wait(&bar[B_E2A], ph);
+      fence_after();
+      if (elect_one()) {
+        // gW2 (+)= [h2 hi | lo]^T [u hi | lo]
+#pragma unroll
+        for (int ks = 0; ks < KSTEPS; ++ks)
+          mma_ss(tb + T_ACC2, mndesc(OFF_Y, ks), ktdesc(OFF_UT, 16, ks), ID_GW2, first | (ks > 0));
+        commit(&bar[B_GW2]);
+      }
+      __syncwarp();
+      tma::mbar_wait(&bar[B_E2B], ph);
+      fence_after();
+      if (elect_one()) {
+        // MMA-5: gh1 = gz2 W1
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          mma_ts(tb + T_D1, tb + T_A1 + 8 * ks, wdesc(OFF_W1T, ks), ID_FWD, ks > 0);
+          mma_ts(tb + T_D1, tb + T_A1 + 64 + 8 * ks, wdesc(OFF_W1T, ks), ID_FWD, 1);
+          mma_ts(tb + T_D1, tb + T_A1 + 8 * ks, wdesc(OFF_W1T + WPLANE, ks), ID_FWD, 1);
+        }
+        commit(&bar[B_M5]);
+      }
+      __syncwarp();
+      tma::mbar_wait(&bar[B_E2C], ph);
+      fence_after();
+      if (elect_one()) {
+        // gW1 (+)= [gz2 hi | lo]^T [h1 hi | lo]
+#pragma unroll
+        for (int ks = 0; ks < KSTEPS; ++ks)
+          mma_ss(tb + T_ACC1, mndesc(OFF_Y, ks), mndesc(OFF_X, ks), ID_GW1, first | (ks > 0));
+        commit(&bar[B_GW1]);
+      }
+      __syncwarp();
+      tma::mbar_wait(&bar[B_E3], ph);
+      fence_after();
+      if (elect_one()) {
+        // gW0 (+)= [gz1 hi | lo]^T [x~ hi | lo]
+#pragma unroll
+        for (int ks = 0; ks < KSTEPS; ++ks)
+          mma_ss(tb + T_ACC0, mndesc(OFF_Y, ks), ktdesc(OFF_XT, 32, ks), ID_GW0, first | (ks > 0));
+        commit(&bar[B_GW0]);
+      }
+      __syncwarp();
+    }
+  }
+
+  // ---- all tiles done: accumulators -> per-CTA partial sums in flat parameter order -------------------------
+  {
+    int nit = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) ++nit;
+    if (nit > 0 && warp != 3) tma::mbar_wait(&bar[B_GW0], (nit - 1) & 1);   // warp 3 has waited for it already
+    fence_after();
+    __syncthreads();
+    float* stage = reinterpret_cast<float*>(sm);         // [128 lanes][176]: the plane region is free now
+    constexpr int SW = 176;
+    if (warp < 4) {
+      const uint32_t tl = tb + ((uint32_t)(32 * warp) << 16);
+      float* row = stage + (size_t)tid * SW;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 128; c0 += 32) {
+        uint32_t v[32];
+        tld32(tl + T_ACC1 + c0, v);
+        wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) row[c0 + i] = __uint_as_float(v[i]);
+      }
+      {
+        uint32_t v[32];
+        tld32(tl + T_ACC0, v);
+        wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) row[128 + i] = __uint_as_float(v[i]);
+        uint32_t w[16];
+        tld16(tl + T_ACC2, w);
+        wait_ld();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) row[160 + i] = __uint_as_float(w[i]);
+      }
+    }
+    fence_before();
+    __syncthreads();
+    float* out = a.partials + (size_t)blockIdx.x * a.dstride;
+    if (nit == 0) {
+      for (int i = tid; i < F.ols; i += NTHREADS) out[i] = 0.f;
+    } else {
+      auto S = [&](int lane_, int col) { return stage[(size_t)lane_ * SW + col]; };
+      for (int i = tid; i < H * H; i += NTHREADS) {        // gW1[o][i]: lanes o | 64 + o, columns i | 64 + i
+        const int o = i >> 6, k = i & 63;
+        out[F.oW1 + i] = (S(o, k) + S(o, 64 + k)) + (S(64 + o, k) + S(64 + o, 64 + k));
+      }
+      for (int i = tid; i < H * (n + 1); i += NTHREADS) {  // gW0[o][k], gb0[o] = column n
+        const int o = i / (n + 1), k = i - o * (n + 1);
+        const float v = (S(o, 128 + k) + S(o, 144 + k)) + (S(64 + o, 128 + k) + S(64 + o, 144 + k));
+        if (k < n) out[F.oW0 + o * n + k] = v; else out[F.ob0 + o] = v;
+      }
+      for (int i = tid; i < m * H; i += NTHREADS) {        // gW2[j][h]: lanes h | 64 + h, columns j | 8 + j
+        const int j = i >> 6, h = i & 63;
+        out[F.oW2 + i] = (S(h, 160 + j) + S(h, 168 + j)) + (S(64 + h, 160 + j) + S(64 + h, 168 + j));
+      }
+    }
+    __syncthreads();
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tb) : "memory");
+  }
+}
+
+// Activation cache of the rows-in-registers kernels (MMA-fragment order, pol_rows.cuh) -> tile planes in the
+// shared-memory order of this kernel.  One thread moves one 32-byte atom of h1 and of h2; rows past N are zero.
+__global__ void __launch_bounds__(256) tc_fill_kernel(const float* __restrict__ frag, float* __restrict__ out,
+                                                      long long N, long long natoms) {
+  constexpr int NF = H / 8;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < natoms; i += stride) {
+    const int q = (int)(i & 7);
+    const long long row = i >> 3;
+    const long long tile = row / ROWS;
+    const int r = (int)(row - tile * ROWS);
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, b0 = a0, b1 = a0;
+    if (row < N) {
+      const long long t64 = row >> 6;
+      const int r64 = (int)(row & 63), hw = r64 >> 4, rr = r64 & 15, g = rr & 7, isB = rr >> 3;
+      const float4* src = reinterpret_cast<const float4*>(
+          reinterpret_cast<const float2*>(frag) + ((size_t)(t64 * 4 + hw) * (4 * NF * 32) + (size_t)(2 * q + isB) * 32 + g * 4));
+      a0 = src[0]; a1 = src[1];
+      const float4* src2 = src + (2 * NF * 32) / 2;     // h2 slots follow the 2 NF h1 slots (float2 units)
+      b0 = src2[0]; b1 = src2[1];
+    }
+    float* dst = out + (size_t)tile * (2 * PLANE / 4) + mn_atom(r, q) / 4;
+    reinterpret_cast<float4*>(dst)[0] = a0; reinterpret_cast<float4*>(dst)[1] = a1;
+    reinterpret_cast<float4*>(dst + PLANE / 4)[0] = b0; reinterpret_cast<float4*>(dst + PLANE / 4)[1] = b1;
+  }
+}
+
+}  // namespace tc
+
+// ---- host side (declared in policy_tile.cuh) -------------------------------------------------------------
+bool tc_fits(const mjrl_ctx* ctx, int n, int m, int h1, int h2) {
+  static const bool off = getenv("MJRL_B200_FVP_TC") && getenv("MJRL_B200_FVP_TC")[0] == '0';
+  if (off || !ctx) return false;
+  if (h1 != tc::H || h2 != tc::H || n + 1 > tc::KX || m < 1 || m > tc::MJ) return false;
+  return (size_t)tc::SMEM_ALLOC <= (size_t)ctx->max_smem_optin;
+}
+
+long long tc_cache_floats(long long N) {
+  const long long ntiles = (N + tc::ROWS - 1) / tc::ROWS;
+  return ntiles * (2 * tc::PLANE / 4);
+}
+
+int launch_tc_fill(mjrl_ctx* ctx, const float* frag_cache, float* tc_cache, long long N, cudaStream_t s) {
+  const long long ntiles = (N + tc::ROWS - 1) / tc::ROWS;
+  const long long natoms = ntiles * tc::ROWS * 8;
+  long long blocks = (natoms + 255) / 256;
+  const long long cap = (long long)ctx->sm_count * 16;
+  if (blocks > cap) blocks = cap;
+  tc::tc_fill_kernel<<<(int)blocks, 256, 0, s>>>(frag_cache, tc_cache, N, natoms);
+  return mjrl_check_launch("tc_fill_kernel");
+}
+
+int launch_fvp_tc(mjrl_ctx* ctx, Args& a, const float* tc_cache, int* grid_out, cudaStream_t s) {
+  if (!tc_cache || !tc_fits(ctx, a.n, a.m, a.h1, a.h2)) return -1;
+  const Flat F(a.n, a.m, a.h1, a.h2);
+  const long long ntiles = (a.N + tc::ROWS - 1) / tc::ROWS;
+  int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
+  if (grid < 1) grid = 1;
+  *grid_out = grid;
+  a.dstride = (F.d + 31) & ~31;
+  a.partials = (float*)mjrl_scratch(ctx, sizeof(float) * (size_t)grid * a.dstride);
+  if (!a.partials) return MJRL_E_STATE;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(tc::fvp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_ALLOC);
+    if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute(fvp_tc): %s", cudaGetErrorString(e)); return (int)e; }
+    attr = true;
+  }
+  tc::TcArgs t;
+  t.params = a.params; t.vec = a.vec; t.obs = a.obs; t.cache = tc_cache;
+  t.in_shift = a.in_shift; t.in_scale = a.in_scale; t.out_scale = a.out_scale;
+  t.partials = a.partials; t.stop_flag = a.stop_flag; t.N = a.N; t.n = a.n; t.m = a.m; t.dstride = a.dstride;
+  tc::fvp_tc_kernel<<<grid, tc::NTHREADS, tc::SMEM_ALLOC, s>>>(t);
+  return mjrl_check_launch("fvp_tc_kernel");
+}
+
+}  // namespace pol

@@ -338,7 +338,8 @@ int mjrl_cg_solve(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* para
                                 k == 0 ? mode_first : mode_rest, stream);
     if (rc) return rc;
     if (k == 0 && jac_fill_after_first) {
-      rc = mjrl_policy_fvp_jac_fill(ctx, desc, params, N, cache, stream);
+      rc = jac_fill_after_first == 2 ? mjrl_policy_fvp_tc_fill(ctx, desc, N, cache, stream)
+                                     : mjrl_policy_fvp_jac_fill(ctx, desc, params, N, cache, stream);
       if (rc) return rc;
     }
     rc = peer ? mjrl_cg_update_peer(ctx, peer, st, d, inv_count, damping, residual_tol, epoch, stream)

@@ -1417,7 +1417,40 @@ int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc,
   int64_t cnt = ntiles * rows::TSR * 2 * HP;   // h1 and h2 of every (padded) timestep
   if (jac_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, nullptr, nullptr, nullptr))
     cnt += jac_cache_floats(desc->m, desc->h1, desc->h2, N);   // + the m Jacobian rows G1 (fvp_jac.cu)
+  if (tc_fits(ctx, desc->n, desc->m, desc->h1, desc->h2))
+    cnt += tc_cache_floats(N);                                  // + h1|h2 in the tile order of fvp_tc.cu
   return cnt;
+}
+
+// float offset of the tcgen05 kernel's tile-ordered region inside the cache buffer (after h1|h2 and G1)
+static int64_t tc_region_offset(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N) {
+  int HP, NPK;
+  size_t smem;
+  if (!rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem)) return -1;
+  const int64_t ntiles = (N + rows::TSR - 1) / rows::TSR;
+  int64_t off = ntiles * rows::TSR * 2 * HP;
+  if (jac_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, nullptr, nullptr, nullptr))
+    off += jac_cache_floats(desc->m, desc->h1, desc->h2, N);
+  return off;
+}
+
+int mjrl_policy_fvp_tc_ok(mjrl_ctx* ctx, const mjrl_policy_desc* desc) {
+  if (!ctx || !desc) return 0;
+  int HP, NPK;
+  size_t smem;
+  return rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem) && HP == 64 &&
+         tc_fits(ctx, desc->n, desc->m, desc->h1, desc->h2) ? 1 : 0;
+}
+
+int mjrl_policy_fvp_tc_fill(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N, float* cache, void* stream) {
+  int rc = check_desc(desc, "policy_fvp_tc_fill");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && cache && N > 0, MJRL_E_ARG, "policy_fvp_tc_fill: bad argument");
+  MJRL_REQUIRE(mjrl_policy_fvp_tc_ok(ctx, desc), MJRL_E_SHAPE,
+               "policy_fvp_tc_fill: this policy shape has no tcgen05 product");
+  const int64_t off = tc_region_offset(ctx, desc, N);
+  MJRL_REQUIRE(off >= 0, MJRL_E_SHAPE, "policy_fvp_tc_fill: shape not taken");
+  return launch_tc_fill(ctx, cache, cache + off, N, (cudaStream_t)stream);
 }
 
 int mjrl_policy_fvp_jac_ok(mjrl_ctx* ctx, const mjrl_policy_desc* desc) {
@@ -1452,7 +1485,7 @@ int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const fl
   int rc = check_desc(desc, "policy_fvp");
   if (rc) return rc;
   MJRL_REQUIRE(ctx && params && obs && vec && fvp_sum && N > 0, MJRL_E_ARG, "policy_fvp: bad argument");
-  MJRL_REQUIRE(cache_mode >= 0 && cache_mode <= 3 && (cache_mode == 0 || cache), MJRL_E_ARG,
+  MJRL_REQUIRE(cache_mode >= 0 && cache_mode <= 4 && (cache_mode == 0 || cache), MJRL_E_ARG,
                "policy_fvp: cache_mode %d needs a cache buffer", cache_mode);
   Args a = {};
   fill_desc(a, desc);
@@ -1465,6 +1498,12 @@ int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const fl
                  "policy_fvp: cache_mode 3 needs a shape mjrl_policy_fvp_jac_ok accepts");
     rc = launch_fvp_jac(ctx, a, &grid, s);
     MJRL_REQUIRE(rc >= 0, MJRL_E_SHAPE, "policy_fvp: Jacobian-cached product does not take this shape");
+  } else if (cache_mode == 4) {
+    MJRL_REQUIRE(mjrl_policy_fvp_tc_ok(ctx, desc), MJRL_E_SHAPE,
+                 "policy_fvp: cache_mode 4 needs a shape mjrl_policy_fvp_tc_ok accepts");
+    const int64_t off = tc_region_offset(ctx, desc, N);
+    rc = launch_fvp_tc(ctx, a, off >= 0 ? cache + off : nullptr, &grid, s);
+    MJRL_REQUIRE(rc >= 0, MJRL_E_SHAPE, "policy_fvp: tcgen05 product does not take this shape");
   } else {
     rc = launch_any<M_FVP>(ctx, a, &grid, s);
   }

@@ -350,4 +350,11 @@ int launch_fvp_jac(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s);
 int launch_jac_fill(mjrl_ctx* ctx, const float* params, int n, int m, int h1, int h2, float* cache, long long N,
                     cudaStream_t s);
 
+// tcgen05 / tensor-memory FVP (fvp_tc.cu), hidden 64 x 64, obs_dim <= 15, act_dim <= 8: shape test, floats of its
+// tile-ordered copy of the h1|h2 cache, the relayout pass from the fragment-ordered cache and the product
+bool tc_fits(const mjrl_ctx* ctx, int n, int m, int h1, int h2);
+long long tc_cache_floats(long long N);
+int launch_tc_fill(mjrl_ctx* ctx, const float* frag_cache, float* tc_cache, long long N, cudaStream_t s);
+int launch_fvp_tc(mjrl_ctx* ctx, Args& a, const float* tc_cache, int* grid_out, cudaStream_t s);
+
 }  // namespace pol

@@ -377,3 +377,70 @@ def test_consecutive_updates_refresh_the_jacobian_cache(case, monkeypatch):
     for mid, fin in finals.values():
         assert rel_l2(mid - g["params"], o1 - g["params"]) < TOL
         assert rel_l2(fin.astype(np.float64) - mid, o2.astype(np.float64) - o1) < 10 * TOL
+
+
+@pytest.mark.parametrize("n,m,N,mid", [(11, 3, 1000, False), (11, 3, 777, True), (12, 4, 96, True), (8, 2, 97, False),
+                                       (3, 1, 64, False), (15, 8, 4097, True), (14, 6, 2049, True), (11, 3, 40000, True)])
+def test_fvp_tensor_memory_variant(n, m, N, mid):
+    """cache_mode 4 (csrc/fvp_tc.cu, hidden 64 x 64): the product on tcgen05 tensor cores with accumulators and A
+    operands in tensor memory, reading h1|h2 from a tile-ordered copy of the cache (one relayout per solve).
+    Same product as the rows-in-registers kernels to fp32 rounding, deterministic, exact against the fp64
+    Gauss-Newton truth, several vectors per fill, in/out transforms, ragged N (partial last tile, several tiles
+    per CTA at N = 40000), act_dim up to 8."""
+    import torch
+    from mjrl_b200 import _lib
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.algos.engine import UpdateEngine
+    from oracle import mjrl_oracle as O
+    rng = np.random.default_rng(n * 100 + N)
+    pol = MLP(EnvSpec(n, m, 100, 1), hidden_sizes=(64, 64), seed=5)
+    flat = pol.get_param_values()
+    tr = None
+    if mid:
+        flat, tr = syn.mid_training_variant(flat, n, m, 77)
+        pol.model.set_transformations(**tr); pol.old_model.set_transformations(**tr)
+    else:
+        flat = flat + 0.3 * rng.standard_normal(flat.shape).astype(np.float32)
+    pol.set_param_values(flat.copy(), True, True)
+    eng = UpdateEngine(pol)
+    dev = eng.device
+    assert _lib.load().mjrl_policy_fvp_tc_ok(eng.ctx.h, eng.dv.desc_ref()) == 1
+    obs = torch.from_numpy((3 * rng.standard_normal((N, n))).astype(np.float32)).to(dev)
+    params = eng.dv.params("new")
+    tp = O.TruthPolicy(O.GaussianPolicy(n, m, (64, 64), flat.copy(), **(tr or {})))
+
+    def product(vec, mode):
+        out = torch.zeros(flat.shape[0], dtype=torch.float64, device=dev)
+        eng.cg_flags.zero_()
+        eng.fvp(params, obs, vec, out, cache_mode=mode)
+        return out.cpu().numpy()
+
+    vecs = [torch.from_numpy(rng.standard_normal(flat.shape[0]).astype(np.float32) * s).to(dev) for s in (0.1, 3.0, 1e-3)]
+    ref0 = product(vecs[0], 1)                    # fills h1|h2
+    assert eng._tc_prepare(params, obs)           # relayout (once: the second call is a no-op)
+    assert eng._tc_prepare(params, obs)
+    for k, vec in enumerate(vecs):
+        ref = ref0 if k == 0 else product(vec, 2)
+        a, b = product(vec, 4), product(vec, 4)
+        np.testing.assert_array_equal(a, b)
+        assert rel_l2(a, ref) < 3e-6, (k, rel_l2(a, ref))
+        if N <= 5000:
+            truth = N * tp.fvp(obs.cpu().numpy(), vec.cpu().numpy().astype(np.float64))
+            assert rel_l2(a, truth) < 1e-5, (k, rel_l2(a, truth))
+        # per block of the flat vector (a wrong bias or head block hides in the norm of W1)
+        F = [0, 64 * n, 64 * n + 64, 64 * n + 64 + 4096, 64 * n + 128 + 4096, 64 * n + 128 + 4096 + 64 * m,
+             64 * n + 128 + 4096 + 64 * m + m]
+        for lo, hi in zip(F[:-1], F[1:]):
+            assert rel_l2(a[lo:hi], ref[lo:hi]) < 1e-5, (k, lo, hi, rel_l2(a[lo:hi], ref[lo:hi]))
+        np.testing.assert_array_equal(a[-m:], ref[-m:])
+
+
+def test_fvp_tensor_memory_variant_not_offered_for_other_shapes():
+    from mjrl_b200 import _lib
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.algos.engine import UpdateEngine
+    for n, m, hidden in ((11, 3, (32, 32)), (17, 3, (64, 64)), (11, 3, (64, 32))):
+        eng = UpdateEngine(MLP(EnvSpec(n, m, 100, 1), hidden_sizes=hidden, seed=5))
+        assert _lib.load().mjrl_policy_fvp_tc_ok(eng.ctx.h, eng.dv.desc_ref()) == 0
