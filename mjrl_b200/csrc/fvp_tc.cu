@@ -27,8 +27,9 @@
 // atoms (SWIZZLE_128B_BASE32B), so the activation cache is stored in HBM in exactly that order and a tile
 // lands in shared memory by ONE linear bulk copy, ready to be a weight-gradient operand.
 //
-// Roles: warps 0-2 own the 96 rows (TMEM lanes 0-95: thread = timestep), warp 3 feeds the bulk copies and sums
-// the bias gradients, one elected lane of warp 4 issues every MMA.  All hand-offs are mbarriers.
+// Roles: warps 0-2 and 4-6 own the 96 rows (TMEM lanes 0-95; warps q and q + 4 share a lane quadrant and split the
+// 64 hidden columns of a row), warp 3 feeds the bulk copies and sums the bias gradients, one elected lane of
+// warp 7 issues every MMA.  All hand-offs are mbarriers.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -41,8 +42,8 @@ constexpr int ROWS = 96;            // timesteps per tile (smem bound: four 24 K
 constexpr int H = 64;               // hidden width
 constexpr int KX = 16;              // padded width of [x~, 1]
 constexpr int MJ = 8;               // largest action dimension
-constexpr int NTHREADS = 160;
-constexpr int ETHREADS = ROWS;      // epilogue threads (warps 0-2)
+constexpr int NTHREADS = 256;
+constexpr int ETHREADS = 2 * ROWS;  // epilogue threads (warps 0-2 and 4-6: two per row)
 constexpr int KSTEPS = ROWS / 8;    // weight-gradient MMAs per product and tile
 
 // ---- shared memory map (bytes) -------------------------------------------------------------------------
@@ -144,6 +145,14 @@ __device__ __forceinline__ void tld32(uint32_t taddr, uint32_t (&v)[32]) {
                "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
                : TC_R16(v, 0), TC_R16(v, 16) : "r"(taddr) : "memory");
 }
+// load + wait in ONE statement: the registers are only valid after tcgen05.wait::ld, and nothing else ties their
+// uses to a separate wait instruction
+__device__ __forceinline__ void tld32w(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+               "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];\n\t"
+               "tcgen05.wait::ld.sync.aligned;"
+               : TC_R16(v, 0), TC_R16(v, 16) : "r"(taddr));
+}
 __device__ __forceinline__ void tld16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                : TC_R16(v, 0) : "r"(taddr) : "memory");
@@ -151,11 +160,11 @@ __device__ __forceinline__ void tld16(uint32_t taddr, uint32_t (&v)[16]) {
 __device__ __forceinline__ void tst32(uint32_t taddr, const uint32_t (&v)[32]) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
                "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
-               :: "r"(taddr), TC_I16(v, 0), TC_I16(v, 16) : "memory");
+               :: "r"(taddr), TC_I16(v, 0), TC_I16(v, 16));
 }
 __device__ __forceinline__ void tst16(uint32_t taddr, const uint32_t (&v)[16]) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
-               :: "r"(taddr), TC_I16(v, 0) : "memory");
+               :: "r"(taddr), TC_I16(v, 0));
 }
 // lo plane of the compensated product: x - trunc_tf32(x) (exact)
 __device__ __forceinline__ float lo_of(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
@@ -185,28 +194,38 @@ struct TcArgs {
   const float* out_scale;
   float* partials;        // [grid][dstride]
   const int32_t* stop_flag;
+  long long* dbg;         // debug: per-phase cycle sums of CTA 0 (MJRL_B200_TC_PHASES=1), else null
   long long N;
   int n, m, dstride;
 };
 
+// Row access without bank conflicts: rows r and r + 4 share a swizzle pattern, so in a 128-bit access two of any
+// eight consecutive lanes would hit the same 16 bytes.  Lanes with bit 2 of the row set take the two halves of
+// every 32-byte atom in the opposite order (the values are put back in column order by selects).
 __device__ __forceinline__ void load_row32(const unsigned char* plane, int r, int blk, float (&v)[32]) {
+  const int sel = (r >> 2) & 1;
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    const float4* p = reinterpret_cast<const float4*>(plane + mn_atom(r, blk * 4 + q));
-    const float4 a = p[0], b = p[1];
-    v[8 * q + 0] = a.x; v[8 * q + 1] = a.y; v[8 * q + 2] = a.z; v[8 * q + 3] = a.w;
-    v[8 * q + 4] = b.x; v[8 * q + 5] = b.y; v[8 * q + 6] = b.z; v[8 * q + 7] = b.w;
+    const unsigned char* p = plane + mn_atom(r, blk * 4 + q);
+    const float4 a = *reinterpret_cast<const float4*>(p + 16 * sel);
+    const float4 b = *reinterpret_cast<const float4*>(p + 16 * (sel ^ 1));
+    v[8 * q + 0] = sel ? b.x : a.x; v[8 * q + 1] = sel ? b.y : a.y; v[8 * q + 2] = sel ? b.z : a.z; v[8 * q + 3] = sel ? b.w : a.w;
+    v[8 * q + 4] = sel ? a.x : b.x; v[8 * q + 5] = sel ? a.y : b.y; v[8 * q + 6] = sel ? a.z : b.z; v[8 * q + 7] = sel ? a.w : b.w;
   }
 }
 __device__ __forceinline__ void store_row32(unsigned char* plane, int r, int blk, const float (&v)[32]) {
+  const int sel = (r >> 2) & 1;
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    float4* p = reinterpret_cast<float4*>(plane + mn_atom(r, blk * 4 + q));
-    p[0] = make_float4(v[8 * q + 0], v[8 * q + 1], v[8 * q + 2], v[8 * q + 3]);
-    p[1] = make_float4(v[8 * q + 4], v[8 * q + 5], v[8 * q + 6], v[8 * q + 7]);
+    unsigned char* p = plane + mn_atom(r, blk * 4 + q);
+    const float4 lo4 = make_float4(v[8 * q + 0], v[8 * q + 1], v[8 * q + 2], v[8 * q + 3]);
+    const float4 hi4 = make_float4(v[8 * q + 4], v[8 * q + 5], v[8 * q + 6], v[8 * q + 7]);
+    *reinterpret_cast<float4*>(p + 16 * sel) = sel ? hi4 : lo4;
+    *reinterpret_cast<float4*>(p + 16 * (sel ^ 1)) = sel ? lo4 : hi4;
   }
 }
 
+template <int MJT>   // action dimension padded to 4 or 8: the head loops are branch-free (rows j >= m of W2, dW2 are zero)
 __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
   extern __shared__ unsigned char smraw[];
   __shared__ uint32_t tslot;
@@ -232,7 +251,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
     tma::mbar_init(&bar[B_W3], 32);
     tma::mbar_init_fence();
   }
-  if (warp == 4) {
+  if (warp == 7) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(smem_u32(&tslot)) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -284,43 +303,59 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
   unsigned char* pY = sm + OFF_Y; unsigned char* pZ = sm + OFF_Z;
   const float* tile_base = a.cache;     // + tile * 2 * PLANE / 4
 
-  if (warp < 3) {
-    // =========================== epilogue warps: thread = timestep row ===================================
-    const int r = tid;
-    const uint32_t tl = tb + ((uint32_t)(32 * warp) << 16);   // this warp's lane quadrant
+  if ((warp & 3) != 3) {
+    // ============ epilogue warps 0-2 and 4-6: thread = (timestep row, 32-column half of the hidden layer) =========
+    // Warps q and q + 4 share TMEM lane quadrant q (tcgen05.ld/st reach lanes 32 (warp % 4) ..): two warps per
+    // scheduler, each thread 32 of the 64 columns of its row.
+    const int q = warp & 3, half = warp >> 2, blk = half;
+    const int r = 32 * q + lane;
+    const uint32_t tl = tb + ((uint32_t)(32 * q) << 16);
+    const uint32_t pair_bar = 1 + q;
+    auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory"); };
+    long long ph_sum[14], tprev = 0;
+#pragma unroll
+    for (int i = 0; i < 14; ++i) ph_sum[i] = 0;
+    const bool stamp_on = a.dbg != nullptr && tid == 0 && blockIdx.x == 0;
+    auto stamp = [&](int i) { if (stamp_on) { const long long c = clock64(); ph_sum[i] += c - tprev; tprev = c; } };
+    if (stamp_on) tprev = clock64();
+    // raw observation row of the next tile, requested one tile ahead (half 1 owns x~)
+    float ox[KX];
+    auto prefetch_obs = [&](int tile) {
+      const long long t = (long long)tile * ROWS + r;
+#pragma unroll
+      for (int k = 0; k < KX; ++k) ox[k] = (half == 1 && tile < ntiles && t < a.N && k < n) ? __ldg(a.obs + t * n + k) : 0.f;
+    };
+    prefetch_obs(blockIdx.x);
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
       const long long t = (long long)tile * ROWS + r;
       const bool valid = t < a.N;
-      // x~ of this row: [ (obs - shift) / (scale + 1e-8), 1, 0.. ]
+      // ---- E0: x~ and h1 as tensor-memory A operands, h1 lo as a weight-gradient operand -----------------
       float xs[KX];
-      auto load_x = [&]() {
+      if (half == 1) {
+        uint32_t hi[16], lo[16];
 #pragma unroll
         for (int k = 0; k < KX; ++k) {
           float v = 0.f;
-          if (valid && k < n) v = (__ldg(a.obs + t * n + k) - vecs[Vec::ISHIFT + k]) * vecs[Vec::IRCP + k];
+          if (valid && k < n) v = (ox[k] - vecs[Vec::ISHIFT + k]) * vecs[Vec::IRCP + k];
           if (valid && k == n) v = 1.f;
           xs[k] = v;
+          hi[k] = __float_as_uint(v); lo[k] = __float_as_uint(lo_of(v));
         }
-      };
-      // ---- E0: x~ and h1 as tensor-memory A operands, h1 lo as a weight-gradient operand -----------------
-      load_x();
-      {
-        uint32_t hi[16], lo[16];
-#pragma unroll
-        for (int k = 0; k < KX; ++k) { hi[k] = __float_as_uint(xs[k]); lo[k] = __float_as_uint(lo_of(xs[k])); }
         tst16(tl + T_LO1, hi);
         tst16(tl + T_LO1 + 16, lo);
       }
+      stamp(0);
       tma::mbar_wait(&bar[B_H1], ph);
-#pragma unroll
-      for (int blk = 0; blk < 2; ++blk) {
+      stamp(1);
+      float s1[32];      // 1 - h1^2 of this thread's 32 columns: used by E1 and E3
+      {
         float h[32];
         uint32_t u32[32];
         load_row32(pX, r, blk, h);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) u32[i] = __float_as_uint(h[i]);
+        for (int i = 0; i < 32; ++i) { u32[i] = __float_as_uint(h[i]); s1[i] = fmaf(-h[i], h[i], 1.f); }
         tst32(tl + T_A1 + 32 * blk, u32);
 #pragma unroll
         for (int i = 0; i < 32; ++i) { h[i] = lo_of(h[i]); u32[i] = __float_as_uint(h[i]); }
@@ -331,20 +366,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
       fence_async();
       fence_before();
       mbar_arrive(&bar[B_E0]);
+      stamp(2);
 
       // ---- E1: dh1 = (1 - h1^2) dz1, in place over dz1 (hi) and next to it (lo) ---------------------------
-      tma::mbar_wait(&bar[B_M1], ph);
-      fence_after();
-#pragma unroll
-      for (int blk = 0; blk < 2; ++blk) {
-        float h[32];
+      {
         uint32_t d[32], l[32];
-        tld32(tl + T_D1 + 32 * blk, d);
-        load_row32(pX, r, blk, h);
-        wait_ld();
+        tma::mbar_wait(&bar[B_M1], ph);
+        fence_after();
+        stamp(3);
+        tld32w(tl + T_D1 + 32 * blk, d);
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          const float v = __uint_as_float(d[i]) * fmaf(-h[i], h[i], 1.f);
+          const float v = __uint_as_float(d[i]) * s1[i];
           d[i] = __float_as_uint(v); l[i] = __float_as_uint(lo_of(v));
         }
         tst32(tl + T_D1 + 32 * blk, d);
@@ -353,135 +386,154 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
       wait_st();
       fence_before();
       mbar_arrive(&bar[B_E1]);
+      stamp(4);
 
       // ---- E2: head on the CUDA cores: dh2, dmu, u, gz2 ---------------------------------------------------
-      tma::mbar_wait(&bar[B_H2], ph);
-      tma::mbar_wait(&bar[B_M2B], ph);
-      fence_after();
-      float dmu[MJ];
-#pragma unroll
-      for (int j = 0; j < MJ; ++j) dmu[j] = 0.f;
-#pragma unroll
-      for (int blk = 0; blk < 2; ++blk) {
-        float h[32];
+      float s2[32];      // 1 - h2^2 of this thread's 32 columns, kept for gz2
+      float u[MJT];
+      {
+        float h[32], dh[32];
         uint32_t d[32];
-        tld32(tl + T_D2 + 32 * blk, d);
+        tma::mbar_wait(&bar[B_H2], ph);
         load_row32(pY, r, blk, h);
-        wait_ld();
-        float dh[32];
+        tma::mbar_wait(&bar[B_M2B], ph);
+        fence_after();
+        stamp(5);
+        tld32w(tl + T_D2 + 32 * blk, d);
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          dh[i] = (__uint_as_float(d[i]) + vecs[Vec::DB1 + 32 * blk + i]) * fmaf(-h[i], h[i], 1.f);
+        for (int i4 = 0; i4 < 8; ++i4) {
+          const float4 b = *reinterpret_cast<const float4*>(vecs + Vec::DB1 + 32 * blk + 4 * i4);
+          s2[4 * i4 + 0] = fmaf(-h[4 * i4 + 0], h[4 * i4 + 0], 1.f); dh[4 * i4 + 0] = (__uint_as_float(d[4 * i4 + 0]) + b.x) * s2[4 * i4 + 0];
+          s2[4 * i4 + 1] = fmaf(-h[4 * i4 + 1], h[4 * i4 + 1], 1.f); dh[4 * i4 + 1] = (__uint_as_float(d[4 * i4 + 1]) + b.y) * s2[4 * i4 + 1];
+          s2[4 * i4 + 2] = fmaf(-h[4 * i4 + 2], h[4 * i4 + 2], 1.f); dh[4 * i4 + 2] = (__uint_as_float(d[4 * i4 + 2]) + b.z) * s2[4 * i4 + 2];
+          s2[4 * i4 + 3] = fmaf(-h[4 * i4 + 3], h[4 * i4 + 3], 1.f); dh[4 * i4 + 3] = (__uint_as_float(d[4 * i4 + 3]) + b.w) * s2[4 * i4 + 3];
+        }
+        // partial dmu_j over this thread's 32 columns: four independent chains per j
 #pragma unroll
-        for (int j = 0; j < MJ; ++j) {
-          if (j < m) {
+        for (int j = 0; j < MJT; ++j) {
+          float p = 0.f;
+          {
             const float4* w2 = reinterpret_cast<const float4*>(vecs + Vec::W2 + j * H + 32 * blk);
             const float4* v2 = reinterpret_cast<const float4*>(vecs + Vec::DW2 + j * H + 32 * blk);
-            float acc = dmu[j];
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
             for (int i4 = 0; i4 < 8; ++i4) {
               const float4 w = w2[i4], v = v2[i4];
-              acc = fmaf(h[4 * i4 + 0], v.x, acc); acc = fmaf(dh[4 * i4 + 0], w.x, acc);
-              acc = fmaf(h[4 * i4 + 1], v.y, acc); acc = fmaf(dh[4 * i4 + 1], w.y, acc);
-              acc = fmaf(h[4 * i4 + 2], v.z, acc); acc = fmaf(dh[4 * i4 + 2], w.z, acc);
-              acc = fmaf(h[4 * i4 + 3], v.w, acc); acc = fmaf(dh[4 * i4 + 3], w.w, acc);
+              a0 = fmaf(h[4 * i4 + 0], v.x, a0); a1 = fmaf(h[4 * i4 + 1], v.y, a1);
+              a2 = fmaf(h[4 * i4 + 2], v.z, a2); a3 = fmaf(h[4 * i4 + 3], v.w, a3);
+              a0 = fmaf(dh[4 * i4 + 0], w.x, a0); a1 = fmaf(dh[4 * i4 + 1], w.y, a1);
+              a2 = fmaf(dh[4 * i4 + 2], w.z, a2); a3 = fmaf(dh[4 * i4 + 3], w.w, a3);
             }
-            dmu[j] = acc;
+            p = (a0 + a1) + (a2 + a3);
           }
+          u[j] = p;
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) h[i] = lo_of(h[i]);
         store_row32(pZ, r, blk, h);                      // h2 lo: weight-gradient operand of gW2
       }
-      float u[MJ];
+      // the two halves of a row add their partial sums through the u array (half 1 -> half 0 -> half 1)
+      if (half == 1) {
 #pragma unroll
-      for (int j = 0; j < MJ; ++j) {
-        u[j] = (valid && j < m) ? vecs[Vec::FISHER + j] * (dmu[j] + vecs[Vec::DB2 + j]) : 0.f;
-        // u^T planes, K-major over the timestep: rows j (hi) and 8 + j (lo), column r
-        *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, j, r)) = u[j];
-        *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, 8 + j, r)) = lo_of(u[j]);
-        vecs[Vec::UARR + r * MJ + j] = u[j];
+        for (int j = 0; j < MJT; ++j) vecs[Vec::UARR + r * MJ + j] = u[j];
+      }
+      pair_sync();
+      if (half == 0) {
+#pragma unroll
+        for (int j = 0; j < MJT; ++j) {
+          const float dmu = u[j] + vecs[Vec::UARR + r * MJ + j];
+          u[j] = (valid && j < m) ? vecs[Vec::FISHER + j] * (dmu + vecs[Vec::DB2 + j]) : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < MJT; ++j) {
+          vecs[Vec::UARR + r * MJ + j] = u[j];
+          // u^T planes, K-major over the timestep: rows j (hi) and 8 + j (lo), column r
+          *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, j, r)) = u[j];
+        }
+      }
+      pair_sync();
+      if (half == 1) {
+#pragma unroll
+        for (int j = 0; j < MJT; ++j) {
+          u[j] = vecs[Vec::UARR + r * MJ + j];
+          *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, 8 + j, r)) = lo_of(u[j]);
+        }
       }
       fence_async();
       mbar_arrive(&bar[B_E2A]);
+      stamp(6);
       // gz2 = (u W2) (1 - h2^2): A operand of MMA-5 now, weight-gradient operand once gW2 has read h2
-      float gz[64];
-#pragma unroll
-      for (int blk = 0; blk < 2; ++blk) {
-        float h[32];
-        load_row32(pY, r, blk, h);
+      float gz[32];
+      {
         uint32_t hi[32], lo[32];
 #pragma unroll
         for (int i4 = 0; i4 < 8; ++i4) {
           float g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f;
 #pragma unroll
-          for (int j = 0; j < MJ; ++j) {
-            if (j < m) {
-              const float4 w = *reinterpret_cast<const float4*>(vecs + Vec::W2 + j * H + 32 * blk + 4 * i4);
-              g0 = fmaf(u[j], w.x, g0); g1 = fmaf(u[j], w.y, g1); g2 = fmaf(u[j], w.z, g2); g3 = fmaf(u[j], w.w, g3);
-            }
+          for (int j = 0; j < MJT; ++j) {
+            const float4 w = *reinterpret_cast<const float4*>(vecs + Vec::W2 + j * H + 32 * blk + 4 * i4);
+            g0 = fmaf(u[j], w.x, g0); g1 = fmaf(u[j], w.y, g1); g2 = fmaf(u[j], w.z, g2); g3 = fmaf(u[j], w.w, g3);
           }
-          gz[32 * blk + 4 * i4 + 0] = g0 * fmaf(-h[4 * i4 + 0], h[4 * i4 + 0], 1.f);
-          gz[32 * blk + 4 * i4 + 1] = g1 * fmaf(-h[4 * i4 + 1], h[4 * i4 + 1], 1.f);
-          gz[32 * blk + 4 * i4 + 2] = g2 * fmaf(-h[4 * i4 + 2], h[4 * i4 + 2], 1.f);
-          gz[32 * blk + 4 * i4 + 3] = g3 * fmaf(-h[4 * i4 + 3], h[4 * i4 + 3], 1.f);
+          gz[4 * i4 + 0] = g0 * s2[4 * i4 + 0]; gz[4 * i4 + 1] = g1 * s2[4 * i4 + 1];
+          gz[4 * i4 + 2] = g2 * s2[4 * i4 + 2]; gz[4 * i4 + 3] = g3 * s2[4 * i4 + 3];
         }
 #pragma unroll
-        for (int i = 0; i < 32; ++i) { hi[i] = __float_as_uint(gz[32 * blk + i]); lo[i] = __float_as_uint(lo_of(gz[32 * blk + i])); }
+        for (int i = 0; i < 32; ++i) { hi[i] = __float_as_uint(gz[i]); lo[i] = __float_as_uint(lo_of(gz[i])); }
         tst32(tl + T_A1 + 32 * blk, hi);
         tst32(tl + T_A1 + 64 + 32 * blk, lo);
       }
       wait_st();
       fence_before();
       mbar_arrive(&bar[B_E2B]);
+      stamp(7);
       tma::mbar_wait(&bar[B_GW2], ph);                  // gW2 has read h2 hi | lo: the planes become gz2
-#pragma unroll
-      for (int blk = 0; blk < 2; ++blk) {
+      stamp(8);
+      {
+        store_row32(pY, r, blk, gz);
         float v[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gz[32 * blk + i];
-        store_row32(pY, r, blk, v);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = lo_of(v[i]);
+        for (int i = 0; i < 32; ++i) v[i] = lo_of(gz[i]);
         store_row32(pZ, r, blk, v);
       }
       fence_async();
       mbar_arrive(&bar[B_E2C]);
+      stamp(9);
 
       // ---- E3: gz1 = gh1 (1 - h1^2); x~^T planes for gW0 -------------------------------------------------
-      tma::mbar_wait(&bar[B_M5], ph);
-      fence_after();
-#pragma unroll
-      for (int blk = 0; blk < 2; ++blk) {
-        float h[32];
+      {
         uint32_t d[32];
-        tld32(tl + T_D1 + 32 * blk, d);
-        load_row32(pX, r, blk, h);
-        wait_ld();
+        tma::mbar_wait(&bar[B_M5], ph);
+        fence_after();
+        stamp(10);
+        tld32w(tl + T_D1 + 32 * blk, d);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) gz[32 * blk + i] = valid ? __uint_as_float(d[i]) * fmaf(-h[i], h[i], 1.f) : 0.f;
+        for (int i = 0; i < 32; ++i) gz[i] = valid ? __uint_as_float(d[i]) * s1[i] : 0.f;
       }
       fence_before();
+      stamp(11);
       tma::mbar_wait(&bar[B_GW1], ph);                  // gW1 has read gz2 and h1 (and every earlier MMA is done)
       tma::mbar_wait(&bar[B_W3], ph);                   // warp 3 has summed gz2 for gb1
-#pragma unroll
-      for (int blk = 0; blk < 2; ++blk) {
+      stamp(12);
+      {
+        store_row32(pY, r, blk, gz);
         float v[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gz[32 * blk + i];
-        store_row32(pY, r, blk, v);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = lo_of(v[i]);
+        for (int i = 0; i < 32; ++i) v[i] = lo_of(gz[i]);
         store_row32(pZ, r, blk, v);
       }
+      if (half == 1) {
 #pragma unroll
-      for (int k = 0; k < KX; ++k) {
-        *reinterpret_cast<float*>(sm + OFF_XT + k128_off(32, k, r)) = xs[k];
-        *reinterpret_cast<float*>(sm + OFF_XT + k128_off(32, 16 + k, r)) = lo_of(xs[k]);
+        for (int k = 0; k < KX; ++k) {
+          *reinterpret_cast<float*>(sm + OFF_XT + k128_off(32, k, r)) = xs[k];
+          *reinterpret_cast<float*>(sm + OFF_XT + k128_off(32, 16 + k, r)) = lo_of(xs[k]);
+        }
       }
       fence_async();
       mbar_arrive(&bar[B_E3]);
+      prefetch_obs(tile + gridDim.x);
+      stamp(13);
     }
+    if (stamp_on) { for (int i = 0; i < 14; ++i) a.dbg[i] = ph_sum[i]; a.dbg[14] = it; }
   } else if (warp == 3) {
     // =========================== loader + bias gradients ==================================================
     double gb1a = 0.0, gb1b = 0.0, gb2 = 0.0;
@@ -496,22 +548,33 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
+      if (lane == 0 && tile + (int)gridDim.x < ntiles)   // the next tile's planes start their way to L2 now
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
+                     :: "l"(tile_base + (size_t)(tile + gridDim.x) * (2 * PLANE / 4)), "r"(2 * PLANE) : "memory");
       tma::mbar_wait(&bar[B_E2C], ph);       // gz2 (hi = the full fp32 value) is in Y, u in UARR
       {
-        const int c0 = 2 * lane, q = c0 >> 3;
-        double s0 = 0.0, s1 = 0.0;
-        float f0 = 0.f, f1 = 0.f;
-#pragma unroll 4
-        for (int rr = 0; rr < ROWS; ++rr) {
-          const float2 v = *reinterpret_cast<const float2*>(pY + mn_atom(rr, q) + (c0 & 7) * 4);
-          f0 += v.x; f1 += v.y;
-          if ((rr & 15) == 15) { s0 += (double)f0; s1 += (double)f1; f0 = 0.f; f1 = 0.f; }
+        const int c0 = 2 * lane, qa = c0 >> 3;
+        float2 acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int rr = 0; rr < ROWS; rr += 8) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float2 v = *reinterpret_cast<const float2*>(pY + mn_atom(rr + k, qa) + (c0 & 7) * 4);
+            acc[k].x += v.x; acc[k].y += v.y;
+          }
         }
-        gb1a += s0; gb1b += s1;
+        gb1a += (double)(((acc[0].x + acc[1].x) + (acc[2].x + acc[3].x)) + ((acc[4].x + acc[5].x) + (acc[6].x + acc[7].x)));
+        gb1b += (double)(((acc[0].y + acc[1].y) + (acc[2].y + acc[3].y)) + ((acc[4].y + acc[5].y) + (acc[6].y + acc[7].y)));
         if (lane < MJ) {
-          float f = 0.f;
-          for (int rr = 0; rr < ROWS; ++rr) f += vecs[Vec::UARR + rr * MJ + lane];
-          gb2 += (double)f;
+          float f[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+          for (int rr = 0; rr < ROWS; rr += 4) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) f[k] += vecs[Vec::UARR + (rr + k) * MJ + lane];
+          }
+          gb2 += (double)((f[0] + f[1]) + (f[2] + f[3]));
         }
       }
       mbar_arrive(&bar[B_W3]);
@@ -526,7 +589,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
     out[F.ob1 + 2 * lane + 1] = (float)gb1b;
     if (lane < m) out[F.ob2 + lane] = (float)gb2;
   } else {
-    // =========================== MMA issuer (one elected lane of warp 4) ==================================
+    // =========================== MMA issuer (one elected lane of warp 7) ==================================
     const uint32_t ID_FWD = idesc_tf32(128, 64, 0, 0);
     const uint32_t ID_GW1 = idesc_tf32(128, 128, 1, 1);
     const uint32_t ID_GW0 = idesc_tf32(128, 32, 1, 0);
@@ -681,7 +744,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
       }
     }
     __syncthreads();
-    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tb) : "memory");
+    if (warp == 7) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tb) : "memory");
   }
 }
 
@@ -749,7 +812,9 @@ int launch_fvp_tc(mjrl_ctx* ctx, Args& a, const float* tc_cache, int* grid_out, 
   if (!a.partials) return MJRL_E_STATE;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(tc::fvp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_ALLOC);
+    cudaError_t e = cudaFuncSetAttribute(tc::fvp_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_ALLOC);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(tc::fvp_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_ALLOC);
     if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute(fvp_tc): %s", cudaGetErrorString(e)); return (int)e; }
     attr = true;
   }
@@ -757,7 +822,24 @@ int launch_fvp_tc(mjrl_ctx* ctx, Args& a, const float* tc_cache, int* grid_out, 
   t.params = a.params; t.vec = a.vec; t.obs = a.obs; t.cache = tc_cache;
   t.in_shift = a.in_shift; t.in_scale = a.in_scale; t.out_scale = a.out_scale;
   t.partials = a.partials; t.stop_flag = a.stop_flag; t.N = a.N; t.n = a.n; t.m = a.m; t.dstride = a.dstride;
-  tc::fvp_tc_kernel<<<grid, tc::NTHREADS, tc::SMEM_ALLOC, s>>>(t);
+  static const bool phases = getenv("MJRL_B200_TC_PHASES") != nullptr;
+  static long long* dbg = nullptr;
+  if (phases && !dbg) cudaMalloc(&dbg, 16 * sizeof(long long));
+  t.dbg = phases ? dbg : nullptr;
+  if (a.m <= 4) tc::fvp_tc_kernel<4><<<grid, tc::NTHREADS, tc::SMEM_ALLOC, s>>>(t);
+  else tc::fvp_tc_kernel<8><<<grid, tc::NTHREADS, tc::SMEM_ALLOC, s>>>(t);
+  if (phases) {   // debug only: synchronous
+    long long h[16];
+    cudaStreamSynchronize(s);
+    cudaMemcpy(h, dbg, sizeof(h), cudaMemcpyDeviceToHost);
+    static const char* nm[14] = {"x~ + st", "wait h1", "E0 h1->tmem", "wait M1", "E1", "wait M2b (+h2)", "E2a dmu,u", "E2b gz2->tmem",
+                                 "wait gW2", "E2c planes", "wait M5", "E3 compute", "wait gW1,w3", "E3 planes"};
+    long long tot = 0;
+    for (int i = 0; i < 14; ++i) tot += h[i];
+    fprintf(stderr, "fvp_tc phases (CTA 0, %lld tiles, %lld cycles per tile):", h[14], h[14] ? tot / h[14] : 0);
+    for (int i = 0; i < 14; ++i) fprintf(stderr, " [%s %lld]", nm[i], h[14] ? h[i] / h[14] : 0);
+    fprintf(stderr, "\n");
+  }
   return mjrl_check_launch("fvp_tc_kernel");
 }
 
