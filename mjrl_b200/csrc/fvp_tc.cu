@@ -225,7 +225,7 @@ __device__ __forceinline__ void store_row32(unsigned char* plane, int r, int blk
   }
 }
 
-template <int MJT>   // action dimension padded to 4 or 8: the head loops are branch-free (rows j >= m of W2, dW2 are zero)
+template <int MJT>   // action dimension padded to 3, 4 or 8: the head loops are branch-free (rows j >= m of W2, dW2 are zero)
 __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
   extern __shared__ unsigned char smraw[];
   __shared__ uint32_t tslot;
@@ -392,10 +392,35 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
       float s2[32];      // 1 - h2^2 of this thread's 32 columns, kept for gz2
       float u[MJT];
       {
-        float h[32], dh[32];
+        float h[32];
         uint32_t d[32];
         tma::mbar_wait(&bar[B_H2], ph);
         load_row32(pY, r, blk, h);
+        float2 hv[16], dhv[16];      // packed pairs: the head runs on FFMA2 (two fp32 FMAs per instruction)
+        float2 acc[MJT][2];
+        // ... while MMA-2 is running: 1 - h2^2, the h2 dW2^T half of dmu, h2 lo
+#pragma unroll
+        for (int i4 = 0; i4 < 8; ++i4) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) s2[4 * i4 + e] = fmaf(-h[4 * i4 + e], h[4 * i4 + e], 1.f);
+          hv[2 * i4] = make_float2(h[4 * i4], h[4 * i4 + 1]);
+          hv[2 * i4 + 1] = make_float2(h[4 * i4 + 2], h[4 * i4 + 3]);
+        }
+#pragma unroll
+        for (int j = 0; j < MJT; ++j) {
+          const float4* v2 = reinterpret_cast<const float4*>(vecs + Vec::DW2 + j * H + 32 * blk);
+          float2 a0 = make_float2(0.f, 0.f), a1 = a0;
+#pragma unroll
+          for (int i4 = 0; i4 < 8; ++i4) {
+            const float4 v = v2[i4];
+            a0 = __ffma2_rn(hv[2 * i4], make_float2(v.x, v.y), a0);
+            a1 = __ffma2_rn(hv[2 * i4 + 1], make_float2(v.z, v.w), a1);
+          }
+          acc[j][0] = a0; acc[j][1] = a1;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) h[i] = lo_of(h[i]);
+        store_row32(pZ, r, blk, h);                      // h2 lo: weight-gradient operand of gW2
         tma::mbar_wait(&bar[B_M2B], ph);
         fence_after();
         stamp(5);
@@ -403,34 +428,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
 #pragma unroll
         for (int i4 = 0; i4 < 8; ++i4) {
           const float4 b = *reinterpret_cast<const float4*>(vecs + Vec::DB1 + 32 * blk + 4 * i4);
-          s2[4 * i4 + 0] = fmaf(-h[4 * i4 + 0], h[4 * i4 + 0], 1.f); dh[4 * i4 + 0] = (__uint_as_float(d[4 * i4 + 0]) + b.x) * s2[4 * i4 + 0];
-          s2[4 * i4 + 1] = fmaf(-h[4 * i4 + 1], h[4 * i4 + 1], 1.f); dh[4 * i4 + 1] = (__uint_as_float(d[4 * i4 + 1]) + b.y) * s2[4 * i4 + 1];
-          s2[4 * i4 + 2] = fmaf(-h[4 * i4 + 2], h[4 * i4 + 2], 1.f); dh[4 * i4 + 2] = (__uint_as_float(d[4 * i4 + 2]) + b.z) * s2[4 * i4 + 2];
-          s2[4 * i4 + 3] = fmaf(-h[4 * i4 + 3], h[4 * i4 + 3], 1.f); dh[4 * i4 + 3] = (__uint_as_float(d[4 * i4 + 3]) + b.w) * s2[4 * i4 + 3];
+          dhv[2 * i4] = __fmul2_rn(__fadd2_rn(make_float2(__uint_as_float(d[4 * i4]), __uint_as_float(d[4 * i4 + 1])), make_float2(b.x, b.y)),
+                                   make_float2(s2[4 * i4], s2[4 * i4 + 1]));
+          dhv[2 * i4 + 1] = __fmul2_rn(__fadd2_rn(make_float2(__uint_as_float(d[4 * i4 + 2]), __uint_as_float(d[4 * i4 + 3])), make_float2(b.z, b.w)),
+                                       make_float2(s2[4 * i4 + 2], s2[4 * i4 + 3]));
         }
-        // partial dmu_j over this thread's 32 columns: four independent chains per j
 #pragma unroll
         for (int j = 0; j < MJT; ++j) {
-          float p = 0.f;
-          {
-            const float4* w2 = reinterpret_cast<const float4*>(vecs + Vec::W2 + j * H + 32 * blk);
-            const float4* v2 = reinterpret_cast<const float4*>(vecs + Vec::DW2 + j * H + 32 * blk);
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+          const float4* w2 = reinterpret_cast<const float4*>(vecs + Vec::W2 + j * H + 32 * blk);
+          float2 a0 = acc[j][0], a1 = acc[j][1];
 #pragma unroll
-            for (int i4 = 0; i4 < 8; ++i4) {
-              const float4 w = w2[i4], v = v2[i4];
-              a0 = fmaf(h[4 * i4 + 0], v.x, a0); a1 = fmaf(h[4 * i4 + 1], v.y, a1);
-              a2 = fmaf(h[4 * i4 + 2], v.z, a2); a3 = fmaf(h[4 * i4 + 3], v.w, a3);
-              a0 = fmaf(dh[4 * i4 + 0], w.x, a0); a1 = fmaf(dh[4 * i4 + 1], w.y, a1);
-              a2 = fmaf(dh[4 * i4 + 2], w.z, a2); a3 = fmaf(dh[4 * i4 + 3], w.w, a3);
-            }
-            p = (a0 + a1) + (a2 + a3);
+          for (int i4 = 0; i4 < 8; ++i4) {
+            const float4 w = w2[i4];
+            a0 = __ffma2_rn(dhv[2 * i4], make_float2(w.x, w.y), a0);
+            a1 = __ffma2_rn(dhv[2 * i4 + 1], make_float2(w.z, w.w), a1);
           }
-          u[j] = p;
+          u[j] = (a0.x + a0.y) + (a1.x + a1.y);
         }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) h[i] = lo_of(h[i]);
-        store_row32(pZ, r, blk, h);                      // h2 lo: weight-gradient operand of gW2
       }
       // the two halves of a row add their partial sums through the u array (half 1 -> half 0 -> half 1)
       if (half == 1) {
@@ -468,14 +482,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
         uint32_t hi[32], lo[32];
 #pragma unroll
         for (int i4 = 0; i4 < 8; ++i4) {
-          float g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f;
+          float2 g0 = make_float2(0.f, 0.f), g1 = g0;
 #pragma unroll
           for (int j = 0; j < MJT; ++j) {
             const float4 w = *reinterpret_cast<const float4*>(vecs + Vec::W2 + j * H + 32 * blk + 4 * i4);
-            g0 = fmaf(u[j], w.x, g0); g1 = fmaf(u[j], w.y, g1); g2 = fmaf(u[j], w.z, g2); g3 = fmaf(u[j], w.w, g3);
+            const float2 uu = make_float2(u[j], u[j]);
+            g0 = __ffma2_rn(uu, make_float2(w.x, w.y), g0);
+            g1 = __ffma2_rn(uu, make_float2(w.z, w.w), g1);
           }
-          gz[4 * i4 + 0] = g0 * s2[4 * i4 + 0]; gz[4 * i4 + 1] = g1 * s2[4 * i4 + 1];
-          gz[4 * i4 + 2] = g2 * s2[4 * i4 + 2]; gz[4 * i4 + 3] = g3 * s2[4 * i4 + 3];
+          gz[4 * i4 + 0] = g0.x * s2[4 * i4 + 0]; gz[4 * i4 + 1] = g0.y * s2[4 * i4 + 1];
+          gz[4 * i4 + 2] = g1.x * s2[4 * i4 + 2]; gz[4 * i4 + 3] = g1.y * s2[4 * i4 + 3];
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) { hi[i] = __float_as_uint(gz[i]); lo[i] = __float_as_uint(lo_of(gz[i])); }
@@ -510,24 +526,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
         for (int i = 0; i < 32; ++i) gz[i] = valid ? __uint_as_float(d[i]) * s1[i] : 0.f;
       }
       fence_before();
-      stamp(11);
-      tma::mbar_wait(&bar[B_GW1], ph);                  // gW1 has read gz2 and h1 (and every earlier MMA is done)
-      tma::mbar_wait(&bar[B_W3], ph);                   // warp 3 has summed gz2 for gb1
-      stamp(12);
-      {
-        store_row32(pY, r, blk, gz);
-        float v[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = lo_of(gz[i]);
-        store_row32(pZ, r, blk, v);
-      }
-      if (half == 1) {
+      if (half == 1) {     // the x~^T planes were last read by gW0 of the previous tile, long complete
 #pragma unroll
         for (int k = 0; k < KX; ++k) {
           *reinterpret_cast<float*>(sm + OFF_XT + k128_off(32, k, r)) = xs[k];
           *reinterpret_cast<float*>(sm + OFF_XT + k128_off(32, 16 + k, r)) = lo_of(xs[k]);
         }
       }
+      float gl[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) gl[i] = lo_of(gz[i]);
+      stamp(11);
+      tma::mbar_wait(&bar[B_GW1], ph);                  // gW1 has read gz2 and h1 (and every earlier MMA is done)
+      tma::mbar_wait(&bar[B_W3], ph);                   // warp 3 has summed gz2 for gb1
+      stamp(12);
+      store_row32(pY, r, blk, gz);
+      store_row32(pZ, r, blk, gl);
       fence_async();
       mbar_arrive(&bar[B_E3]);
       prefetch_obs(tile + gridDim.x);
@@ -579,7 +593,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
       }
       mbar_arrive(&bar[B_W3]);
       const int next = tile + gridDim.x;
-      tma::mbar_wait(&bar[B_E3], ph);        // gW1 is done and every row thread has read its h1 row for the last time
+      tma::mbar_wait(&bar[B_GW1], ph);       // gW1 has read h1 hi | lo; the row threads read X only in E0 (s1 stays in registers)
       if (next < ntiles) load_plane(next, 0);
       tma::mbar_wait(&bar[B_GW0], ph);       // gz1 planes (Y, Z) are free
       if (next < ntiles) load_plane(next, 1);
@@ -812,7 +826,9 @@ int launch_fvp_tc(mjrl_ctx* ctx, Args& a, const float* tc_cache, int* grid_out, 
   if (!a.partials) return MJRL_E_STATE;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(tc::fvp_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_ALLOC);
+    cudaError_t e = cudaFuncSetAttribute(tc::fvp_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_ALLOC);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(tc::fvp_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_ALLOC);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(tc::fvp_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_ALLOC);
     if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute(fvp_tc): %s", cudaGetErrorString(e)); return (int)e; }
@@ -826,7 +842,8 @@ int launch_fvp_tc(mjrl_ctx* ctx, Args& a, const float* tc_cache, int* grid_out, 
   static long long* dbg = nullptr;
   if (phases && !dbg) cudaMalloc(&dbg, 16 * sizeof(long long));
   t.dbg = phases ? dbg : nullptr;
-  if (a.m <= 4) tc::fvp_tc_kernel<4><<<grid, tc::NTHREADS, tc::SMEM_ALLOC, s>>>(t);
+  if (a.m <= 3) tc::fvp_tc_kernel<3><<<grid, tc::NTHREADS, tc::SMEM_ALLOC, s>>>(t);
+  else if (a.m <= 4) tc::fvp_tc_kernel<4><<<grid, tc::NTHREADS, tc::SMEM_ALLOC, s>>>(t);
   else tc::fvp_tc_kernel<8><<<grid, tc::NTHREADS, tc::SMEM_ALLOC, s>>>(t);
   if (phases) {   // debug only: synchronous
     long long h[16];
