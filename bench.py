@@ -12,8 +12,9 @@ same parameters before every step so each step does identical work.
 Prints ONE JSON line (rank 0).  `value` = device-resident throughput (CUDA events, L2 flushed
 between steps, max over ranks); `e2e` = the same update through the public API from pinned
 HOST fp64 buffers, H2D and the D2H of the results inside the timed region; `roofline`
-describes the dominant kernel (the FVP pass); `cpu_baseline` is the oracle port timed on this
-box's host cores on a bounded 100k-timestep sample.
+describes the dominant kernel (the FVP pass); `cpu_baseline` is the reference's own update
+(staged in oracle/_ref; the oracle port when nothing is staged) timed on this box's host cores on a
+bounded 100k-timestep sample; `parity` is the CUDA path against it on that same sample.
 """
 import argparse
 import json
@@ -58,48 +59,80 @@ def peaks():
 
 
 # ------------------------------------------------------------------------------------------
-# CPU baseline / reference arm: the oracle port (the reference is pure Python and cannot travel
-# to the GPU box; oracle/mjrl_oracle.py is pinned bit-exact to it by tests/golden)
+# CPU baseline / reference arm.  `kind: "reference"`: the reference's OWN modules (process_samples,
+# NPG.train_from_paths, LinearBaseline.fit) staged in oracle/_ref by oracle/build_ref.py (the package is pure
+# Python; the staged copy travels to the GPU box, /root/reference does not).  `kind: "port"`: the oracle
+# restatement (oracle/mjrl_oracle.py, pinned bit-exact to the reference by tests/golden), used when nothing is
+# staged.
 # ------------------------------------------------------------------------------------------
 def cpu_update_setup(shape, N, seed):
     import torch
     from mjrl_b200.utils import synthetic as syn
     from oracle import mjrl_oracle as O
+    from oracle import ref_runner as RR
     n, m, hidden, horizon, _ = syn.SHAPES[shape]
     torch.set_num_threads(os.cpu_count())
     flat = O.init_policy_params(n, m, hidden, seed=123)
     b0 = syn.make_flat_batch(N, n, m, horizon, seed, flat, hidden)
     b1 = syn.make_flat_batch(N, n, m, horizon, seed + 1, flat, hidden)
-    base = O.LinearBaseline()
-    p0 = syn.flat_to_paths(b0)
-    O.compute_returns(p0, GAMMA)
+    kind = "reference" if RR.available() else "port"
+    if kind == "reference":
+        R = RR.load()
+        base = R.lb.LinearBaseline(R.EnvSpec(n, m, horizon, 1))
+        p0 = syn.flat_to_paths(b0)
+        R.ps.compute_returns(p0, GAMMA)
+    else:
+        base = O.LinearBaseline()
+        p0 = syn.flat_to_paths(b0)
+        O.compute_returns(p0, GAMMA)
     base.fit(p0)                                   # steady state: predict() is non-trivial (F8)
-    return O, syn, (n, m, hidden), flat, b1, base
+    return dict(kind=kind, O=O, RR=RR, syn=syn, dims=(n, m, hidden, horizon), flat=flat, b0=b0, b1=b1, base=base)
 
 
-def cpu_update_once(O, syn, dims, flat, b1, base):
+def cpu_update_once(c, keep=False):
     import copy
-    n, m, hidden = dims
-    pol = O.GaussianPolicy(n, m, hidden, flat)
-    paths = syn.flat_to_paths(b1)
-    bl = copy.deepcopy(base)
-    t = time.perf_counter()
-    O.full_npg_iteration(pol, bl, paths, GAMMA, LAM, normalized_step_size=STEP,
-                         cg_iters=CG_ITERS, damping=DAMPING)
-    return time.perf_counter() - t
+    n, m, hidden, horizon = c["dims"]
+    paths = c["syn"].flat_to_paths(c["b1"])
+    bl = copy.deepcopy(c["base"])
+    if c["kind"] == "reference":
+        pol, _, agent = c["RR"].make_agent(n, m, hidden, horizon, c["flat"], step=STEP, cg_iters=CG_ITERS, damping=DAMPING)
+        agent.baseline = bl
+        t = time.perf_counter()
+        c["RR"].full_iteration(agent, paths, GAMMA, LAM)
+        dt = time.perf_counter() - t
+        if keep:
+            c["last"] = dict(new_params=pol.get_param_values(), coeffs=np.asarray(bl._coeffs), paths=paths)
+    else:
+        O = c["O"]
+        pol = O.GaussianPolicy(n, m, hidden, c["flat"])
+        t = time.perf_counter()
+        out = O.full_npg_iteration(pol, bl, paths, GAMMA, LAM, normalized_step_size=STEP,
+                                   cg_iters=CG_ITERS, damping=DAMPING)
+        dt = time.perf_counter() - t
+        if keep:
+            c["last"] = dict(new_params=out["new_params"], coeffs=np.asarray(bl._coeffs), paths=paths)
+    return dt
+
+
+def _cpu_desc(kind):
+    return ("the reference's own modules (mjrl.utils.process_samples, mjrl.algos.npg_cg.NPG.train_from_paths, "
+            "mjrl.baselines.linear_baseline.LinearBaseline.fit; numpy + CPU torch autograd, python-loop scans are "
+            "single-threaded)" if kind == "reference" else
+            "oracle port of the reference update (numpy + CPU torch autograd, python-loop scans are single-threaded)")
 
 
 def cpu_baseline(shape, reps=5):
     import torch
-    ctx = cpu_update_setup(shape, CPU_SAMPLE_N, 900)
-    cpu_update_once(*ctx)                          # warm-up (first torch call is slow)
-    ts = sorted(cpu_update_once(*ctx) for _ in range(reps))
+    c = cpu_update_setup(shape, CPU_SAMPLE_N, 900)
+    cpu_update_once(c)                             # warm-up (first torch call is slow)
+    ts = sorted(cpu_update_once(c, keep=True) for _ in range(reps))
     med = ts[len(ts) // 2]
-    return {"value": CPU_SAMPLE_N / med, "unit": "timesteps/s", "cores": torch.get_num_threads(),
-            "kind": "port",
-            "sample": "oracle port of the reference update (numpy + CPU torch autograd, python-loop "
-                      "scans are single-threaded), %d timesteps of %s, median of %d after 1 warm-up"
-                      % (CPU_SAMPLE_N, shape, reps)}
+    cb = {"value": CPU_SAMPLE_N / med, "unit": "timesteps/s", "cores": torch.get_num_threads(),
+          "kind": c["kind"],
+          "sample": "%s, %d timesteps of %s, median of %d after 1 warm-up"
+                    % (_cpu_desc(c["kind"]), CPU_SAMPLE_N, shape, reps),
+          "versions": {"numpy": np.__version__, "torch": torch.__version__}}
+    return cb, c
 
 
 def run_reference(args):
@@ -107,24 +140,165 @@ def run_reference(args):
     if rank != 0:
         return
     import torch
-    ctx = cpu_update_setup(args.workload, CPU_SAMPLE_N, 900)
+    c = cpu_update_setup(args.workload, CPU_SAMPLE_N, 900)
     for _ in range(max(1, args.warmup)):
-        cpu_update_once(*ctx)
-    ts = [cpu_update_once(*ctx) for _ in range(args.steps)]
+        cpu_update_once(c)
+    ts = [cpu_update_once(c) for _ in range(args.steps)]
     tot = sum(ts)
     val = CPU_SAMPLE_N * args.steps / tot
-    cb = {"value": val, "unit": "timesteps/s", "cores": torch.get_num_threads(), "kind": "port",
-          "sample": "%d-timestep sample of %s per step" % (CPU_SAMPLE_N, args.workload)}
+    cb = {"value": val, "unit": "timesteps/s", "cores": torch.get_num_threads(), "kind": c["kind"],
+          "sample": "%d-timestep sample of %s per step: %s" % (CPU_SAMPLE_N, args.workload, _cpu_desc(c["kind"]))}
     print(json.dumps({
         "impl": "reference", "metric": "NPG update timesteps/sec", "value": val,
         "unit": "timesteps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "%s NPG + MLP(64,64) + LinearBaseline, CPU oracle port on a bounded "
-                               "sample of %d timesteps/step" % (args.workload, CPU_SAMPLE_N)},
+        "config": {"workload": "%s NPG + MLP(64,64) + LinearBaseline, %s on a bounded "
+                               "sample of %d timesteps/step" % (args.workload,
+                                                                "the reference's own CPU update" if c["kind"] == "reference"
+                                                                else "CPU oracle port", CPU_SAMPLE_N)},
         "cpu_baseline": cb,
         "e2e": {"value": val, "unit": "timesteps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
+
+
+def parity_at_sample_size(c, device):
+    """The CUDA path on the SAME 100k-timestep batch the CPU arm just pushed through the reference: parity at a
+    size where every CTA of the policy kernels accumulates over thousands of timesteps (the unit tests run
+    N <= 40k).  Gates (north_star): returns / advantages / baseline predictions 1e-6, gradient / FVP / step 1e-4;
+    the 10-iteration step is compared through the fp64 truth (the reference's own fp32 CG is only
+    reproducible to ~1e-3 on this shape, so both are measured against the all-fp64 solve)."""
+    import torch
+    from mjrl_b200 import _lib
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.policies.gaussian_linear import LinearPolicy
+    from mjrl_b200.baselines.linear_baseline import LinearBaseline
+    from mjrl_b200.algos.npg_cg import NPG
+    O, syn = c["O"], c["syn"]
+    n, m, hidden, horizon = c["dims"]
+    flat = c["flat"]
+    rel = lambda a, b: float(np.linalg.norm(np.asarray(a, np.float64).ravel() - np.asarray(b, np.float64).ravel()) /
+                             max(np.linalg.norm(np.asarray(b, np.float64).ravel()), 1e-300))
+    spec = EnvSpec(n, m, horizon, 1)
+    pol = MLP(spec, hidden_sizes=hidden, seed=123) if hidden else LinearPolicy(spec, seed=123)
+    pol.set_param_values(flat.copy(), True, True)
+    base = LinearBaseline(spec)
+    p0 = syn.flat_to_paths(c["b0"])
+    from mjrl_b200.utils import process_samples as ps
+    ps.compute_returns(p0, GAMMA)
+    base.fit(p0)
+    agent = NPG(None, pol, base, normalized_step_size=STEP, FIM_invert_args={"iters": CG_ITERS, "damping": DAMPING})
+    paths = syn.flat_to_paths(c["b1"])
+    # the reference's own call sequence (batch_reinforce.py:86-101) through the drop-in modules: the path dicts
+    # receive returns / baseline / advantages like the reference's
+    ps.compute_returns(paths, GAMMA)
+    ps.compute_advantages(paths, base, GAMMA, LAM)
+    agent.train_from_paths(paths)
+    base.fit(paths)
+    ref = c["last"]
+    cat = lambda ps_, k: np.concatenate([p[k] for p in ps_])
+    out = {"timesteps": int(c["b1"]["observations"].shape[0]), "against": c["kind"],
+           "returns_rel": rel(cat(paths, "returns"), cat(ref["paths"], "returns")),
+           "baseline_pred_rel": rel(cat(paths, "baseline"), cat(ref["paths"], "baseline")),
+           "advantages_rel": rel(cat(paths, "advantages"), cat(ref["paths"], "advantages")),
+           "baseline_coeffs_pred_rel": None, "kl_abs": None}
+    obs, act = c["b1"]["observations"], c["b1"]["actions"]
+    adv = cat(ref["paths"], "advantages")
+    adv_w = (adv - np.mean(adv)) / (np.std(adv) + 1e-6)
+    # gradient and Fisher-vector product of the starting policy, CUDA path vs oracle autograd (fp32) and fp64 truth
+    opol = O.GaussianPolicy(n, m, hidden, flat)
+    g_ref = O.flat_vpg(opol, obs, act, adv_w)
+    pol2 = MLP(spec, hidden_sizes=hidden, seed=123) if hidden else LinearPolicy(spec, seed=123)
+    pol2.set_param_values(flat.copy(), True, True)
+    ag2 = NPG(None, pol2, LinearBaseline(spec), normalized_step_size=STEP,
+              FIM_invert_args={"iters": CG_ITERS, "damping": DAMPING})
+    out["grad_rel"] = rel(ag2.flat_vpg(obs, act, adv_w), g_ref)
+    hv_ref = O.hvp(opol, obs, act, g_ref, DAMPING)
+    out["fvp_rel"] = rel(ag2.HVP(obs, act, g_ref, DAMPING), hv_ref)
+    # the product variant the CG solve runs at this size (tensor-memory kernel when the shape has it)
+    eng = ag2._engine()
+    d_obs = torch.from_numpy(np.ascontiguousarray(obs, dtype=np.float32)).to(eng.device)
+    params = eng.dv.params("new")
+    v32 = torch.from_numpy(g_ref.astype(np.float32)).to(eng.device)
+    o64 = torch.empty(eng.dv.d, dtype=torch.float64, device=eng.device)
+    eng.cg_flags.zero_()
+    mode = 0
+    if hidden and eng._fvp_cache(d_obs.shape[0]) is not None:
+        eng.fvp(params, d_obs, v32, o64, cache_mode=1)
+        eng._cache_key = eng._hold(params, d_obs)
+        mode = eng._cached_mode(params, d_obs)
+    eng.fvp(params, d_obs, v32, o64, cache_mode=mode)
+    hv_dev = (o64 / d_obs.shape[0]).float().cpu().numpy() + np.float32(DAMPING) * g_ref
+    out["fvp_rel_cg_kernel"] = rel(hv_dev, hv_ref)
+    out["fvp_cg_kernel_mode"] = {0: "uncached", 2: "activation cache (rows kernel)", 3: "Jacobian rows (rows kernel)",
+                                 4: "tensor memory (tcgen05)"}.get(mode, str(mode))
+    if hidden:
+        tp = O.TruthPolicy(opol)
+        gt = tp.vpg(obs, act, adv_w)
+        out["grad_rel_vs_truth"] = rel(ag2.flat_vpg(obs, act, adv_w), gt)
+        out["fvp_rel_vs_truth"] = rel(hv_dev, tp.fvp(obs, g_ref.astype(np.float64), DAMPING))
+        xs = O.truth_cg(tp, obs, gt, cg_iters=CG_ITERS, damping=DAMPING)
+        step_true = np.sqrt(abs(STEP / (gt @ xs + 1e-20))) * xs
+        out["step_rel_vs_truth"] = rel(pol.get_param_values().astype(np.float64) - flat, step_true)
+        out["reference_step_rel_vs_truth"] = rel(ref["new_params"].astype(np.float64) - flat, step_true)
+    out["step_rel_vs_reference"] = rel(pol.get_param_values().astype(np.float64) - flat,
+                                       ref["new_params"].astype(np.float64) - flat)
+    # baseline coefficients through their predictions (cond(A) up to 1e9: compare X c, not c)
+    X = np.concatenate([O.linear_features(p) for p in ref["paths"]])
+    out["baseline_coeffs_pred_rel"] = rel(X @ np.asarray(base._coeffs), X @ ref["coeffs"])
+    out["kl_abs_vs_target"] = abs(agent.last_update["kl_dist"] - 0.5 * STEP)
+    out["kl_cuda"] = agent.last_update["kl_dist"]
+    out.pop("kl_abs")
+    gates = {"returns_rel": 1e-6, "baseline_pred_rel": 1e-6, "advantages_rel": 1e-6, "grad_rel": 1e-4,
+             "fvp_rel": 1e-4, "fvp_rel_cg_kernel": 1e-4, "baseline_coeffs_pred_rel": 1e-6}
+    out["gates"] = gates
+    ok = all(out[k] <= v for k, v in gates.items())
+    if hidden:   # H1 protocol for the 10-iteration step
+        ok = ok and out["step_rel_vs_truth"] <= max(1e-4, 1.05 * out["reference_step_rel_vs_truth"]) + 1e-6
+    out["pass"] = bool(ok)
+    return out
+
+
+def rank_invariance(dev, world, rank):
+    """Multi-GPU correctness on the bench line itself (the 1-GPU test box skips the torchrun tests): the same small
+    batch updated (a) sharded by whole paths over all ranks and (b) on one GPU with no exchange; every rank computes
+    (b) itself.  Relative difference of the NPG step and of the refit baseline's predictions."""
+    import torch.distributed as td
+    from mjrl_b200.sharding import shard_paths
+    from mjrl_b200.utils import synthetic as syn
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.baselines.linear_baseline import LinearBaseline
+    from mjrl_b200.algos.npg_cg import NPG
+    from mjrl_b200.algos.engine import Dist
+    from mjrl_b200.batch import drop_cache
+    from oracle import mjrl_oracle as O
+    n, m, hidden, horizon = 11, 3, (64, 64), 250
+    Nt = 40000 * world       # >= 32768 per rank: the sharded run uses the same product kernel as the headline
+    spec = EnvSpec(n, m, horizon, 1)
+    flat = MLP(spec, hidden_sizes=hidden, seed=123).get_param_values()
+    hb = syn.make_flat_batch(Nt, n, m, horizon, 7000, flat, hidden)
+    res = {}
+    for mode in ("sharded", "single"):
+        pol = MLP(spec, hidden_sizes=hidden, seed=123)
+        base = LinearBaseline(spec)
+        ag = NPG(None, pol, base, normalized_step_size=STEP, FIM_invert_args={"iters": CG_ITERS, "damping": DAMPING})
+        paths = syn.flat_to_paths(hb)
+        if mode == "sharded":
+            ag.dist = Dist()
+            paths = shard_paths(paths, rank, world)
+        else:
+            ag.dist = Dist.__new__(Dist); ag.dist.td = None; ag.dist.world = 1; ag.dist.rank = 0
+            ag.dist.calls = 0; ag.dist.group = None; ag.dist.peer = None; ag.dist.peer_note = "single"
+        drop_cache()
+        ag.train_step(len(paths), gamma=GAMMA, gae_lambda=LAM, paths=paths)
+        res[mode] = (pol.get_param_values().astype(np.float64) - flat, np.asarray(base._coeffs, dtype=np.float64))
+    X = np.concatenate([O.linear_features(p) for p in syn.flat_to_paths(hb)[:50]])
+    rel = lambda a, b: float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+    return {"timesteps": Nt, "step_rel": rel(res["sharded"][0], res["single"][0]),
+            "coef_rel": rel(X @ res["sharded"][1], X @ res["single"][1]),
+            "note": "sharded over %d ranks vs the same batch on one GPU without any exchange (10 CG iterations)" % world}
 
 
 # ------------------------------------------------------------------------------------------
@@ -296,6 +470,7 @@ def run_b200(args):
     for _ in range(2):
         reset(); step_e2e()
     barrier()
+    d2h0 = _lib.D2H_BYTES[0]
     t0 = time.perf_counter()
     for k in range(args.steps):
         reset()
@@ -307,7 +482,7 @@ def run_b200(args):
         td.all_reduce(te, op=td.ReduceOp.MAX)
     e2e_s = float(te.item()) / args.steps
     d = int(pol.d)
-    d2h = 4 * d + 8 * (2 + 1 + 4) + 8 * 4 + (4 * 18689 if use_mlp else 8 * (n + 4))
+    d2h = (_lib.D2H_BYTES[0] - d2h0) // args.steps      # counted where the update reads results back (_lib.to_host)
     e2e = {"value": N * world / e2e_s, "unit": "timesteps/s", "ms_per_step": 1e3 * e2e_s,
            "h2d_bytes_per_step": int(b.h2d_bytes), "d2h_bytes_per_step": int(d2h)}
 
@@ -378,7 +553,20 @@ def run_b200(args):
             a.record(); eng._jac_prepare(params, resident.obs); bq.record()
         torch.cuda.synchronize()
         jac_fill_ms = sorted(a.elapsed_time(bq) for a, bq in fe)[2]
-    fvp_ms = time_fvp(3) if jac else fvp_rows_ms
+    fvp_jac_ms = time_fvp(3) if jac else None
+    # hidden 64 x 64: tensor-memory product (csrc/fvp_tc.cu, tcgen05) = what the CG solve runs when the shape has it
+    tc = bool(cached and eng._tc_prepare(params, resident.obs))
+    tc_fill_ms = None
+    if tc:
+        fe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(5)]
+        for a, bq in fe:
+            eng._tc_key = None
+            a.record(); eng._tc_prepare(params, resident.obs); bq.record()
+        torch.cuda.synchronize()
+        tc_fill_ms = sorted(a.elapsed_time(bq) for a, bq in fe)[2]
+    fvp_tc_ms = time_fvp(4) if tc else None
+    fvp_ms = fvp_tc_ms if tc else (fvp_jac_ms if jac else fvp_rows_ms)
+    jac_used = jac and not tc
     hbm_peak, peak_src, sm_max = peaks()
     U = (n * hidden[0] + hidden[0] * hidden[1] + hidden[1] * m) if hidden else n * m
     # MACs per timestep: forward U, tangent U + (h1 h2 + h2 m), backward data h1 h2 + h2 m, weight grads U
@@ -387,9 +575,9 @@ def run_b200(args):
     # fill_flop); the kernels issue fewer: the activation cache reads the forward pass back (- 2U), the
     # Jacobian cache also drops the tangent propagation and the backward data products (4U left)
     fvp_flop = fill_flop
-    issued_flop = (4.0 * U if jac else fill_flop - 2.0 * U) if cached else fill_flop
+    issued_flop = (4.0 * U if jac_used else fill_flop - 2.0 * U) if cached else fill_flop
     hp = (32 if max(hidden) <= 32 else 64) if hidden else 0
-    fvp_bytes = 4.0 * n + (4.0 * 2 * hp if cached else 0.0) + (4.0 * m * hp if jac else 0.0)   # obs + caches
+    fvp_bytes = 4.0 * n + (4.0 * 2 * hp if cached else 0.0) + (4.0 * m * hp if jac_used else 0.0)   # obs + caches
     ach = N * fvp_bytes / (fvp_ms * 1e-3) / 1e9
     fma_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12          # nominal fp32 FMA peak at max clock
     bf16_peak = None
@@ -398,16 +586,29 @@ def run_b200(args):
         bf16_peak = float(json.load(open(pk)).get("bf16_tflops", 0.0)) or None
     tensor_peak, tensor_src = (bf16_peak, peak_src) if bf16_peak else (1590.0, "fallback (B200_PROFILING.md)")
     traffic = None
-    tp = os.path.join(ROOT, "profiles", "r01_fvp_traffic.json")
+    tp = os.path.join(ROOT, "profiles", "r02_fvp_traffic.json" if tc else "r01_fvp_traffic.json")
     if os.path.exists(tp) and args.workload == "C3-hopper":
         tj = json.load(open(tp))
-        key = ("dram_bytes_per_timestep_jac" if jac else "dram_bytes_per_timestep_cached") if cached \
+        key = "dram_bytes_per_timestep_tc" if tc else \
+            ("dram_bytes_per_timestep_jac" if jac else "dram_bytes_per_timestep_cached") if cached \
             else "dram_bytes_per_timestep"
         if key in tj:
             traffic = float(tj[key]) * N
+    # measured non-bf16 peaks of this pool's B200 (profiles/peaks_measured.json: probes under profiles/probes)
+    pm = {}
+    pmf = os.path.join(ROOT, "profiles", "peaks_measured.json")
+    if os.path.exists(pmf):
+        pm = json.load(open(pmf))
+    fma_peak_meas = pm.get("fp32_fma_tflops")
+    tf32_tc_peak = pm.get("tf32_tcgen05_tflops")
     ach_tf = N * fvp_flop / (fvp_ms * 1e-3) / 1e12
+    tf32_issued = 3.0 * N * issued_flop / (fvp_ms * 1e-3) / 1e12
     roofline = {
-        "kernel": ("fvp_jac_kernel (analytic Fisher-vector product on cached activations and output-Jacobian "
+        "kernel": ("fvp_tc_kernel (analytic Fisher-vector product on tcgen05 tensor cores: tangent + backward pass per "
+                   "96-timestep tile, A operands and accumulators in tensor memory, kind::tf32 with hi/lo error "
+                   "compensation; %d of the %d products of an update, after the cache-filling first product and one "
+                   "tc_fill relayout pass)" % (CG_ITERS - 1, CG_ITERS)) if tc else
+                  ("fvp_jac_kernel (analytic Fisher-vector product on cached activations and output-Jacobian "
                    "rows; all %d products of an update, after one jac_fill_kernel pass)" % CG_ITERS) if jac else
                   ("fvp_rows_kernel<use cache> (analytic Fisher-vector product; %d of the %d products of an "
                    "update, the first one also computes the forward pass and fills the cache)"
@@ -415,23 +616,28 @@ def run_b200(args):
                   "FVP kernel (analytic Fisher-vector product, %d per update)" % CG_ITERS,
         "bound": "tensor", "achieved": ach_tf, "peak": tensor_peak, "unit": "TFLOP/s",
         "frac": ach_tf / tensor_peak, "peak_source": tensor_src + ", dense bf16 burst",
-        "traffic": traffic, "traffic_source": "ncu dram bytes of one launch (profiles/r01_fvp_traffic.json) scaled by N",
+        "traffic": traffic,
+        "traffic_source": "ncu dram bytes of one launch (profiles/%s) scaled by N" % os.path.basename(tp),
         "ms_per_launch": fvp_ms, "ms_per_launch_fill": fvp_fill_ms,
-        "ms_per_launch_activation_cached": fvp_rows_ms, "ms_jac_fill": jac_fill_ms,
+        "ms_per_launch_activation_cached": fvp_rows_ms, "ms_per_launch_jacobian_cached": fvp_jac_ms,
+        "ms_per_launch_tensor_memory": fvp_tc_ms, "ms_jac_fill": jac_fill_ms, "ms_tc_fill": tc_fill_ms,
         "algorithmic_flop_per_timestep": fvp_flop, "issued_flop_per_timestep": issued_flop,
         "algorithmic_bytes_per_timestep": fvp_bytes,
-        "note": "compute bound (%.0f flop per byte, SURVEY F13/H3).  The pass must hold fp32 accuracy "
-                "(1e-4 parity gate, measured ~1e-6), so every algorithmic flop is 3 TF32 tensor flops "
-                "(a_hi*b_hi + a_hi*b_lo + a_lo*b_hi) on mma.sync m16n8k8 (tcgen05 has no fp32-accurate "
-                "kind and its per-instruction issue floor at N=64 gives no gain here, DESIGN.md).  "
-                "`achieved` counts SURVEY 8(d)'s algorithmic flops of one product; the kernel issues "
-                "`issued_flop_per_timestep` of them (the caches replace the rest by HBM reads), which "
-                "`fp32_fma` and `tensor_flops_issued_tflops` are quoted on.  TF32 dense peak is half the "
-                "bf16 peak used as denominator.  ncu: profiles/r01d_jac_ncu_summary.txt."
-                % (fvp_flop / fvp_bytes),
-        "tensor_flops_issued_tflops": 3.0 * N * issued_flop / (fvp_ms * 1e-3) / 1e12,
+        "note": "compute bound (%.0f flop per byte, SURVEY F13/H3).  The pass must hold fp32 accuracy (1e-4 parity "
+                "gate, measured ~1e-6) and no tensor-core kind is fp32-accurate, so every algorithmic flop is 3 "
+                "kind::tf32 flops (hi*hi + lo*hi + hi*lo; the hi plane is the raw fp32 word, which the tensor core "
+                "truncates).  `achieved` counts SURVEY 8(d)'s algorithmic flops of one product against the measured "
+                "dense-bf16 peak; the kernel issues `issued_flop_per_timestep` of them (h1, h2 come from the cache), "
+                "i.e. `tensor_flops_issued_tflops` of TF32 work, quoted next to the measured tcgen05 TF32 peak in "
+                "`tf32`.  ncu: profiles/r02_tc_ncu_summary.txt." % (fvp_flop / fvp_bytes),
+        "tensor_flops_issued_tflops": tf32_issued,
+        "tf32": {"achieved_tflops": tf32_issued, "peak_tflops_measured": tf32_tc_peak,
+                 "frac": (tf32_issued / tf32_tc_peak) if tf32_tc_peak else None,
+                 "peak_source": pm.get("tf32_tcgen05_source")},
         "fp32_fma": {"achieved_tflops": N * issued_flop / (fvp_ms * 1e-3) / 1e12, "peak_tflops_nominal": fma_peak,
-                     "frac": N * issued_flop / (fvp_ms * 1e-3) / 1e12 / fma_peak, "flop_per_timestep": issued_flop},
+                     "peak_tflops_measured": fma_peak_meas,
+                     "frac": N * issued_flop / (fvp_ms * 1e-3) / 1e12 / (fma_peak_meas or fma_peak),
+                     "flop_per_timestep": issued_flop},
         "hbm": {"achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak},
         "whole_update_hbm": {"bytes_per_timestep": 56 * n + 16 * m + 88,
                              "achieved": N * (56 * n + 16 * m + 88) / (ms_step * 1e-3) / 1e9,
@@ -447,9 +653,17 @@ def run_b200(args):
             mlp_extra = mlpbase_timing(spec, resident, N)
         except Exception as e:   # e.g. obs_dim too wide for the fit kernels' shared-memory plan
             mlp_extra = {"unavailable": str(e)[:200]}
-    cb = None
+    cb = parity = None
     if rank == 0 and not args.no_cpu_baseline:
-        cb = cpu_baseline(args.workload)
+        cb, cctx = cpu_baseline(args.workload)
+        if world == 1:
+            try:
+                parity = parity_at_sample_size(cctx, dev)
+            except Exception as e:
+                parity = {"error": repr(e)[:300], "pass": False}
+    rinv = None
+    if world > 1 and not use_mlp:
+        rinv = rank_invariance(dev, world, rank)
     if rank == 0:
         print(json.dumps({
             "metric": "NPG update timesteps/sec", "value": value, "unit": "timesteps/s",
@@ -471,6 +685,8 @@ def run_b200(args):
                        "policy_reset_each_step": True},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
             **({"strong_scaling": strong} if strong else {}),
+            **({"rank_invariance": rinv} if rinv else {}),
+            **({"parity": parity} if parity else {}),
             "cpu_baseline": cb, "mlp_baseline": mlp_extra}))
     if world > 1:
         td.destroy_process_group()

@@ -120,6 +120,16 @@ def context(device=None):
     return _ctx[device]
 
 
+# bytes brought back from the device by the update path (bench.py reports the per-step count)
+D2H_BYTES = [0]
+
+
+def to_host(t):
+    """Device tensor -> numpy (synchronises the stream), counted in D2H_BYTES."""
+    D2H_BYTES[0] += int(t.numel() * t.element_size())
+    return t.cpu().numpy()
+
+
 def stream_ptr():
     import torch
     return c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -8,6 +8,7 @@ import time as timer
 import numpy as np
 import torch
 
+from .. import _lib
 from ..batch import PathBatch, batch_for
 from ..utils import process_samples
 from ..utils.logger import DataLog
@@ -140,7 +141,7 @@ class BatchREINFORCE:
         return n
 
     def _finish_stats(self, stats, paths):
-        base_stats = [float(v) for v in stats.cpu().numpy()]
+        base_stats = [float(v) for v in _lib.to_host(stats)]
         mean_return = base_stats[0]
         self.running_score = mean_return if self.running_score is None else \
             0.9 * self.running_score + 0.1 * mean_return
@@ -156,7 +157,7 @@ class BatchREINFORCE:
         p_old, curr = eng.dv.params("old"), eng.dv.params("new")
         old_ll = torch.empty(batch.N, dtype=torch.float32, device=eng.device)
         old_mean = torch.empty((batch.N, m), dtype=torch.float32, device=eng.device)
-        if torch.equal(p_old, curr):
+        if np.array_equal(self.policy.get_param_values(), self.policy.get_old_param_values()):
             eng.gradient(curr, batch.obs, batch.act, w, None, cache=(old_ll, old_mean))
         else:
             old_ll, old_mean = eng.old_cache(p_old, batch.obs, batch.act)
@@ -166,9 +167,9 @@ class BatchREINFORCE:
         eng.cg_x.copy_(eng.grad[:d] / N_glob)
         new_dev = eng.step(curr, 1.0 / N_glob, 0.0, const_alpha=float(self.alpha))
         out = eng.evaluate(new_dev, batch.obs, batch.act, w, old_ll, old_mean, p_old[d - m:], N_glob)
-        host = torch.cat([out, eng.grad[d:d + 1] / N_glob]).cpu().numpy()
+        host = _lib.to_host(torch.cat([out, eng.grad[d:d + 1] / N_glob]))
         t_gLL = timer.time() - ts
-        new_params = new_dev.cpu().numpy()
+        new_params = _lib.to_host(new_dev)
         eng.dist.check()     # multi-GPU: a peer exchange that timed out invalidates the update
         surr_after, kl_dist, surr_before = float(host[0]), float(host[1]), float(host[2])
         self.policy.set_param_values(new_params, set_new=True, set_old=True)

@@ -6,6 +6,7 @@ import numpy as np
 import torch
 
 from ..utils.logger import DataLog
+from .. import _lib
 from .batch_reinforce import BatchREINFORCE, _dev32
 
 
@@ -54,7 +55,8 @@ class NPG(BatchREINFORCE):
         p_old, curr = eng.dv.params("old"), eng.dv.params("new")
         old_ll = torch.empty(batch.N, dtype=torch.float32, device=eng.device)
         old_mean = torch.empty((batch.N, m), dtype=torch.float32, device=eng.device)
-        same = torch.equal(p_old, curr)
+        # host-side: both vectors come from the host copy of the policy (no device reduce, no sync)
+        same = np.array_equal(self.policy.get_param_values(), self.policy.get_old_param_values())
         ts = timer.time()
         if demo is None:
             if same:
@@ -88,8 +90,8 @@ class NPG(BatchREINFORCE):
     def _commit(self, eng, st, new_dev, out, paths, stats, extra_log=None, surr_before_dev=None):
         d = eng.dv.d
         sb = eng.grad[d:d + 1] / st["N_glob"] if surr_before_dev is None else surr_before_dev
-        host = torch.cat([out, sb, eng.scal4]).cpu().numpy()   # the update's single sync point
-        new_params = new_dev.cpu().numpy()
+        host = _lib.to_host(torch.cat([out, sb, eng.scal4]))   # the update's single sync point
+        new_params = _lib.to_host(new_dev)
         eng.dist.check()     # multi-GPU: a peer exchange that timed out invalidates the update
         surr_after, kl_dist, surr_before = float(host[0]), float(host[1]), float(host[2])
         alpha, n_step_size = float(host[3]), float(host[5])

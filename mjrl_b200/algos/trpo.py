@@ -3,6 +3,7 @@ import numpy as np
 import torch
 
 from ..utils.logger import DataLog
+from .. import _lib
 from .npg_cg import NPG
 
 
@@ -39,7 +40,8 @@ class TRPO(NPG):
         for k in range(100):
             new_dev = eng.step(st["curr"], st["g_scale"], n_step_size, alpha_scale=scale)
             out = eng.evaluate(new_dev, batch.obs, batch.act, w, st["old_ll"], st["old_mean"], old_ls,
-                               st["N_glob"]).cpu().numpy()
+                               st["N_glob"])
+            out = _lib.to_host(out)
             surr_after, kl = float(out[0]), float(np.float32(out[1]))
             ok = bool(kl < self.kl_dist)
             trials.append((kl, surr_after, ok))

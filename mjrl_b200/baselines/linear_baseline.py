@@ -65,8 +65,8 @@ class LinearBaseline:
                        ptr(prev), ptr(new), ptr(info), stream_ptr())
         errs = None
         if sync or return_errors:
-            self._coeffs = new.cpu().numpy()
-            h = info.cpu().numpy()
+            self._coeffs = _lib.to_host(new)
+            h = _lib.to_host(info)
             self.last_fit_info = dict(reg_coeff=h[0], retries=int(h[1]))
             if return_errors:
                 errs = (float(h[2]), float(h[3]))
