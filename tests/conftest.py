@@ -10,7 +10,7 @@ if ROOT not in sys.path:
 
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 GOLDEN_CASES = ["c1_linear", "c1_linear_mid", "c2_swimmer", "c3_hopper", "c3_hopper_mid",
-                "c5_adroit_mid"]
+                "c5_adroit_mid", "c4_ant_mid", "c5_adroit_64"]
 
 
 def pytest_configure(config):

@@ -415,6 +415,12 @@ if __name__ == "__main__":
         run_quadbase_case(R, "quadbase_pointmass", 6, 25, 1000, 9000)
         run_quadbase_case(R, "quadbase_hopper", 11, 200, 3000, 9001)
         sys.exit(0)
+    if "--c4c5-only" in sys.argv:
+        # BASELINE.json configs[3] / configs[4] shapes at the class-default (64, 64): Ant obs 111 / act 8 with
+        # mid-training transforms (TRPO backtrack count included), Adroit obs 45 / act 24
+        run_case(R, "c4_ant_mid", 111, 8, (64, 64), 100, 1200, 4000, True)
+        run_case(R, "c5_adroit_64", 45, 24, (64, 64), 100, 1500, 5001, False)
+        sys.exit(0)
     if "--mlpbase-only" in sys.argv:
         run_mlpbase_case(R, "mlpbase_1step", 11, 60, 150, 7000, 1, 0.0)
         run_mlpbase_case(R, "mlpbase_hopper", 11, 200, 1500, 7001, 2, 1e-3)
@@ -426,6 +432,8 @@ if __name__ == "__main__":
     run_case(R, "c3_hopper_mid", 11, 3, (64, 64), 200, 3000, 3001, True)
     run_case(R, "c5_adroit_mid", 45, 24, (32, 32), 100, 2000, 5000, True)
     run_case(R, "c1_linear_mid", 6,  2, (),        25, 1000, 1001, True)
+    run_case(R, "c4_ant_mid", 111, 8, (64, 64), 100, 1200, 4000, True)
+    run_case(R, "c5_adroit_64", 45, 24, (64, 64), 100, 1500, 5001, False)
     run_mlpbase_case(R, "mlpbase_1step", 11, 60, 150, 7000, 1, 0.0)
     run_mlpbase_case(R, "mlpbase_hopper", 11, 200, 1500, 7001, 2, 1e-3)
     run_ppo_case(R, "ppo_hopper_mid", 11, 3, (64, 64), 100, 640, 8000, True, 2)
