@@ -239,6 +239,13 @@ int mjrl_policy_grad_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const f
                             const float* obs, const float* act, const float* w, const float* old_ll,
                             int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
                             float* mean_out, float* fvp_cache, void* stream);
+/* mjrl_policy_grad_cached for shapes with the tensor-memory product (mjrl_policy_fvp_tc_ok): h1, h2 go straight
+ * into that product's tile-ordered copy (no fragment-ordered cache, no mjrl_policy_fvp_tc_fill pass); the CG
+ * solve then runs cache_mode 4 from its first product.  Modes 1-3 are NOT valid after this call. */
+int mjrl_policy_grad_cached_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                               const float* obs, const float* act, const float* w, const float* old_ll,
+                               int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
+                               float* mean_out, float* fvp_cache, void* stream);
 int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
                            const float* obs, int64_t N, const float* vec, double* fvp_sum,
                            const int32_t* stop_flag, float* cache, int32_t cache_mode, void* stream);

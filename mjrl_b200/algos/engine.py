@@ -182,13 +182,19 @@ class UpdateEngine:
         ll_out, mean_out = cache if cache is not None else (None, None)
         # the pass computes h1, h2 of (params, obs) anyway: leave them for the FVPs of the CG solve
         fcache = self._fvp_cache(N)
-        self.ctx.call("mjrl_policy_grad_cached", self.dv.desc_ref(), ptr(params), ptr(obs), ptr(act), ptr(w),
+        if self._tc_ok is None:
+            self._tc_ok = bool(_lib.load().mjrl_policy_fvp_tc_ok(self.ctx.h, self.dv.desc_ref()))
+        direct_tc = fcache is not None and self._tc_ok and N >= TC_MIN_N
+        # hidden 64 x 64 at a batch the tensor-memory product takes: h1, h2 go straight into its tile order
+        self.ctx.call("mjrl_policy_grad_cached_tc" if direct_tc else "mjrl_policy_grad_cached",
+                      self.dv.desc_ref(), ptr(params), ptr(obs), ptr(act), ptr(w),
                       ptr(old_ll), c_i64(N), ptr(tgt), c_void_p(tgt.data_ptr() + 8 * d),
                       ptr(ll_out), ptr(mean_out), ptr(fcache), stream_ptr())
         # the pass refilled h1|h2 for these tensors; Jacobian rows of any earlier policy / batch are stale
-        self._cache_key = self._hold(params, obs) if fcache is not None else None
+        key = self._hold(params, obs) if fcache is not None else None
+        self._cache_key = None if direct_tc else key     # fragment-ordered h1|h2 (modes 2, 3)
+        self._tc_key = key if direct_tc else None        # tile-ordered copy (mode 4)
         self._jac_key = None
-        self._tc_key = None
         self.launches += 3
         if accumulate:
             self.grad[:d] += tgt[:d]   # demo term: only the gradient, not the surrogate (dapg.py:93,98)
@@ -288,6 +294,8 @@ class UpdateEngine:
             # subsamples): the first product fills the activation cache, the others reuse it
             if subsample is not None:
                 mode = 0
+            elif self._tc_key is not None and self._tc_key == self._key(params, o):
+                mode = 4      # the gradient pass left h1|h2 in the tile order of the tensor-memory product
             elif self._cache_key is not None and self._cache_key == self._key(params, o):
                 # h1|h2 filled by the gradient pass (or the first product) at these tensors; small action
                 # dimensions also cache the output-Jacobian rows and run the cheaper product (fvp_jac.cu)
@@ -328,6 +336,8 @@ class UpdateEngine:
         fill_jac = 0
         if cache is None:
             first = rest = 0
+        elif self._tc_key is not None and self._tc_key == key:
+            first = rest = 4      # the gradient pass left h1|h2 in the tile order of the tensor-memory product
         elif self._cache_key is not None and self._cache_key == key:
             first = rest = self._cached_mode(params, obs)
         else:

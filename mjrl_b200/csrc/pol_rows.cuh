@@ -220,8 +220,26 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_rows_kernel(const Args a) {
 #pragma unroll
       for (int e = 0; e < 4; ++e) h1[nf][e] = tanh_fast(h1[nf][e]);
     float2* cslot = reinterpret_cast<float2*>(a.cache) + ((size_t)tile * 4 + hw) * (4 * NF * 32) + lane;
+    // cache_mode 5: h1, h2 go straight into the tile order of the tensor-memory product (fvp_tc.cu: tiles of 96
+    // timesteps, per tile an h1 and an h2 plane of 2 x [96 rows][128 B], 32-byte atoms swizzled by row mod 4);
+    // the 4 lanes of a quad write the 32 contiguous bytes of one atom
+    float* tcA = nullptr; float* tcB = nullptr;
+    if (GRAD && a.cache && a.cache_mode == 5) {
+      const long long tA = gA / 96, tB = gB / 96;
+      const int rA96 = (int)(gA - tA * 96), rB96 = (int)(gB - tB * 96);
+      tcA = a.cache + (size_t)tA * (2 * 96 * 64) + rA96 * 32 + 2 * c;
+      tcB = a.cache + (size_t)tB * (2 * 96 * 64) + rB96 * 32 + 2 * c;
+    }
+    auto tc_off = [](int nf, int r96) { return (nf >> 2) * (96 * 32) + (((nf & 3) ^ (r96 & 3)) << 3); };
+    const int sA = (int)(gA % 96) & 3, sB = (int)(gB % 96) & 3;
     if (GRAD) {
-      if (a.cache) {
+      if (tcA) {
+#pragma unroll
+        for (int nf = 0; nf < NF; ++nf) {
+          *reinterpret_cast<float2*>(tcA + tc_off(nf, sA)) = make_float2(h1[nf][0], h1[nf][1]);
+          *reinterpret_cast<float2*>(tcB + tc_off(nf, sB)) = make_float2(h1[nf][2], h1[nf][3]);
+        }
+      } else if (a.cache) {
 #pragma unroll
         for (int nf = 0; nf < NF; ++nf) {
           cslot[(2 * nf) * 32] = make_float2(h1[nf][0], h1[nf][1]);
@@ -261,7 +279,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_rows_kernel(const Args a) {
     for (int nf = 0; nf < NF; ++nf)
 #pragma unroll
       for (int e = 0; e < 4; ++e) h2[nf][e] = tanh_fast(h2[nf][e]);
-    if (GRAD && a.cache) {
+    if (GRAD && tcA) {
+#pragma unroll
+      for (int nf = 0; nf < NF; ++nf) {
+        *reinterpret_cast<float2*>(tcA + 96 * 64 + tc_off(nf, sA)) = make_float2(h2[nf][0], h2[nf][1]);
+        *reinterpret_cast<float2*>(tcB + 96 * 64 + tc_off(nf, sB)) = make_float2(h2[nf][2], h2[nf][3]);
+      }
+    } else if (GRAD && a.cache) {
 #pragma unroll
       for (int nf = 0; nf < NF; ++nf) {
         cslot[(2 * (NF + nf)) * 32] = make_float2(h2[nf][0], h2[nf][1]);

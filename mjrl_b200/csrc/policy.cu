@@ -1408,6 +1408,46 @@ int mjrl_policy_grad_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const f
   return mjrl_check_launch("policy_grad reduce");
 }
 
+static int64_t tc_region_offset(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N);
+
+int mjrl_policy_grad_cached_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                               const float* obs, const float* act, const float* w, const float* old_ll,
+                               int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
+                               float* mean_out, float* fvp_cache, void* stream) {
+  int rc = check_desc(desc, "policy_grad_cached_tc");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params && obs && act && grad_sum && fvp_cache && N > 0, MJRL_E_ARG,
+               "policy_grad_cached_tc: bad argument");
+  MJRL_REQUIRE(mjrl_policy_fvp_tc_ok(ctx, desc), MJRL_E_SHAPE,
+               "policy_grad_cached_tc: this policy shape has no tcgen05 product");
+  const int64_t off = tc_region_offset(ctx, desc, N);
+  MJRL_REQUIRE(off >= 0, MJRL_E_SHAPE, "policy_grad_cached_tc: shape not taken");
+  cudaStream_t s = (cudaStream_t)stream;
+  // rows of the last 96-timestep tile that no 64-timestep tile of the gradient pass writes: must be finite
+  // (they are operands of the weight-gradient MMAs, multiplied by zero rows)
+  {
+    const int64_t ntc = (N + 95) / 96, covered = ((N + rows::TSR - 1) / rows::TSR) * rows::TSR;
+    if (covered < ntc * 96) {
+      cudaError_t e = cudaMemsetAsync(fvp_cache + off + (ntc - 1) * (2 * 96 * 64), 0, sizeof(float) * 2 * 96 * 64, s);
+      if (e != cudaSuccess) { mjrl_set_error("policy_grad_cached_tc: memset: %s", cudaGetErrorString(e)); return (int)e; }
+    }
+  }
+  Args a = {};
+  fill_desc(a, desc);
+  a.params = params; a.obs = obs; a.act = act; a.w = w; a.old_ll = old_ll; a.N = N;
+  a.ll_out = ll_out; a.mean_out = mean_out;
+  a.cache = fvp_cache + off; a.cache_mode = 5;
+  int grid;
+  rc = launch_pol_rows<M_GRAD>(ctx, a, &grid, s);
+  MJRL_REQUIRE(rc >= 0, MJRL_E_SHAPE, "policy_grad_cached_tc: rows kernel does not take this shape");
+  if (rc) return rc;
+  const Flat F(desc->n, desc->m, desc->h1, desc->h2);
+  reduce_partials_kernel<<<(F.d + 31) / 32, 256, 0, s>>>(a.partials, grid, a.dstride, F.d, grad_sum,
+                                                            F.ols, 0.0, nullptr, nullptr, nullptr);
+  if (surr_sum) reduce_scalars_kernel<<<1, 32, 0, s>>>(a.spartials, grid, surr_sum, 1, nullptr);
+  return mjrl_check_launch("policy_grad_cached_tc reduce");
+}
+
 int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N) {
   if (!ctx || !desc || N <= 0) return 0;
   int HP, NPK;

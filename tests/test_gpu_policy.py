@@ -70,14 +70,16 @@ def test_forward_surrogate_gradient_fvp(golden):
     assert rel_l2(pol.log_likelihood(obs, act), g["pert_LL"]) < 1e-5
 
 
-@pytest.mark.parametrize("jac_min_n", [0, 1 << 30])
-def test_npg_update_and_cg_protocol(golden, jac_min_n, monkeypatch):
-    """jac_min_n = 0: the CG solve runs the Jacobian-cached product (act_dim <= 4 shapes) whatever the batch
-    size; 1 << 30: the activation-cached one.  Both must pass the same gates."""
+@pytest.mark.parametrize("variant", ["jac", "act", "tc"])
+def test_npg_update_and_cg_protocol(golden, variant, monkeypatch):
+    """Which product the CG solve runs, whatever the batch size: "tc" the tensor-memory product (hidden 64 x 64
+    shapes; the gradient pass then writes h1|h2 straight into its tile order), "jac" the Jacobian-cached rows
+    kernel (act_dim <= 4 shapes), "act" the activation-cached one.  All must pass the same gates."""
     from mjrl_b200.algos import engine
     from mjrl_b200.algos.npg_cg import NPG
     from oracle import mjrl_oracle as O
-    monkeypatch.setattr(engine, "JAC_MIN_N", jac_min_n)
+    monkeypatch.setattr(engine, "JAC_MIN_N", 0 if variant == "jac" else 1 << 30)
+    monkeypatch.setattr(engine, "TC_MIN_N", 0 if variant == "tc" else 1 << 30)
     g = golden
     p1 = prepared_paths(g)
     pol = make_policy(g)
@@ -361,15 +363,16 @@ def test_consecutive_updates_refresh_the_jacobian_cache(case, monkeypatch):
     g = load_golden(case)
     iters = 3            # k <= 3 iterates of the reference agree with any summation order to 3e-7
     finals = {}
-    for jac_min_n in (0, 1 << 30):
+    for jac_min_n, tc_min_n in ((0, 1 << 30), (1 << 30, 1 << 30), (1 << 30, 0)):
         monkeypatch.setattr(engine, "JAC_MIN_N", jac_min_n)
+        monkeypatch.setattr(engine, "TC_MIN_N", tc_min_n)
         p1 = prepared_paths(g)
         pol = make_policy(g)
         ag = agent(NPG, g, pol, normalized_step_size=0.01, FIM_invert_args={'iters': iters, 'damping': 1e-4})
         ag.train_from_paths(p1)
         mid = pol.get_param_values().copy()
         ag.train_from_paths(p1)
-        finals[jac_min_n] = (mid, pol.get_param_values().copy())
+        finals[(jac_min_n, tc_min_n)] = (mid, pol.get_param_values().copy())
     opol = O.GaussianPolicy(g["n"], g["m"], g["hidden"], g["params"], **(g["transforms"] or {}))
     p1 = prepared_paths(g)
     o1 = O.npg_update(opol, p1, cg_iters=iters)["new_params"].copy()
