@@ -66,7 +66,7 @@ constexpr uint32_t OFF_UT = OFF_XT + XTPLANE;
 constexpr uint32_t OFF_VEC = OFF_UT + UTPLANE;      // fp32 vectors, see Vec
 constexpr uint32_t VEC_FLOATS = 2 * MJ * H + H + 3 * MJ + 2 * KX + ROWS * MJ;
 constexpr uint32_t OFF_BAR = OFF_VEC + 4 * VEC_FLOATS;
-constexpr int NBAR = 20;
+constexpr int NBAR = 29;
 constexpr uint32_t SMEM_BYTES = OFF_BAR + 8 * NBAR + 16;
 constexpr uint32_t SMEM_ALLOC = SMEM_BYTES + 1024;  // the base is aligned up to 1024 in the kernel
 struct Vec {   // float offsets inside the vector block
@@ -81,7 +81,10 @@ struct Vec {   // float offsets inside the vector block
   static constexpr int UARR = IRCP + KX;       // [96][MJ] u of the tile (bias gradient gb2)
 };
 // barriers
-enum { B_H1 = 0, B_H2, B_E0, B_E1, B_E2A, B_E2B, B_E2C, B_E3, B_M1, B_M2A, B_M2B, B_GW2, B_M5, B_GW1, B_GW0, B_W3 };
+// the tail of a tile is pipelined per TMEM lane quadrant q (32 rows): gW2 / gW1 / gW0 are issued in three parts of
+// four k-steps, and the row threads of quadrant q only wait for (and signal) part q
+enum { B_H1 = 0, B_H2, B_E0, B_E1, B_E2A, B_E2B, B_M1, B_M2A, B_M2B, B_M5, B_GW0,
+       B_GW2 = 11, B_E2C = 14, B_GW1 = 17, B_E3 = 20, B_W3 = 23, B_H1Q = 26, B_COUNT = 29 };
 
 // ---- tensor memory map (columns) ------------------------------------------------------------------------
 constexpr uint32_t T_D1 = 0;        // dz1 -> dh1 hi (in place) -> gh1
@@ -246,9 +249,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
   for (uint32_t i = tid; i < VEC_FLOATS; i += NTHREADS) vecs[i] = 0.f;
   if (tid == 0) {
     tma::mbar_init(&bar[B_H1], 1); tma::mbar_init(&bar[B_H2], 1);
-    for (int b = B_E0; b <= B_E3; ++b) tma::mbar_init(&bar[b], ETHREADS);
+    for (int b = B_E0; b <= B_E2B; ++b) tma::mbar_init(&bar[b], ETHREADS);
     for (int b = B_M1; b <= B_GW0; ++b) tma::mbar_init(&bar[b], 1);
-    tma::mbar_init(&bar[B_W3], 32);
+    for (int qq = 0; qq < 3; ++qq) {
+      tma::mbar_init(&bar[B_GW2 + qq], 1); tma::mbar_init(&bar[B_GW1 + qq], 1);
+      tma::mbar_init(&bar[B_E2C + qq], 64); tma::mbar_init(&bar[B_E3 + qq], 64);
+      tma::mbar_init(&bar[B_W3 + qq], 32);
+      tma::mbar_init(&bar[B_H1Q + qq], 1);
+    }
     tma::mbar_init_fence();
   }
   if (warp == 7) {
@@ -347,7 +355,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
         tst16(tl + T_LO1 + 16, lo);
       }
       stamp(0);
-      tma::mbar_wait(&bar[B_H1], ph);
+      tma::mbar_wait(&bar[B_H1Q + q], ph);             // this quadrant's 32 rows of h1
       stamp(1);
       float s1[32];      // 1 - h1^2 of this thread's 32 columns: used by E1 and E3
       {
@@ -502,7 +510,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
       fence_before();
       mbar_arrive(&bar[B_E2B]);
       stamp(7);
-      tma::mbar_wait(&bar[B_GW2], ph);                  // gW2 has read h2 hi | lo: the planes become gz2
+      tma::mbar_wait(&bar[B_GW2 + q], ph);              // gW2 has read this quadrant's rows of h2 hi | lo: they become gz2
       stamp(8);
       {
         store_row32(pY, r, blk, gz);
@@ -512,7 +520,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
         store_row32(pZ, r, blk, v);
       }
       fence_async();
-      mbar_arrive(&bar[B_E2C]);
+      mbar_arrive(&bar[B_E2C + q]);
       stamp(9);
 
       // ---- E3: gz1 = gh1 (1 - h1^2); x~^T planes for gW0 -------------------------------------------------
@@ -537,13 +545,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
 #pragma unroll
       for (int i = 0; i < 32; ++i) gl[i] = lo_of(gz[i]);
       stamp(11);
-      tma::mbar_wait(&bar[B_GW1], ph);                  // gW1 has read gz2 and h1 (and every earlier MMA is done)
-      tma::mbar_wait(&bar[B_W3], ph);                   // warp 3 has summed gz2 for gb1
+      tma::mbar_wait(&bar[B_GW1 + q], ph);              // gW1 has read this quadrant's rows of gz2 (and every earlier MMA is done)
+      tma::mbar_wait(&bar[B_W3 + q], ph);               // warp 3 has summed them for gb1
       stamp(12);
       store_row32(pY, r, blk, gz);
       store_row32(pZ, r, blk, gl);
       fence_async();
-      mbar_arrive(&bar[B_E3]);
+      mbar_arrive(&bar[B_E3 + q]);
       prefetch_obs(tile + gridDim.x);
       stamp(13);
     }
@@ -551,37 +559,54 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
   } else if (warp == 3) {
     // =========================== loader + bias gradients ==================================================
     double gb1a = 0.0, gb1b = 0.0, gb2 = 0.0;
-    auto load_plane = [&](int tile, int which) {   // which 0: h1 -> X, 1: h2 -> Y
+    auto load_h2 = [&](int tile) {                 // h2 -> Y, one copy
       if (lane == 0) {
-        uint64_t* b = &bar[which ? B_H2 : B_H1];
-        tma::mbar_expect(b, PLANE);
-        tma::bulk_g2s(sm + (which ? OFF_Y : OFF_X), tile_base + (size_t)tile * (2 * PLANE / 4) + (which ? PLANE / 4 : 0), PLANE, b);
+        tma::mbar_expect(&bar[B_H2], PLANE);
+        tma::bulk_g2s(sm + OFF_Y, tile_base + (size_t)tile * (2 * PLANE / 4) + PLANE / 4, PLANE, &bar[B_H2]);
       }
     };
-    if ((int)blockIdx.x < ntiles) { load_plane(blockIdx.x, 0); load_plane(blockIdx.x, 1); }
+    auto load_h1q = [&](int tile, int qq) {        // rows 32 qq .. of h1 -> X: 4 KB of each of the two column blocks
+      if (lane == 0) {
+        uint64_t* b = &bar[B_H1Q + qq];
+        tma::mbar_expect(b, 2 * 32 * 128);
+        const float* src = tile_base + (size_t)tile * (2 * PLANE / 4) + qq * (32 * 128 / 4);
+        tma::bulk_g2s(sm + OFF_X + qq * (32 * 128), src, 32 * 128, b);
+        tma::bulk_g2s(sm + OFF_X + BLK + qq * (32 * 128), src + BLK / 4, 32 * 128, b);
+      }
+    };
+    if ((int)blockIdx.x < ntiles) {
+      for (int qq = 0; qq < 3; ++qq) load_h1q(blockIdx.x, qq);
+      load_h2(blockIdx.x);
+    }
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
       if (lane == 0 && tile + (int)gridDim.x < ntiles)   // the next tile's planes start their way to L2 now
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
                      :: "l"(tile_base + (size_t)(tile + gridDim.x) * (2 * PLANE / 4)), "r"(2 * PLANE) : "memory");
-      tma::mbar_wait(&bar[B_E2C], ph);       // gz2 (hi = the full fp32 value) is in Y, u in UARR
       {
         const int c0 = 2 * lane, qa = c0 >> 3;
-        float2 acc[8];
+        float sx = 0.f, sy = 0.f;
+#pragma unroll 1
+        for (int qq = 0; qq < 3; ++qq) {
+          tma::mbar_wait(&bar[B_E2C + qq], ph);       // rows of quadrant qq of gz2 (hi = the full fp32 value) are in Y
+          float2 acc[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = make_float2(0.f, 0.f);
+          for (int k = 0; k < 8; ++k) acc[k] = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int rr = 0; rr < ROWS; rr += 8) {
+          for (int rr = 0; rr < 32; rr += 8) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const float2 v = *reinterpret_cast<const float2*>(pY + mn_atom(rr + k, qa) + (c0 & 7) * 4);
-            acc[k].x += v.x; acc[k].y += v.y;
+            for (int k = 0; k < 8; ++k) {
+              const float2 v = *reinterpret_cast<const float2*>(pY + mn_atom(32 * qq + rr + k, qa) + (c0 & 7) * 4);
+              acc[k].x += v.x; acc[k].y += v.y;
+            }
           }
+          mbar_arrive(&bar[B_W3 + qq]);
+          sx += ((acc[0].x + acc[1].x) + (acc[2].x + acc[3].x)) + ((acc[4].x + acc[5].x) + (acc[6].x + acc[7].x));
+          sy += ((acc[0].y + acc[1].y) + (acc[2].y + acc[3].y)) + ((acc[4].y + acc[5].y) + (acc[6].y + acc[7].y));
         }
-        gb1a += (double)(((acc[0].x + acc[1].x) + (acc[2].x + acc[3].x)) + ((acc[4].x + acc[5].x) + (acc[6].x + acc[7].x)));
-        gb1b += (double)(((acc[0].y + acc[1].y) + (acc[2].y + acc[3].y)) + ((acc[4].y + acc[5].y) + (acc[6].y + acc[7].y)));
-        if (lane < MJ) {
+        gb1a += (double)sx; gb1b += (double)sy;
+        if (lane < MJ) {    // u of the tile (written before B_E2A, which precedes every B_E2C)
           float f[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
           for (int rr = 0; rr < ROWS; rr += 4) {
@@ -591,12 +616,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
           gb2 += (double)((f[0] + f[1]) + (f[2] + f[3]));
         }
       }
-      mbar_arrive(&bar[B_W3]);
       const int next = tile + gridDim.x;
-      tma::mbar_wait(&bar[B_GW1], ph);       // gW1 has read h1 hi | lo; the row threads read X only in E0 (s1 stays in registers)
-      if (next < ntiles) load_plane(next, 0);
+#pragma unroll 1
+      for (int qq = 0; qq < 3; ++qq) {
+        // gW1 part qq has read rows 32 qq .. of h1 hi | lo (the row threads read X only in E0: s1 stays in registers)
+        tma::mbar_wait(&bar[B_GW1 + qq], ph);
+        if (next < ntiles) load_h1q(next, qq);
+      }
       tma::mbar_wait(&bar[B_GW0], ph);       // gz1 planes (Y, Z) are free
-      if (next < ntiles) load_plane(next, 1);
+      if (next < ntiles) load_h2(next);
     }
     float* out = a.partials + (size_t)blockIdx.x * a.dstride;
     out[F.ob1 + 2 * lane] = (float)gb1a;
@@ -660,11 +688,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
       tma::mbar_wait(&bar[B_E2A], ph);
       fence_after();
       if (elect_one()) {
-        // gW2 (+)= [h2 hi | lo]^T [u hi | lo]
+        // gW2 (+)= [h2 hi | lo]^T [u hi | lo], one part per lane quadrant
 #pragma unroll
-        for (int ks = 0; ks < KSTEPS; ++ks)
-          mma_ss(tb + T_ACC2, mndesc(OFF_Y, ks), ktdesc(OFF_UT, 16, ks), ID_GW2, first | (ks > 0));
-        commit(&bar[B_GW2]);
+        for (int qq = 0; qq < 3; ++qq) {
+#pragma unroll
+          for (int ks = 4 * qq; ks < 4 * qq + 4; ++ks)
+            mma_ss(tb + T_ACC2, mndesc(OFF_Y, ks), ktdesc(OFF_UT, 16, ks), ID_GW2, first | (ks > 0));
+          commit(&bar[B_GW2 + qq]);
+        }
       }
       __syncwarp();
       tma::mbar_wait(&bar[B_E2B], ph);
@@ -680,26 +711,32 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
         commit(&bar[B_M5]);
       }
       __syncwarp();
-      tma::mbar_wait(&bar[B_E2C], ph);
-      fence_after();
-      if (elect_one()) {
-        // gW1 (+)= [gz2 hi | lo]^T [h1 hi | lo]
+#pragma unroll 1
+      for (int qq = 0; qq < 3; ++qq) {
+        tma::mbar_wait(&bar[B_E2C + qq], ph);
+        fence_after();
+        if (elect_one()) {
+          // gW1 (+)= [gz2 hi | lo]^T [h1 hi | lo]
 #pragma unroll
-        for (int ks = 0; ks < KSTEPS; ++ks)
-          mma_ss(tb + T_ACC1, mndesc(OFF_Y, ks), mndesc(OFF_X, ks), ID_GW1, first | (ks > 0));
-        commit(&bar[B_GW1]);
+          for (int ks = 0; ks < 4; ++ks)
+            mma_ss(tb + T_ACC1, mndesc(OFF_Y, 4 * qq + ks), mndesc(OFF_X, 4 * qq + ks), ID_GW1, first | ((qq | ks) > 0));
+          commit(&bar[B_GW1 + qq]);
+        }
+        __syncwarp();
       }
-      __syncwarp();
-      tma::mbar_wait(&bar[B_E3], ph);
-      fence_after();
-      if (elect_one()) {
-        // gW0 (+)= [gz1 hi | lo]^T [x~ hi | lo]
+#pragma unroll 1
+      for (int qq = 0; qq < 3; ++qq) {
+        tma::mbar_wait(&bar[B_E3 + qq], ph);
+        fence_after();
+        if (elect_one()) {
+          // gW0 (+)= [gz1 hi | lo]^T [x~ hi | lo]
 #pragma unroll
-        for (int ks = 0; ks < KSTEPS; ++ks)
-          mma_ss(tb + T_ACC0, mndesc(OFF_Y, ks), ktdesc(OFF_XT, 32, ks), ID_GW0, first | (ks > 0));
-        commit(&bar[B_GW0]);
+          for (int ks = 0; ks < 4; ++ks)
+            mma_ss(tb + T_ACC0, mndesc(OFF_Y, 4 * qq + ks), ktdesc(OFF_XT, 32, 4 * qq + ks), ID_GW0, first | ((qq | ks) > 0));
+          if (qq == 2) commit(&bar[B_GW0]);
+        }
+        __syncwarp();
       }
-      __syncwarp();
     }
   }
 
