@@ -845,14 +845,6 @@ inline int launch_fvp_rows(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s
   if (!a.partials) return MJRL_E_STATE;
   const bool use = a.cache && a.cache_mode == 2;
   if (a.cache_mode != 1 && !use) a.cache = nullptr;
-  if (use) {   // warp-specialised variant of the cached product (fvp_ws.cu): opt-in, MJRL_B200_FVP_WS=1
-    // (measured 0.794 ms against 0.775 ms for the half-CTA kernel on the Hopper shape: DESIGN.md 3.1)
-    static const bool ws_on = getenv("MJRL_B200_FVP_WS") && getenv("MJRL_B200_FVP_WS")[0] == '1';
-    if (ws_on) {
-      const int rc = launch_fvp_ws(ctx, a, grid, s);
-      if (rc >= 0) return rc;
-    }
-  }
 #define ROWS_CASE(H, K)                                                                     \
   if (HP == H && NPK == K)                                                                  \
     return use ? launch_rows_one<H, K, true>(ctx, a, grid, smem, s)                         \

@@ -310,7 +310,7 @@ __device__ __forceinline__ void mma_wgrad(float (&acc)[NFR][4], const float* __r
     for (int e = 0; e < 4; ++e) acc[j][e] += odd[j][e];
 }
 
-// ---- arguments shared by every policy kernel (policy.cu, fvp_rows.cuh, pol_rows.cuh, fvp_ws.cu) ----
+// ---- arguments shared by every policy kernel (policy.cu, fvp_rows.cuh, pol_rows.cuh, fvp_jac.cu) ----
 enum Mode { M_FWD = 0, M_EVAL = 1, M_GRAD = 2, M_FVP = 3 };
 
 struct Args {
@@ -338,9 +338,6 @@ struct Args {
   float* cache;   // FVP rows kernel: forward activations in fragment order (fill or use), may be null
   int cache_mode; // 0 none, 1 fill, 2 use, 3 use h1|h2 and the Jacobian rows G1 (fvp_jac.cu)
 };
-
-// warp-specialised cached FVP (fvp_ws.cu): returns -1 when it does not take the shape
-int launch_fvp_ws(mjrl_ctx* ctx, const Args& a, int grid, cudaStream_t s);
 
 // Jacobian-cached FVP (fvp_jac.cu), act_dim <= 4: shape test, extra cache floats after the h1|h2 region,
 // the fill pass and the product (-1 when the shape does not fit)

@@ -293,37 +293,6 @@ def test_fvp_jacobian_variant_not_offered_for_wide_actions():
     assert eng._jac_prepare(eng.dv.params("new"), obs) is False
 
 
-def test_warp_specialised_fvp_variant_in_subprocess():
-    """MJRL_B200_FVP_WS=1 selects the warp-specialised cached FVP kernel (csrc/fvp_ws.cu; the switch is
-    read once per process, hence the subprocess): same result as the default kernel to fp32 rounding."""
-    import os, subprocess, sys
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    code = r"""
-import sys, numpy as np, torch
-sys.path.insert(0, %r)
-from mjrl_b200.policies.gaussian_mlp import MLP
-from mjrl_b200.utils.gym_env import EnvSpec
-from mjrl_b200.algos.engine import UpdateEngine
-rng = np.random.default_rng(3)
-pol = MLP(EnvSpec(11, 3, 100, 1), hidden_sizes=(64, 64), seed=5)
-flat = pol.get_param_values(); flat = flat + 0.3 * rng.standard_normal(flat.shape).astype(np.float32)
-pol.set_param_values(flat.copy(), True, True)
-eng = UpdateEngine(pol); dev = eng.device
-obs = torch.from_numpy(rng.standard_normal((1500, 11)).astype(np.float32)).to(dev)
-vec = torch.from_numpy(rng.standard_normal(flat.shape[0]).astype(np.float32) * 0.1).to(dev)
-outs = []
-for mode in (1, 2, 2):
-    out = torch.zeros(flat.shape[0], dtype=torch.float64, device=dev)
-    eng.cg_flags.zero_(); eng.fvp(eng.dv.params("new"), obs, vec, out, cache_mode=mode); outs.append(out.cpu().numpy())
-rel = np.linalg.norm(outs[1] - outs[0]) / np.linalg.norm(outs[0])
-assert np.array_equal(outs[1], outs[2]) and rel < 2e-6, rel
-print("WS_OK %%.2e" %% rel)
-""" % root
-    env = dict(os.environ, MJRL_B200_FVP_WS="1")
-    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0 and "WS_OK" in r.stdout, r.stdout + r.stderr
-
-
 def test_cg_solve_reference_signature_over_hvp_eval(golden):
     """utils.cg_solve (mjrl/utils/cg_solve.py:3-22) with the operator npg_cg.py:122-124 builds:
     `cg_solve(agent.build_Hvp_eval([obs, act], regu_coef), vpg_grad, x_0=vpg_grad.copy(), cg_iters=k)`
