@@ -429,8 +429,15 @@ def run_b200(args):
         resident.returns = resident.baseline = resident.adv = None
         return agent.train_step(N, gamma=GAMMA, gae_lambda=LAM, paths=resident)
 
-    def step_e2e():
-        b = PathBatch(h_obs, h_act, h_rew, off, term, device=local)   # H2D from pinned host memory
+    # e2e inputs: pinned HOST buffers as a producer of this package leaves them -- observations and actions in
+    # fp32 (the cast the reference applies on every call, gaussian_mlp.py:103-104, done once by the producer; the
+    # values are fp32-representable), rewards in fp64.  `e2e_fp64_paths` times the same step from fp64
+    # observation / action buffers, i.e. arrays laid out like the reference's list of path dicts.
+    h_obs32, h_act32 = pin(hb["observations"].astype(np.float32)), pin(hb["actions"].astype(np.float32))
+
+    def step_e2e(fp64=False):
+        b = PathBatch(h_obs if fp64 else h_obs32, h_act if fp64 else h_act32, h_rew, off, term,
+                      device=local)                                # H2D from pinned host memory
         out = agent.train_step(N, gamma=GAMMA, gae_lambda=LAM, paths=b)
         return b, out
 
@@ -484,7 +491,24 @@ def run_b200(args):
     d = int(pol.d)
     d2h = (_lib.D2H_BYTES[0] - d2h0) // args.steps      # counted where the update reads results back (_lib.to_host)
     e2e = {"value": N * world / e2e_s, "unit": "timesteps/s", "ms_per_step": 1e3 * e2e_s,
-           "h2d_bytes_per_step": int(b.h2d_bytes), "d2h_bytes_per_step": int(d2h)}
+           "h2d_bytes_per_step": int(b.h2d_bytes), "d2h_bytes_per_step": int(d2h),
+           "host_buffers": "pinned; observations / actions fp32, rewards fp64"}
+    # the same from fp64 observation / action buffers (the reference's `paths` dtype)
+    for _ in range(2):
+        reset(); step_e2e(True)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        reset()
+        b64, _ = step_e2e(True)
+        torch.cuda.synchronize()
+    barrier()
+    te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        td.all_reduce(te, op=td.ReduceOp.MAX)
+    e2e64_s = float(te.item()) / args.steps
+    e2e["fp64_paths"] = {"value": N * world / e2e64_s, "ms_per_step": 1e3 * e2e64_s,
+                         "h2d_bytes_per_step": int(b64.h2d_bytes)}
 
     # ---- strong scaling (north_star: ONE batch of the named size sharded over the GPUs) -----------
     # The headline `value` is weak scaling (the named batch per GPU).  Here the same N timesteps are split

@@ -126,7 +126,10 @@ class UpdateEngine:
             self.dist.enable_peer(self.ctx, d + 1)
         dev = self.device
         f64 = lambda k: torch.zeros(k, dtype=torch.float64, device=dev)
-        self.grad = f64(d + 1)              # [gradient sum | surrogate sum] packed for one all-reduce
+        # [gradient sum | surrogate sum] packed for one all-reduce, followed by the update's scalar results
+        # (surrogate / KL sums, step scalars): one contiguous device->host read at the end of an update
+        self.gbuf = f64(d + 1 + 6)
+        self.grad = self.gbuf[:d + 1]
         self.cg_x, self.cg_r, self.cg_p, self.cg_z = f64(d), f64(d), f64(d), f64(d)
         self.cg_scal = f64(8)
         self.cg_p32 = torch.zeros(d, dtype=torch.float32, device=dev)
@@ -134,8 +137,8 @@ class UpdateEngine:
         self.cg = CGState(*[c_void_p(t.data_ptr()) for t in
                             (self.cg_x, self.cg_r, self.cg_p, self.cg_z, self.cg_scal, self.cg_p32,
                              self.cg_flags)])
-        self.sums2 = f64(2)
-        self.scal4 = f64(4)
+        self.sums2 = self.gbuf[d + 1:d + 3]
+        self.scal4 = self.gbuf[d + 3:d + 7]
         self.mom = f64(4)
         self.new_params = torch.zeros(d, dtype=torch.float32, device=dev)
         self.launches = 0  # kernels launched by this engine (bench's gpu_launches)
@@ -381,11 +384,18 @@ class UpdateEngine:
         self.launches += 1
         return self.new_params
 
-    def evaluate(self, params_new, obs, act, w, old_ll, old_mean, old_log_std, N_global):
-        """(surrogate, KL) of params_new against the cached old policy -> device fp64 [2] means."""
+    def evaluate(self, params_new, obs, act, w, old_ll, old_mean, old_log_std, N_global, raw=False):
+        """(surrogate, KL) of params_new against the cached old policy -> device fp64 [2] means (`raw`: the sums,
+        left in `self.sums2` for `tail()`: the caller divides on the host)."""
         self.ctx.call("mjrl_policy_eval", self.dv.desc_ref(), ptr(params_new), ptr(obs), ptr(act),
                       ptr(w), ptr(old_ll), ptr(old_mean), ptr(old_log_std), c_i64(obs.shape[0]),
                       ptr(self.sums2), stream_ptr())
         self.launches += 2
         self.dist.allreduce(self.sums2)
-        return self.sums2 / N_global
+        return self.sums2 if raw else self.sums2 / N_global
+
+    def tail(self):
+        """Device view [surrogate-before sum, surrogate-after sum, KL sum, alpha, g.x, n_step_size, alpha*scale]:
+        what an update reads back, contiguous behind the gradient."""
+        d = self.dv.d
+        return self.gbuf[d:d + 7]

@@ -89,8 +89,14 @@ class NPG(BatchREINFORCE):
 
     def _commit(self, eng, st, new_dev, out, paths, stats, extra_log=None, surr_before_dev=None):
         d = eng.dv.d
-        sb = eng.grad[d:d + 1] / st["N_glob"] if surr_before_dev is None else surr_before_dev
-        host = _lib.to_host(torch.cat([out, sb, eng.scal4]))   # the update's single sync point
+        if out is None:
+            # the sums of evaluate(raw=True) sit behind the gradient next to the step scalars: ONE contiguous read,
+            # no device-side concatenation or division (the means are formed here, in the same fp64 arithmetic)
+            t = _lib.to_host(eng.tail())                       # the update's single sync point
+            host = np.concatenate([t[1:3] / st["N_glob"], t[0:1] / st["N_glob"], t[3:7]])
+        else:
+            sb = eng.grad[d:d + 1] / st["N_glob"] if surr_before_dev is None else surr_before_dev
+            host = _lib.to_host(torch.cat([out, sb, eng.scal4]))   # the update's single sync point
         new_params = _lib.to_host(new_dev)
         eng.dist.check()     # multi-GPU: a peer exchange that timed out invalidates the update
         surr_after, kl_dist, surr_before = float(host[0]), float(host[1]), float(host[2])
@@ -117,6 +123,6 @@ class NPG(BatchREINFORCE):
         eng, batch, w, stats = self._prepare(paths)
         st = self._npg_direction(eng, batch, w, trace=cg_trace)
         new_dev = eng.step(st["curr"], st["g_scale"], self.n_step_size, const_alpha=self.alpha)
-        out = eng.evaluate(new_dev, batch.obs, batch.act, w, st["old_ll"], st["old_mean"],
-                           st["p_old"][eng.dv.d - eng.dv.m:], st["N_glob"])
-        return self._commit(eng, st, new_dev, out, paths, stats)
+        eng.evaluate(new_dev, batch.obs, batch.act, w, st["old_ll"], st["old_mean"],
+                     st["p_old"][eng.dv.d - eng.dv.m:], st["N_glob"], raw=True)
+        return self._commit(eng, st, new_dev, None, paths, stats)
