@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--baseline", default="linear", choices=["linear", "mlp"],
                     help="value baseline inside the timed update: LinearBaseline (north_star (b), default) or "
                          "MLPBaseline (BASELINE.json configs[2]; its fit is a serial chain of Adam steps)")
+    ap.add_argument("--algo", default="npg", choices=["npg", "trpo", "dapg"],
+                    help="update rule inside the timed step: NPG (default, the metric), TRPO with its KL line search "
+                         "(BASELINE.json configs[3]) or DAPG with 25 synthetic demonstration paths (configs[4])")
     ap.add_argument("--phases", action="store_true", help="also print a per-phase breakdown to stderr")
     return ap.parse_args()
 
@@ -386,8 +389,18 @@ def run_b200(args):
         base = MLPBaseline(spec, epochs=1)
     else:
         base = LinearBaseline(spec)
-    agent = NPG(None, pol, base, normalized_step_size=STEP,
-                FIM_invert_args={"iters": CG_ITERS, "damping": DAMPING})
+    fim = {"iters": CG_ITERS, "damping": DAMPING}
+    if args.algo == "trpo":
+        from mjrl_b200.algos.trpo import TRPO
+        agent = TRPO(None, pol, base, kl_dist=0.5 * STEP, FIM_invert_args=fim)
+        _tfp = agent.train_from_paths
+        agent.train_from_paths = lambda paths, **kw: _tfp(paths, verbose=False, **kw)
+    elif args.algo == "dapg":
+        from mjrl_b200.algos.dapg import DAPG
+        demo = syn.flat_to_paths(syn.make_flat_batch(25 * min(horizon, 200), n, m, min(horizon, 200), 4242, flat0, hidden))
+        agent = DAPG(None, pol, base, demo_paths=demo, kl_dist=0.5 * STEP, lam_0=1.0, lam_1=0.95, FIM_invert_args=fim)
+    else:
+        agent = NPG(None, pol, base, normalized_step_size=STEP, FIM_invert_args=fim)
 
     # synthetic trajectories (seed depends on the rank: every GPU owns its own whole paths)
     hb = syn.make_flat_batch(N, n, m, horizon, 3000 + rank, flat0, hidden)
@@ -422,6 +435,8 @@ def run_b200(args):
         def reset():
             pol.set_param_values(flat0.copy(), True, True)
             base._coeffs = coeffs0.copy()
+            if args.algo == "dapg":
+                agent.iter_count = 0.0
 
     resident = PathBatch(h_obs, h_act, h_rew, off, term, device=local)
 
@@ -677,6 +692,12 @@ def run_b200(args):
             mlp_extra = mlpbase_timing(spec, resident, N)
         except Exception as e:   # e.g. obs_dim too wide for the fit kernels' shared-memory plan
             mlp_extra = {"unavailable": str(e)[:200]}
+    configs2 = None
+    if rank == 0 and world == 1 and not use_mlp and args.algo == "npg" and args.workload == "C3-hopper":
+        try:
+            configs2 = configs2_value(spec, hidden, flat0, (h_obs32, h_act32, h_rew, off, term), local, N)
+        except Exception as e:
+            configs2 = {"unavailable": repr(e)[:200]}
     cb = parity = None
     if rank == 0 and not args.no_cpu_baseline:
         cb, cctx = cpu_baseline(args.workload)
@@ -694,9 +715,11 @@ def run_b200(args):
             "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "%s: NPG + %s + %s, obs %d act %d, %d timesteps per GPU "
+            "config": {"workload": "%s: %s + %s + %s, obs %d act %d, %d timesteps per GPU "
                                    "(%d paths), gamma %.3f lambda %.2f, %d CG iters, damping %g"
-                                   % (args.workload, "MLP%s" % (hidden,) if hidden else "LinearPolicy",
+                                   % (args.workload, {"npg": "NPG", "trpo": "TRPO (KL line search)",
+                                                      "dapg": "DAPG (25 demonstration paths)"}[args.algo],
+                                      "MLP%s" % (hidden,) if hidden else "LinearPolicy",
                                       "MLPBaseline(epochs=1, batch 64: %d serial Adam steps)" % base.last_fit_steps
                                       if use_mlp else "LinearBaseline", n, m,
                                       N, len(off) - 1, GAMMA, LAM, CG_ITERS, DAMPING),
@@ -708,12 +731,57 @@ def run_b200(args):
                        "l2": "256 MB buffer written between timed steps (outside the event brackets)",
                        "policy_reset_each_step": True},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
+            **({"value_configs2": configs2.get("value"), "configs2": configs2} if configs2 else {}),
             **({"strong_scaling": strong} if strong else {}),
             **({"rank_invariance": rinv} if rinv else {}),
             **({"parity": parity} if parity else {}),
             "cpu_baseline": cb, "mlp_baseline": mlp_extra}))
     if world > 1:
         td.destroy_process_group()
+
+
+def configs2_value(spec, hidden, flat0, host, local, N):
+    """BASELINE.json configs[2] VERBATIM: the same 1M-timestep update with `MLPBaseline` (epochs 1, batch 64) inside
+    the timed region -- returns, MLP predict, GAE, gradient, CG, step, evaluation and the baseline's fit, a serial
+    chain of int(N/64)-1 dependent Adam steps (mlp_baseline.py:83-98) that no amount of data parallelism shortens.
+    CUDA events, 1 warm-up + 3 timed steps, policy and baseline reset before each."""
+    import torch
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.baselines.mlp_baseline import MLPBaseline
+    from mjrl_b200.algos.npg_cg import NPG
+    from mjrl_b200.batch import PathBatch
+    from mjrl_b200.utils import process_samples as ps
+    torch.manual_seed(7); np.random.seed(7)
+    pol = MLP(spec, hidden_sizes=hidden, seed=123)
+    base = MLPBaseline(spec, epochs=1)
+    agent = NPG(None, pol, base, normalized_step_size=STEP, FIM_invert_args={"iters": CG_ITERS, "damping": DAMPING})
+    batch = PathBatch(*host, device=local)
+    dev = batch.device
+    ps.returns_on_device(batch, GAMMA)
+    base.fit_batch(batch)
+    st0 = {k: v.clone() for k, v in base._state(dev).items()}
+    step0 = base.adam_step
+
+    def one():
+        pol.set_param_values(flat0.copy(), True, True)
+        for k, v in base._state(dev).items():
+            v.copy_(st0[k])
+        base.adam_step = step0
+        batch.returns = batch.baseline = batch.adv = None
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        agent.train_step(N, gamma=GAMMA, gae_lambda=LAM, paths=batch)
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b)
+
+    one()
+    ts = sorted(one() for _ in range(3))
+    ms = ts[1]
+    return {"value": N / (ms * 1e-3), "unit": "timesteps/s", "ms_per_step": ms, "fit_steps": base.last_fit_steps,
+            "workload": "NPG + MLP(64,64) + MLPBaseline(epochs=1, batch 64) on the same batch: BASELINE.json configs[2] "
+                        "verbatim; the fit is %d SERIAL Adam steps" % base.last_fit_steps}
 
 
 def mlpbase_timing(spec, batch, N):

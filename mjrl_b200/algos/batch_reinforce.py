@@ -123,8 +123,7 @@ class BatchREINFORCE:
         (npg_cg.py:87-104)."""
         eng = self._engine()
         batch = paths if isinstance(paths, PathBatch) else batch_for(paths)
-        if batch.adv is None:
-            batch.adv = batch.gather("advantages")
+        batch.adv = batch.current("advantages", batch.adv)
         w = eng.whiten(batch.adv, eps=1e-6)
         stats = torch.empty(4, dtype=torch.float64, device=eng.device)
         eng.ctx.call("mjrl_path_return_stats", _ptr(batch.rew), _ptr(batch.offsets),

@@ -133,6 +133,9 @@ class PPO(BatchREINFORCE):
         if aliased:
             p_old_eff[:d - m].copy_(params[:d - m])
             old_ll, old_mean = eng.old_cache(p_old_eff, batch.obs, batch.act)
+        # ppo_clip.py:100-103: set_param_values(set_new=True) clamps log_std at min_log_std BEFORE surr_after and the
+        # KL are computed; Adam can push log_std below the floor
+        ctx.call("mjrl_policy_clamp_log_std", eng.dv.desc_ref(), ptr(params), c_float(self.policy.min_log_std), st)
         out = eng.evaluate(params, batch.obs, batch.act, w, old_ll, old_mean, p_old[d - m:], N_glob)
         host = torch.cat([out, surr_before_dev]).cpu().numpy()
         params_after_opt = params.cpu().numpy()

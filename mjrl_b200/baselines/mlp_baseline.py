@@ -192,8 +192,8 @@ class MLPBaseline:
     # ---- reference-compatible API -------------------------------------------------------------
     def fit(self, paths, return_errors=False):
         batch = batch_for(paths)
-        if "returns" in paths[0] and batch.returns is None:
-            batch.returns = batch.gather("returns")
+        if "returns" in paths[0]:
+            batch.returns = batch.current("returns", batch.returns)
         return self.fit_batch(batch, return_errors=return_errors)
 
     def predict(self, path):

@@ -127,8 +127,27 @@ class PathBatch:
             return
         h = tensor.detach().cpu().numpy()
         off = self.h_offsets
+        views = []
         for i, p in enumerate(self.paths):
             p[key] = h[off[i]:off[i + 1]]
+            views.append(p[key])
+        if not hasattr(self, "_views"):
+            self._views = {}
+        self._views[key] = views
+
+    def current(self, key, dev):
+        """Device copy of a per-path field for a consumer that the reference would hand the path dicts to: the
+        resident tensor `dev` when every dict still holds exactly the array this batch scattered there, else the
+        dicts' arrays re-uploaded -- the reference re-reads `path[key]` on every call (npg_cg.py:87-91,
+        linear_baseline.py:22-23), so a caller that REPLACES advantages / returns between compute_advantages and
+        train_from_paths / fit is honoured.  (Editing a scattered array in place is not detected: drop_cache().)"""
+        if self.paths is None or key not in self.paths[0]:
+            return dev
+        views = getattr(self, "_views", {}).get(key)
+        if dev is not None and views is not None and len(views) == len(self.paths) and \
+                all(p.get(key) is v for p, v in zip(self.paths, views)):
+            return dev
+        return self.gather(key)
 
     def gather(self, key):
         """Upload a per-path fp64 field of the dicts (e.g. 'returns' set by someone else)."""

@@ -416,3 +416,37 @@ def test_fvp_tensor_memory_variant_not_offered_for_other_shapes():
     for n, m, hidden in ((11, 3, (32, 32)), (17, 3, (64, 64)), (11, 3, (64, 32))):
         eng = UpdateEngine(MLP(EnvSpec(n, m, 100, 1), hidden_sizes=hidden, seed=5))
         assert _lib.load().mjrl_policy_fvp_tc_ok(eng.ctx.h, eng.dv.desc_ref()) == 0
+
+
+def test_replaced_advantages_and_returns_are_honoured():
+    """The reference re-reads path['advantages'] / path['returns'] from the dicts on every call (npg_cg.py:87-91,
+    linear_baseline.py:22-23).  A caller that replaces them between compute_advantages and train_from_paths /
+    baseline.fit must see the replacement used, not the device copy of the earlier computation."""
+    from conftest import load_golden
+    from mjrl_b200.algos.npg_cg import NPG
+    from mjrl_b200.baselines.linear_baseline import LinearBaseline
+    from mjrl_b200.utils import process_samples as ps
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from oracle import mjrl_oracle as O
+    g = load_golden("c3_hopper")
+    paths = syn.flat_to_paths(batch_of(g, "b1_"))
+    spec = EnvSpec(g["n"], g["m"], g["horizon"], 1)
+    base = LinearBaseline(spec)
+    base._coeffs = g["fit0_coeffs"].copy()
+    ps.compute_returns(paths, g["gamma"])
+    ps.compute_advantages(paths, base, g["gamma"], g["gae_lambda"])      # scatters device results into the dicts
+    rng = np.random.default_rng(5)
+    for p in paths:                                                      # user post-processing: NEW arrays
+        p["advantages"] = p["advantages"] * rng.uniform(0.5, 2.0) + 0.3
+        p["returns"] = p["returns"] - 1.5
+    o_paths = [dict(p) for p in paths]
+    pol = make_policy(g)
+    ag = agent(NPG, g, pol, normalized_step_size=0.01, FIM_invert_args={'iters': 3, 'damping': 1e-4})
+    ag.train_from_paths(paths)
+    opol = O.GaussianPolicy(g["n"], g["m"], g["hidden"], g["params"], **(g["transforms"] or {}))
+    out = O.npg_update(opol, o_paths, cg_iters=3)
+    assert rel_l2(pol.get_param_values() - g["params"], out["new_params"] - g["params"]) < TOL
+    base.fit(paths)
+    ob = O.LinearBaseline(); ob.fit(o_paths)
+    X = np.concatenate([O.linear_features(p) for p in o_paths])
+    assert rel_l2(X @ np.asarray(base._coeffs), X @ ob._coeffs) < 1e-6
