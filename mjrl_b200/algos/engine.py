@@ -185,9 +185,7 @@ class UpdateEngine:
         ll_out, mean_out = cache if cache is not None else (None, None)
         # the pass computes h1, h2 of (params, obs) anyway: leave them for the FVPs of the CG solve
         fcache = self._fvp_cache(N)
-        if self._tc_ok is None:
-            self._tc_ok = bool(_lib.load().mjrl_policy_fvp_tc_ok(self.ctx.h, self.dv.desc_ref()))
-        direct_tc = fcache is not None and self._tc_ok and N >= TC_MIN_N
+        direct_tc = fcache is not None and self._tc_kind() > 0 and N >= TC_MIN_N
         # hidden 64 x 64 at a batch the tensor-memory product takes: h1, h2 go straight into its tile order
         self.ctx.call("mjrl_policy_grad_cached_tc" if direct_tc else "mjrl_policy_grad_cached",
                       self.dv.desc_ref(), ptr(params), ptr(obs), ptr(act), ptr(w),
@@ -228,12 +226,18 @@ class UpdateEngine:
             self._jac_key = key
         return True
 
+    def _tc_kind(self):
+        """0: no tcgen05 product for this policy shape; 1: the fused kernel (csrc/fvp_tc.cu; its planes come from the
+        gradient pass or from a relayout of the fragment-ordered cache); 2: the three-pass form for wide observation /
+        action vectors (csrc/fvp_tc_wide.cu; planes and x~ image from the gradient pass only)."""
+        if self._tc_ok is None:
+            self._tc_ok = int(_lib.load().mjrl_policy_fvp_tc_ok(self.ctx.h, self.dv.desc_ref()))
+        return self._tc_ok
+
     def _tc_prepare(self, params, obs):
         """With the h1|h2 cache valid for (params, obs): make its tile-ordered copy for the tensor-memory product
         (csrc/fvp_tc.cu) valid too -- one relayout pass per CG solve.  False when the shape has no such product."""
-        if self._tc_ok is None:
-            self._tc_ok = bool(_lib.load().mjrl_policy_fvp_tc_ok(self.ctx.h, self.dv.desc_ref()))
-        if not self._tc_ok or self._cache is None:
+        if self._tc_kind() != 1 or self._cache is None:
             return False
         key = self._key(params, obs)
         if self._tc_key != key:
@@ -349,11 +353,9 @@ class UpdateEngine:
             self._jac_key = None
             self._tc_key = None
             if iters > 1:
-                if self._tc_ok is None:
-                    self._tc_ok = bool(_lib.load().mjrl_policy_fvp_tc_ok(self.ctx.h, self.dv.desc_ref()))
                 if self._jac_ok is None:
                     self._jac_ok = bool(_lib.load().mjrl_policy_fvp_jac_ok(self.ctx.h, self.dv.desc_ref()))
-                if self._tc_ok and N >= TC_MIN_N:
+                if self._tc_kind() == 1 and N >= TC_MIN_N:
                     rest, fill_jac = 4, 2        # relayout pass after the first (cache-filling) product
                     self._tc_key = key
                 elif self._jac_ok and N >= JAC_MIN_N:

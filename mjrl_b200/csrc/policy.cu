@@ -14,6 +14,7 @@
 // These passes are fp32-FMA bound, not HBM bound.
 #include <stdlib.h>
 
+#include "fvp_tc.cuh"
 #include "policy_tile.cuh"
 
 namespace pol {
@@ -348,6 +349,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_kernel(const Args a) {
       }
     }
     __syncthreads();
+    if (HP == 64 && MODE == M_GRAD && a.cache_mode == 5 && a.cache) {
+      // h1 | h2 of the tile in the plane order of the tcgen05 product (fvp_tc.cuh: 96-timestep tiles, 32-byte atoms)
+      for (int i = tid; i < TS * 8; i += NTHREADS) {
+        const int tr = i >> 3, qa = i & 7;
+        const long long row = t0 + tr;
+        if (row >= (a.N + tc::ROWS - 1) / tc::ROWS * tc::ROWS) continue;   // past the last 96-timestep tile
+        const long long t96 = row / tc::ROWS;
+        const int r96 = (int)(row - t96 * tc::ROWS);
+        float* dst = a.cache + (size_t)t96 * (2 * tc::PLANE / 4) + tc::mn_atom(r96, qa) / 4;
+        const float4* s1 = reinterpret_cast<const float4*>(sH1 + tr * LDH + 8 * qa);
+        const float4* s2 = reinterpret_cast<const float4*>(sH2 + tr * LDH + 8 * qa);
+        reinterpret_cast<float4*>(dst)[0] = s1[0]; reinterpret_cast<float4*>(dst)[1] = s1[1];
+        reinterpret_cast<float4*>(dst + tc::PLANE / 4)[0] = s2[0]; reinterpret_cast<float4*>(dst + tc::PLANE / 4)[1] = s2[1];
+      }
+    }
     PHASE_STAMP(2);
     // ---- P3a: head.  4 lanes split K for one timestep (lane q takes k = q, q+4, ...: the
     // activation reads of a warp then cover all 32 banks and the four weight rows of one step
@@ -910,7 +926,7 @@ int launch_mode(mjrl_ctx* ctx, Args& a, int* grid_out, cudaStream_t s) {
     const int rc = launch_pol_rows<MODE>(ctx, a, grid_out, s);
     if (rc >= 0) return rc;
   }
-  a.cache = nullptr;   // the tile kernels below neither fill nor use the activation cache
+  if (a.cache_mode != 5) a.cache = nullptr;   // the tile kernels below neither fill nor use the fragment-ordered cache
   const int HP = hmax <= 32 ? 32 : 64;
   const Flat F(a.n, a.m, a.h1, a.h2);
   const bool bwd = MODE == M_GRAD || MODE == M_FVP;
@@ -1412,9 +1428,35 @@ int mjrl_policy_grad_cached_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, cons
                "policy_grad_cached_tc: bad argument");
   MJRL_REQUIRE(mjrl_policy_fvp_tc_ok(ctx, desc), MJRL_E_SHAPE,
                "policy_grad_cached_tc: this policy shape has no tcgen05 product");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (mjrl_policy_fvp_tc_ok(ctx, desc) == 2) {
+    // wide observation / action vectors (fvp_tc_wide.cu): the shared-memory tile kernel writes the planes, one more
+    // pass builds the x~ image both first-layer passes of every product read
+    Args a = {};
+    fill_desc(a, desc);
+    a.params = params; a.obs = obs; a.act = act; a.w = w; a.old_ll = old_ll; a.N = N;
+    a.ll_out = ll_out; a.mean_out = mean_out;
+    a.cache = fvp_cache; a.cache_mode = 5;
+    {
+      const int64_t ntc = (N + 95) / 96, covered = ((N + 63) / 64) * 64;   // the tile kernel walks 64 timesteps at a time
+      if (covered < ntc * 96) {
+        cudaError_t e = cudaMemsetAsync(fvp_cache + (ntc - 1) * (2 * 96 * 64), 0, sizeof(float) * 2 * 96 * 64, s);
+        if (e != cudaSuccess) { mjrl_set_error("policy_grad_cached_tc: memset: %s", cudaGetErrorString(e)); return (int)e; }
+      }
+    }
+    rc = launch_tcw_ximg(ctx, a, fvp_cache, s);
+    if (rc) return rc;
+    int grid;
+    rc = launch_mode<M_GRAD>(ctx, a, &grid, s);
+    if (rc) return rc;
+    const Flat F(desc->n, desc->m, desc->h1, desc->h2);
+    reduce_partials_kernel<<<(F.d + 31) / 32, 256, 0, s>>>(a.partials, grid, a.dstride, F.d, grad_sum,
+                                                              F.ols, 0.0, nullptr, nullptr, nullptr);
+    if (surr_sum) reduce_scalars_kernel<<<1, 32, 0, s>>>(a.spartials, grid, surr_sum, 1, nullptr);
+    return mjrl_check_launch("policy_grad_cached_tc reduce");
+  }
   const int64_t off = tc_region_offset(ctx, desc, N);
   MJRL_REQUIRE(off >= 0, MJRL_E_SHAPE, "policy_grad_cached_tc: shape not taken");
-  cudaStream_t s = (cudaStream_t)stream;
   // rows of the last 96-timestep tile that no 64-timestep tile of the gradient pass writes: must be finite
   // (they are operands of the weight-gradient MMAs, multiplied by zero rows)
   {
@@ -1444,7 +1486,8 @@ int64_t mjrl_policy_fvp_cache_count(mjrl_ctx* ctx, const mjrl_policy_desc* desc,
   if (!ctx || !desc || N <= 0) return 0;
   int HP, NPK;
   size_t smem;
-  if (!rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem)) return 0;
+  if (!rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem))
+    return tcw_fits(ctx, desc->n, desc->m, desc->h1, desc->h2) ? tcw_cache_floats(desc->n, N) : 0;
   const int64_t ntiles = (N + rows::TSR - 1) / rows::TSR;
   int64_t cnt = ntiles * rows::TSR * 2 * HP;   // h1 and h2 of every (padded) timestep
   if (jac_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, nullptr, nullptr, nullptr))
@@ -1470,16 +1513,18 @@ int mjrl_policy_fvp_tc_ok(mjrl_ctx* ctx, const mjrl_policy_desc* desc) {
   if (!ctx || !desc) return 0;
   int HP, NPK;
   size_t smem;
-  return rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem) && HP == 64 &&
-         tc_fits(ctx, desc->n, desc->m, desc->h1, desc->h2) ? 1 : 0;
+  if (rows_fits(ctx, desc->n, desc->m, desc->h1, desc->h2, &HP, &NPK, &smem))
+    return HP == 64 && tc_fits(ctx, desc->n, desc->m, desc->h1, desc->h2) ? 1 : 0;
+  // shapes the rows-in-registers kernels do not take: the three-pass form, fed by mjrl_policy_grad_cached_tc only
+  return tcw_fits(ctx, desc->n, desc->m, desc->h1, desc->h2) ? 2 : 0;
 }
 
 int mjrl_policy_fvp_tc_fill(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N, float* cache, void* stream) {
   int rc = check_desc(desc, "policy_fvp_tc_fill");
   if (rc) return rc;
   MJRL_REQUIRE(ctx && cache && N > 0, MJRL_E_ARG, "policy_fvp_tc_fill: bad argument");
-  MJRL_REQUIRE(mjrl_policy_fvp_tc_ok(ctx, desc), MJRL_E_SHAPE,
-               "policy_fvp_tc_fill: this policy shape has no tcgen05 product");
+  MJRL_REQUIRE(mjrl_policy_fvp_tc_ok(ctx, desc) == 1, MJRL_E_SHAPE,
+               "policy_fvp_tc_fill: this policy shape has no fragment-ordered cache to re-order");
   const int64_t off = tc_region_offset(ctx, desc, N);
   MJRL_REQUIRE(off >= 0, MJRL_E_SHAPE, "policy_fvp_tc_fill: shape not taken");
   return launch_tc_fill(ctx, cache, cache + off, N, (cudaStream_t)stream);
@@ -1533,8 +1578,12 @@ int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const fl
   } else if (cache_mode == 4) {
     MJRL_REQUIRE(mjrl_policy_fvp_tc_ok(ctx, desc), MJRL_E_SHAPE,
                  "policy_fvp: cache_mode 4 needs a shape mjrl_policy_fvp_tc_ok accepts");
-    const int64_t off = tc_region_offset(ctx, desc, N);
-    rc = launch_fvp_tc(ctx, a, off >= 0 ? cache + off : nullptr, &grid, s);
+    if (mjrl_policy_fvp_tc_ok(ctx, desc) == 2) {
+      rc = launch_fvp_tcw(ctx, a, cache, &grid, s);
+    } else {
+      const int64_t off = tc_region_offset(ctx, desc, N);
+      rc = launch_fvp_tc(ctx, a, off >= 0 ? cache + off : nullptr, &grid, s);
+    }
     MJRL_REQUIRE(rc >= 0, MJRL_E_SHAPE, "policy_fvp: tcgen05 product does not take this shape");
   } else {
     rc = launch_any<M_FVP>(ctx, a, &grid, s);

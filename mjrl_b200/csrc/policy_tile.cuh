@@ -336,7 +336,7 @@ struct Args {
   int n, m, h1, h2, dstride;
   int prefetch;   // 1: double-buffered obs/act staging (Layout::XR/AR present)
   float* cache;   // FVP rows kernel: forward activations in fragment order (fill or use), may be null
-  int cache_mode; // 0 none, 1 fill, 2 use, 3 use h1|h2 and the Jacobian rows G1 (fvp_jac.cu)
+  int cache_mode; // 0 none, 1 fill, 2 use, 3 use h1|h2 and the Jacobian rows G1 (fvp_jac.cu), 5 fill in the tile order of fvp_tc.cu
 };
 
 // Jacobian-cached FVP (fvp_jac.cu), act_dim <= 4: shape test, extra cache floats after the h1|h2 region,
@@ -353,5 +353,11 @@ bool tc_fits(const mjrl_ctx* ctx, int n, int m, int h1, int h2);
 long long tc_cache_floats(long long N);
 int launch_tc_fill(mjrl_ctx* ctx, const float* frag_cache, float* tc_cache, long long N, cudaStream_t s);
 int launch_fvp_tc(mjrl_ctx* ctx, Args& a, const float* tc_cache, int* grid_out, cudaStream_t s);
+// three-pass tcgen05 product for wide observation / action vectors (fvp_tc_wide.cu): shape test, cache floats
+// ([h1 | h2 planes][x~ image][DZ1][GZ1]), the x~ image pass (once per gradient pass) and the product
+bool tcw_fits(const mjrl_ctx* ctx, int n, int m, int h1, int h2);
+long long tcw_cache_floats(int n, long long N);
+int launch_tcw_ximg(mjrl_ctx* ctx, const Args& a, float* cache, cudaStream_t s);
+int launch_fvp_tcw(mjrl_ctx* ctx, Args& a, float* cache, int* grid_out, cudaStream_t s);
 
 }  // namespace pol

@@ -408,14 +408,86 @@ def test_fvp_tensor_memory_variant(n, m, N, mid):
         np.testing.assert_array_equal(a[-m:], ref[-m:])
 
 
+@pytest.mark.parametrize("n,m,N,mid", [(111, 8, 1000, True), (45, 24, 777, True), (24, 3, 96, False), (63, 16, 4097, True),
+                                       (64, 9, 2049, False), (127, 24, 500, True), (31, 1, 97, False), (111, 8, 40000, True),
+                                       (45, 24, 30000, False)])
+def test_fvp_tensor_memory_wide_variant(n, m, N, mid):
+    """cache_mode 4 for the shapes the fused kernel does not hold (csrc/fvp_tc_wide.cu: obs_dim + 1 <= 128, act_dim <=
+    24; Ant 111 / 8, Adroit 45 / 24): first layer as two tcgen05 passes of its own around the main kernel, fed by the
+    gradient pass (planes + x~ image).  Same product as the shared-memory tile kernel to fp32 rounding, deterministic,
+    exact against the fp64 Gauss-Newton truth, per block of the flat vector, ragged N, several tiles per CTA."""
+    import torch
+    from mjrl_b200 import _lib
+    from mjrl_b200.policies.gaussian_mlp import MLP
+    from mjrl_b200.utils.gym_env import EnvSpec
+    from mjrl_b200.algos import engine as E
+    from oracle import mjrl_oracle as O
+    rng = np.random.default_rng(n * 100 + N)
+    pol = MLP(EnvSpec(n, m, 100, 1), hidden_sizes=(64, 64), seed=5)
+    flat = pol.get_param_values()
+    tr = None
+    if mid:
+        flat, tr = syn.mid_training_variant(flat, n, m, 77)
+        pol.model.set_transformations(**tr); pol.old_model.set_transformations(**tr)
+    else:
+        flat = flat + 0.1 * rng.standard_normal(flat.shape).astype(np.float32)
+    pol.set_param_values(flat.copy(), True, True)
+    eng = E.UpdateEngine(pol)
+    dev = eng.device
+    assert _lib.load().mjrl_policy_fvp_tc_ok(eng.ctx.h, eng.dv.desc_ref()) == 2
+    obs = torch.from_numpy((2 * rng.standard_normal((N, n))).astype(np.float32)).to(dev)
+    act = torch.from_numpy(rng.standard_normal((N, m)).astype(np.float32)).to(dev)
+    w = torch.from_numpy(rng.standard_normal(N).astype(np.float32)).to(dev)
+    params = eng.dv.params("new")
+    tp = O.TruthPolicy(O.GaussianPolicy(n, m, (64, 64), flat.copy(), **(tr or {})))
+    keep, E.TC_MIN_N = E.TC_MIN_N, 1 << 60
+    try:
+        g_plain = eng.gradient(params, obs, act, w).clone()
+        E.TC_MIN_N = 0
+        g_tc = eng.gradient(params, obs, act, w).clone()          # also leaves the planes and the x~ image
+    finally:
+        E.TC_MIN_N = keep
+    np.testing.assert_array_equal(g_plain.cpu().numpy(), g_tc.cpu().numpy())
+    assert eng._tc_key is not None
+
+    def product(vec, mode):
+        out = torch.zeros(flat.shape[0], dtype=torch.float64, device=dev)
+        eng.cg_flags.zero_()
+        eng.fvp(params, obs, vec, out, cache_mode=mode)
+        return out.cpu().numpy()
+
+    F = [0, 64 * n, 64 * n + 64, 64 * n + 64 + 4096, 64 * n + 128 + 4096, 64 * n + 128 + 4096 + 64 * m,
+         64 * n + 128 + 4096 + 64 * m + m]
+    for k, s in enumerate((0.1, 3.0, 1e-3)):
+        vec = torch.from_numpy(rng.standard_normal(flat.shape[0]).astype(np.float32) * s).to(dev)
+        a, b = product(vec, 4), product(vec, 4)
+        np.testing.assert_array_equal(a, b)
+        truth = None
+        if N <= 5000:
+            truth = N * tp.fvp(obs.cpu().numpy(), vec.cpu().numpy().astype(np.float64))
+            assert rel_l2(a, truth) < 1e-5, (k, rel_l2(a, truth))
+        if n + m > 140:
+            ref = truth       # the tile kernel's product does not fit shared memory at this shape (its gradient pass does)
+        else:
+            ref = product(vec, 0)
+            assert rel_l2(a, ref) < 3e-6, (k, rel_l2(a, ref))
+        for lo, hi in zip(F[:-1], F[1:]):
+            assert rel_l2(a[lo:hi], ref[lo:hi]) < 1e-5, (k, lo, hi, rel_l2(a[lo:hi], ref[lo:hi]))
+        if ref is not truth:
+            np.testing.assert_array_equal(a[-m:], ref[-m:])
+
+
 def test_fvp_tensor_memory_variant_not_offered_for_other_shapes():
     from mjrl_b200 import _lib
     from mjrl_b200.policies.gaussian_mlp import MLP
     from mjrl_b200.utils.gym_env import EnvSpec
     from mjrl_b200.algos.engine import UpdateEngine
-    for n, m, hidden in ((11, 3, (32, 32)), (17, 3, (64, 64)), (11, 3, (64, 32))):
+    for n, m, hidden in ((11, 3, (32, 32)), (11, 3, (64, 32)), (128, 3, (64, 64)), (45, 25, (64, 64)), (111, 8, (32, 32))):
         eng = UpdateEngine(MLP(EnvSpec(n, m, 100, 1), hidden_sizes=hidden, seed=5))
-        assert _lib.load().mjrl_policy_fvp_tc_ok(eng.ctx.h, eng.dv.desc_ref()) == 0
+        assert _lib.load().mjrl_policy_fvp_tc_ok(eng.ctx.h, eng.dv.desc_ref()) == 0, (n, m, hidden)
+    # obs_dim 17 (HalfCheetah / Walker shapes): too wide for the fused kernel and for the rows-in-registers plan -> three-pass form
+    eng = UpdateEngine(MLP(EnvSpec(17, 6, 100, 1), hidden_sizes=(64, 64), seed=5))
+    assert _lib.load().mjrl_policy_fvp_tc_ok(eng.ctx.h, eng.dv.desc_ref()) == 2
 
 
 def test_replaced_advantages_and_returns_are_honoured():
