@@ -230,7 +230,12 @@ int mjrl_policy_fvp_jac_fill(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const 
  * and A operands in tensor memory).  It reads h1, h2 from a copy of the cache in its own tile order:
  * mjrl_policy_fvp_tc_ok: 1 when the shape has this variant (mjrl_policy_fvp_cache_count then includes the
  * copy).  mjrl_policy_fvp_tc_fill builds the copy from an ALREADY FILLED h1|h2 cache (once per CG solve, a pure
- * relayout); products then pass cache_mode 4.  Same result as the other modes to fp32 rounding (~1e-6). */
+ * relayout); products then pass cache_mode 4.  Same result as the other modes to fp32 rounding (~1e-6).
+ * Return value 2: a shape the fused kernel does not hold (obs_dim + 1 <= 128, act_dim <= 24; Ant 111 / 8, Adroit
+ * 45 / 24) that runs the three-pass form of csrc/fvp_tc_wide.cu instead: first-layer tangent and weight-gradient
+ * products as tcgen05 passes of their own around the main kernel.  Its cache (mjrl_policy_fvp_cache_count) holds the
+ * planes, an [x~ | 1] image and two first-layer images; only mjrl_policy_grad_cached_tc fills it (no
+ * mjrl_policy_fvp_tc_fill for these shapes). */
 int mjrl_policy_fvp_tc_ok(mjrl_ctx* ctx, const mjrl_policy_desc* desc);
 int mjrl_policy_fvp_tc_fill(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N, float* cache, void* stream);
 /* mjrl_policy_grad that also fills that cache (flat_vpg runs at the parameters the CG solve that
@@ -246,6 +251,15 @@ int mjrl_policy_grad_cached_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, cons
                                const float* obs, const float* act, const float* w, const float* old_ll,
                                int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
                                float* mean_out, float* fvp_cache, void* stream);
+/* mjrl_policy_eval (surrogate and KL sums of batch_reinforce.py:57-75) on the tcgen05 pass of csrc/pol_tc.cu, for
+ * shapes mjrl_policy_fvp_tc_ok accepts.  The gradient pass mjrl_policy_grad_cached_tc runs the same kernel family
+ * unless MJRL_B200_GRAD_TC=0.  Shapes of kind 2 read the [x~ | 1] image that mjrl_policy_grad_cached_tc left in
+ * `fvp_cache` for the SAME obs / N / input transforms (fvp_cache may be NULL for kind 1).  Same sums as
+ * mjrl_policy_eval to fp32 rounding. */
+int mjrl_policy_eval_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                        const float* obs, const float* act, const float* w, const float* old_ll,
+                        const float* old_mean, const float* old_log_std, int64_t N, double* sums2,
+                        float* fvp_cache, void* stream);
 int mjrl_policy_fvp_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
                            const float* obs, int64_t N, const float* vec, double* fvp_sum,
                            const int32_t* stop_flag, float* cache, int32_t cache_mode, void* stream);

@@ -100,7 +100,7 @@ class Context:
 # kernels each entry point launches (csrc/*.cu), for the launch count bench.py reports
 KERNELS_PER_CALL = {"mjrl_moments": 4, "mjrl_moments_noalloc": 4, "mjrl_path_return_stats": 2, "mjrl_linbase_gram": 2,
                     "mjrl_quadbase_gram": 2,
-                    "mjrl_policy_eval": 2, "mjrl_policy_grad": 3, "mjrl_policy_fvp": 2,
+                    "mjrl_policy_eval": 2, "mjrl_policy_eval_tc": 2, "mjrl_policy_grad": 3, "mjrl_policy_fvp": 2,
                     "mjrl_policy_fvp_cached": 2, "mjrl_policy_grad_cached": 3, "mjrl_policy_grad_cached_tc": 3,
                     "mjrl_policy_act": 2, "mjrl_rollout_act": 2, "mjrl_mlpbase_features": 2, "mjrl_mlpbase_sqerr": 2}
 

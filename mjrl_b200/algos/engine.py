@@ -24,6 +24,8 @@ from .._lib import CGState, c_double, c_float, c_i64, c_int, c_void_p, ptr, stre
 JAC_MIN_N = int(os.environ.get("MJRL_B200_FVP_JAC_MIN_N", "32768"))
 # Same threshold for the tensor-memory product (csrc/fvp_tc.cu): it needs a relayout pass per solve.
 TC_MIN_N = int(os.environ.get("MJRL_B200_FVP_TC_MIN_N", "32768"))
+# surrogate / KL evaluation on the tcgen05 pass (csrc/pol_tc.cu) for the shapes and batch sizes the product takes
+EVAL_TC = os.environ.get("MJRL_B200_EVAL_TC", "1") != "0"
 
 
 class Dist:
@@ -148,6 +150,7 @@ class UpdateEngine:
         self._jac_ok = None
         self._tc_key = None   # same for the tile-ordered copy the tensor-memory product reads
         self._tc_ok = None
+        self._ximg_key = None  # obs the [x~ | 1] image of the wide tcgen05 passes was built from
         self._held = None     # tensors of the current cache keys (see _hold)
 
     # ------------------------------------------------------------------ building blocks
@@ -195,6 +198,7 @@ class UpdateEngine:
         key = self._hold(params, obs) if fcache is not None else None
         self._cache_key = None if direct_tc else key     # fragment-ordered h1|h2 (modes 2, 3)
         self._tc_key = key if direct_tc else None        # tile-ordered copy (mode 4)
+        self._ximg_key = self._key(obs, obs) if direct_tc and self._tc_kind() == 2 else None   # [x~ | 1] image (wide shapes)
         self._jac_key = None
         self.launches += 3
         if accumulate:
@@ -389,9 +393,19 @@ class UpdateEngine:
     def evaluate(self, params_new, obs, act, w, old_ll, old_mean, old_log_std, N_global, raw=False):
         """(surrogate, KL) of params_new against the cached old policy -> device fp64 [2] means (`raw`: the sums,
         left in `self.sums2` for `tail()`: the caller divides on the host)."""
-        self.ctx.call("mjrl_policy_eval", self.dv.desc_ref(), ptr(params_new), ptr(obs), ptr(act),
-                      ptr(w), ptr(old_ll), ptr(old_mean), ptr(old_log_std), c_i64(obs.shape[0]),
-                      ptr(self.sums2), stream_ptr())
+        N = obs.shape[0]
+        kind = self._tc_kind() if N >= TC_MIN_N and EVAL_TC else 0
+        if kind == 2 and not (self._cache is not None and self._ximg_key is not None and self._ximg_key == self._key(obs, obs)):
+            kind = 0      # wide shapes need the [x~ | 1] image the gradient pass of THIS batch left in the cache
+        if kind:
+            self.ctx.call("mjrl_policy_eval_tc", self.dv.desc_ref(), ptr(params_new), ptr(obs), ptr(act),
+                          ptr(w), ptr(old_ll), ptr(old_mean), ptr(old_log_std), c_i64(N),
+                          ptr(self.sums2), ptr(self._cache), stream_ptr())
+            self.launches += 1 if kind == 2 else 0
+        else:
+            self.ctx.call("mjrl_policy_eval", self.dv.desc_ref(), ptr(params_new), ptr(obs), ptr(act),
+                          ptr(w), ptr(old_ll), ptr(old_mean), ptr(old_log_std), c_i64(N),
+                          ptr(self.sums2), stream_ptr())
         self.launches += 2
         self.dist.allreduce(self.sums2)
         return self.sums2 if raw else self.sums2 / N_global

@@ -35,14 +35,6 @@ constexpr int MAXKB = 4;                           // obs_dim + 1 <= 128
 constexpr uint32_t XBLK = ROWS * 128;              // one 32-column block of the x~ image: [96 rows][128 B]
 constexpr int AUX_THREADS = 192;                   // passes A and C: 4 row / lane warps, loader, MMA issuer
 
-__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
-               :: "l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-
 // ---- x~ image ----------------------------------------------------------------------------------------------
 // per tile: KB blocks of [96 rows][32 columns], 128-byte rows, 16-byte chunks XOR-swizzled by the row index mod 8;
 // column obs_dim holds the 1 of the bias, columns past it and rows past N are zero.  One thread writes 16 bytes.
@@ -918,6 +910,66 @@ static int tcw_attr(K kern, uint32_t bytes, const char* what) {
   return 0;
 }
 
+TcwRegions tcw_regions(float* cache, int n, long long N) {
+  const long long ntiles = (N + tc::ROWS - 1) / tc::ROWS;
+  TcwRegions r;
+  r.KB = tcw_kb(n);
+  r.h12 = cache;
+  r.ximg = r.h12 + ntiles * (2 * (long long)tc::PLANE / 4);
+  r.z1 = r.ximg + ntiles * (long long)r.KB * (tcw::XBLK / 4);
+  r.gz1 = r.z1 + ntiles * ((long long)tc::PLANE / 4);
+  return r;
+}
+
+static int tcw_aux_attrs() {
+  static bool attr = false;
+  if (attr) return 0;
+  int rc = tcw_attr(tcw::l0_fwd_kernel<1>, tcw::FwdMap<1>::ALLOC, "l0_fwd<1>");
+  if (!rc) rc = tcw_attr(tcw::l0_fwd_kernel<2>, tcw::FwdMap<2>::ALLOC, "l0_fwd<2>");
+  if (!rc) rc = tcw_attr(tcw::l0_fwd_kernel<3>, tcw::FwdMap<3>::ALLOC, "l0_fwd<3>");
+  if (!rc) rc = tcw_attr(tcw::l0_fwd_kernel<4>, tcw::FwdMap<4>::ALLOC, "l0_fwd<4>");
+  if (!rc) rc = tcw_attr(tcw::l0_grad_kernel<1>, tcw::GradMap<1>::ALLOC, "l0_grad<1>");
+  if (!rc) rc = tcw_attr(tcw::l0_grad_kernel<2>, tcw::GradMap<2>::ALLOC, "l0_grad<2>");
+  if (!rc) rc = tcw_attr(tcw::l0_grad_kernel<3>, tcw::GradMap<3>::ALLOC, "l0_grad<3>");
+  if (!rc) rc = tcw_attr(tcw::l0_grad_kernel<4>, tcw::GradMap<4>::ALLOC, "l0_grad<4>");
+  if (!rc) attr = true;
+  return rc;
+}
+
+// z1 image = [x~ 1] [W0 | b0]^T with W0, b0 the first-layer rows of the flat vector `weights` (the CG direction for a
+// product, the parameters for a forward pass)
+int launch_tcw_l0_fwd(mjrl_ctx* ctx, const TcwRegions& r, const float* weights, long long N, int n, int m, int grid,
+                      const int32_t* stop_flag, cudaStream_t s) {
+  int rc = tcw_aux_attrs();
+  if (rc) return rc;
+  tcw::AuxArgs x = {};
+  x.ximg = r.ximg; x.vec = weights; x.dz1 = r.z1; x.stop_flag = stop_flag; x.N = N; x.n = n; x.m = m; x.KB = r.KB;
+  switch (r.KB) {
+    case 1: tcw::l0_fwd_kernel<1><<<grid, tcw::AUX_THREADS, tcw::FwdMap<1>::ALLOC, s>>>(x); break;
+    case 2: tcw::l0_fwd_kernel<2><<<grid, tcw::AUX_THREADS, tcw::FwdMap<2>::ALLOC, s>>>(x); break;
+    case 3: tcw::l0_fwd_kernel<3><<<grid, tcw::AUX_THREADS, tcw::FwdMap<3>::ALLOC, s>>>(x); break;
+    default: tcw::l0_fwd_kernel<4><<<grid, tcw::AUX_THREADS, tcw::FwdMap<4>::ALLOC, s>>>(x); break;
+  }
+  return mjrl_check_launch("l0_fwd_kernel");
+}
+
+// W0 / b0 slices of partials[grid][dstride] = gz1^T [x~ 1] from the GZ1 image
+int launch_tcw_l0_grad(mjrl_ctx* ctx, const TcwRegions& r, float* partials, int dstride, long long N, int n, int m,
+                       int grid, const int32_t* stop_flag, cudaStream_t s) {
+  int rc = tcw_aux_attrs();
+  if (rc) return rc;
+  tcw::AuxArgs x = {};
+  x.ximg = r.ximg; x.gz1 = r.gz1; x.partials = partials; x.stop_flag = stop_flag;
+  x.N = N; x.n = n; x.m = m; x.dstride = dstride; x.KB = r.KB;
+  switch (r.KB) {
+    case 1: tcw::l0_grad_kernel<1><<<grid, tcw::AUX_THREADS, tcw::GradMap<1>::ALLOC, s>>>(x); break;
+    case 2: tcw::l0_grad_kernel<2><<<grid, tcw::AUX_THREADS, tcw::GradMap<2>::ALLOC, s>>>(x); break;
+    case 3: tcw::l0_grad_kernel<3><<<grid, tcw::AUX_THREADS, tcw::GradMap<3>::ALLOC, s>>>(x); break;
+    default: tcw::l0_grad_kernel<4><<<grid, tcw::AUX_THREADS, tcw::GradMap<4>::ALLOC, s>>>(x); break;
+  }
+  return mjrl_check_launch("l0_grad_kernel");
+}
+
 int launch_fvp_tcw(mjrl_ctx* ctx, Args& a, float* cache, int* grid_out, cudaStream_t s) {
   if (!cache || !tcw_fits(ctx, a.n, a.m, a.h1, a.h2)) return -1;
   const Flat F(a.n, a.m, a.h1, a.h2);
@@ -933,51 +985,22 @@ int launch_fvp_tcw(mjrl_ctx* ctx, Args& a, float* cache, int* grid_out, cudaStre
     int rc = tcw_attr(tcw::fvp_wide_kernel<8>, tcw::WideMap<8>::ALLOC, "fvp_wide<8>");
     if (!rc) rc = tcw_attr(tcw::fvp_wide_kernel<16>, tcw::WideMap<16>::ALLOC, "fvp_wide<16>");
     if (!rc) rc = tcw_attr(tcw::fvp_wide_kernel<24>, tcw::WideMap<24>::ALLOC, "fvp_wide<24>");
-    if (!rc) rc = tcw_attr(tcw::l0_fwd_kernel<1>, tcw::FwdMap<1>::ALLOC, "l0_fwd<1>");
-    if (!rc) rc = tcw_attr(tcw::l0_fwd_kernel<2>, tcw::FwdMap<2>::ALLOC, "l0_fwd<2>");
-    if (!rc) rc = tcw_attr(tcw::l0_fwd_kernel<3>, tcw::FwdMap<3>::ALLOC, "l0_fwd<3>");
-    if (!rc) rc = tcw_attr(tcw::l0_fwd_kernel<4>, tcw::FwdMap<4>::ALLOC, "l0_fwd<4>");
-    if (!rc) rc = tcw_attr(tcw::l0_grad_kernel<1>, tcw::GradMap<1>::ALLOC, "l0_grad<1>");
-    if (!rc) rc = tcw_attr(tcw::l0_grad_kernel<2>, tcw::GradMap<2>::ALLOC, "l0_grad<2>");
-    if (!rc) rc = tcw_attr(tcw::l0_grad_kernel<3>, tcw::GradMap<3>::ALLOC, "l0_grad<3>");
-    if (!rc) rc = tcw_attr(tcw::l0_grad_kernel<4>, tcw::GradMap<4>::ALLOC, "l0_grad<4>");
     if (rc) return rc;
     attr = true;
   }
-  const int KB = tcw_kb(a.n);
-  float* h12 = cache;
-  float* ximg = h12 + ntiles * (2 * (long long)tc::PLANE / 4);
-  float* dz1 = ximg + ntiles * (long long)KB * (tcw::XBLK / 4);
-  float* gz1 = dz1 + ntiles * ((long long)tc::PLANE / 4);
-
-  tcw::AuxArgs x = {};
-  x.ximg = ximg; x.vec = a.vec; x.dz1 = dz1; x.gz1 = gz1; x.partials = a.partials; x.stop_flag = a.stop_flag;
-  x.N = a.N; x.n = a.n; x.m = a.m; x.dstride = a.dstride; x.KB = KB;
-  switch (KB) {
-    case 1: tcw::l0_fwd_kernel<1><<<grid, tcw::AUX_THREADS, tcw::FwdMap<1>::ALLOC, s>>>(x); break;
-    case 2: tcw::l0_fwd_kernel<2><<<grid, tcw::AUX_THREADS, tcw::FwdMap<2>::ALLOC, s>>>(x); break;
-    case 3: tcw::l0_fwd_kernel<3><<<grid, tcw::AUX_THREADS, tcw::FwdMap<3>::ALLOC, s>>>(x); break;
-    default: tcw::l0_fwd_kernel<4><<<grid, tcw::AUX_THREADS, tcw::FwdMap<4>::ALLOC, s>>>(x); break;
-  }
-  int rc = mjrl_check_launch("l0_fwd_kernel");
+  const TcwRegions r = tcw_regions(cache, a.n, a.N);
+  int rc = launch_tcw_l0_fwd(ctx, r, a.vec, a.N, a.n, a.m, grid, a.stop_flag, s);
   if (rc) return rc;
 
   tcw::WideArgs w = {};
-  w.params = a.params; w.vec = a.vec; w.cache = h12; w.dz1 = dz1; w.gz1 = gz1; w.out_scale = a.out_scale;
+  w.params = a.params; w.vec = a.vec; w.cache = r.h12; w.dz1 = r.z1; w.gz1 = r.gz1; w.out_scale = a.out_scale;
   w.partials = a.partials; w.stop_flag = a.stop_flag; w.N = a.N; w.n = a.n; w.m = a.m; w.dstride = a.dstride;
   if (a.m <= 8) tcw::fvp_wide_kernel<8><<<grid, tcw::NTHREADS, tcw::WideMap<8>::ALLOC, s>>>(w);
   else if (a.m <= 16) tcw::fvp_wide_kernel<16><<<grid, tcw::NTHREADS, tcw::WideMap<16>::ALLOC, s>>>(w);
   else tcw::fvp_wide_kernel<24><<<grid, tcw::NTHREADS, tcw::WideMap<24>::ALLOC, s>>>(w);
   rc = mjrl_check_launch("fvp_wide_kernel");
   if (rc) return rc;
-
-  switch (KB) {
-    case 1: tcw::l0_grad_kernel<1><<<grid, tcw::AUX_THREADS, tcw::GradMap<1>::ALLOC, s>>>(x); break;
-    case 2: tcw::l0_grad_kernel<2><<<grid, tcw::AUX_THREADS, tcw::GradMap<2>::ALLOC, s>>>(x); break;
-    case 3: tcw::l0_grad_kernel<3><<<grid, tcw::AUX_THREADS, tcw::GradMap<3>::ALLOC, s>>>(x); break;
-    default: tcw::l0_grad_kernel<4><<<grid, tcw::AUX_THREADS, tcw::GradMap<4>::ALLOC, s>>>(x); break;
-  }
-  return mjrl_check_launch("l0_grad_kernel");
+  return launch_tcw_l0_grad(ctx, r, a.partials, a.dstride, a.N, a.n, a.m, grid, a.stop_flag, s);
 }
 
 }  // namespace pol

@@ -1384,6 +1384,34 @@ int mjrl_policy_eval(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* p
   return mjrl_check_launch("policy_eval reduce");
 }
 
+int mjrl_policy_eval_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
+                        const float* obs, const float* act, const float* w, const float* old_ll,
+                        const float* old_mean, const float* old_log_std, int64_t N, double* sums2,
+                        float* fvp_cache, void* stream) {
+  int rc = check_desc(desc, "policy_eval_tc");
+  if (rc) return rc;
+  MJRL_REQUIRE(ctx && params && obs && act && old_ll && old_mean && old_log_std && sums2 && N > 0,
+               MJRL_E_ARG, "policy_eval_tc: bad argument");
+  const int kind = mjrl_policy_fvp_tc_ok(ctx, desc);
+  MJRL_REQUIRE(kind == 1 || (kind == 2 && fvp_cache), MJRL_E_SHAPE,
+               "policy_eval_tc: this policy shape has no tcgen05 pass (or the wide form was given no cache)");
+  Args a = {};
+  fill_desc(a, desc);
+  a.params = params; a.obs = obs; a.act = act; a.w = w; a.old_ll = old_ll; a.old_mean = old_mean;
+  a.old_log_std = old_log_std; a.N = N;
+  int grid;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (kind == 2) {
+    const TcwRegions r = tcw_regions(fvp_cache, desc->n, N);
+    rc = launch_pol_tc<M_EVAL>(ctx, a, nullptr, &r, &grid, s);
+  } else {
+    rc = launch_pol_tc<M_EVAL>(ctx, a, nullptr, nullptr, &grid, s);
+  }
+  if (rc) return rc;
+  reduce_scalars_kernel<<<1, 32, 0, s>>>(a.spartials, grid, sums2, 3, nullptr);
+  return mjrl_check_launch("policy_eval_tc reduce");
+}
+
 int mjrl_policy_grad(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
                      const float* obs, const float* act, const float* w, const float* old_ll,
                      int64_t N, double* grad_sum, double* surr_sum, float* ll_out, float* mean_out,
@@ -1418,6 +1446,12 @@ int mjrl_policy_grad_cached(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const f
 
 static int64_t tc_region_offset(mjrl_ctx* ctx, const mjrl_policy_desc* desc, int64_t N);
 
+// gradient / evaluation passes on tcgen05 (pol_tc.cu) unless MJRL_B200_GRAD_TC=0 (then the mma.sync kernels fill the planes)
+static bool grad_on_tc() {
+  static const bool off = getenv("MJRL_B200_GRAD_TC") && getenv("MJRL_B200_GRAD_TC")[0] == '0';
+  return !off;
+}
+
 int mjrl_policy_grad_cached_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* params,
                                const float* obs, const float* act, const float* w, const float* old_ll,
                                int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
@@ -1447,7 +1481,13 @@ int mjrl_policy_grad_cached_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, cons
     rc = launch_tcw_ximg(ctx, a, fvp_cache, s);
     if (rc) return rc;
     int grid;
-    rc = launch_mode<M_GRAD>(ctx, a, &grid, s);
+    if (grad_on_tc()) {
+      const TcwRegions r = tcw_regions(fvp_cache, desc->n, N);
+      a.cache = nullptr; a.cache_mode = 0;
+      rc = launch_pol_tc<M_GRAD>(ctx, a, r.h12, &r, &grid, s);
+    } else {
+      rc = launch_mode<M_GRAD>(ctx, a, &grid, s);
+    }
     if (rc) return rc;
     const Flat F(desc->n, desc->m, desc->h1, desc->h2);
     reduce_partials_kernel<<<(F.d + 31) / 32, 256, 0, s>>>(a.partials, grid, a.dstride, F.d, grad_sum,
@@ -1470,10 +1510,14 @@ int mjrl_policy_grad_cached_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, cons
   fill_desc(a, desc);
   a.params = params; a.obs = obs; a.act = act; a.w = w; a.old_ll = old_ll; a.N = N;
   a.ll_out = ll_out; a.mean_out = mean_out;
-  a.cache = fvp_cache + off; a.cache_mode = 5;
   int grid;
-  rc = launch_pol_rows<M_GRAD>(ctx, a, &grid, s);
-  MJRL_REQUIRE(rc >= 0, MJRL_E_SHAPE, "policy_grad_cached_tc: rows kernel does not take this shape");
+  if (grad_on_tc()) {
+    rc = launch_pol_tc<M_GRAD>(ctx, a, fvp_cache + off, nullptr, &grid, s);     // pol_tc.cu: fills the planes itself
+  } else {
+    a.cache = fvp_cache + off; a.cache_mode = 5;
+    rc = launch_pol_rows<M_GRAD>(ctx, a, &grid, s);
+    MJRL_REQUIRE(rc >= 0, MJRL_E_SHAPE, "policy_grad_cached_tc: rows kernel does not take this shape");
+  }
   if (rc) return rc;
   const Flat F(desc->n, desc->m, desc->h1, desc->h2);
   reduce_partials_kernel<<<(F.d + 31) / 32, 256, 0, s>>>(a.partials, grid, a.dstride, F.d, grad_sum,

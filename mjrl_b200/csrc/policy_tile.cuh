@@ -359,5 +359,15 @@ bool tcw_fits(const mjrl_ctx* ctx, int n, int m, int h1, int h2);
 long long tcw_cache_floats(int n, long long N);
 int launch_tcw_ximg(mjrl_ctx* ctx, const Args& a, float* cache, cudaStream_t s);
 int launch_fvp_tcw(mjrl_ctx* ctx, Args& a, float* cache, int* grid_out, cudaStream_t s);
+struct TcwRegions { float *h12, *ximg, *z1, *gz1; int KB; };   // regions of the wide cache buffer
+TcwRegions tcw_regions(float* cache, int n, long long N);
+int launch_tcw_l0_fwd(mjrl_ctx* ctx, const TcwRegions& r, const float* weights, long long N, int n, int m, int grid,
+                      const int32_t* stop_flag, cudaStream_t s);
+int launch_tcw_l0_grad(mjrl_ctx* ctx, const TcwRegions& r, float* partials, int dstride, long long N, int n, int m,
+                       int grid, const int32_t* stop_flag, cudaStream_t s);
+// gradient / surrogate+KL passes on tcgen05 (pol_tc.cu); `planes` = tile-ordered h1 | h2 region the gradient pass
+// fills (null for an evaluation), `wide` = the regions of the three-pass form or null for the fused narrow form
+template <int MODE>
+int launch_pol_tc(mjrl_ctx* ctx, Args& a, float* planes, const TcwRegions* wide, int* grid_out, cudaStream_t s);
 
 }  // namespace pol
