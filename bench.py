@@ -263,6 +263,37 @@ def parity_at_sample_size(c, device):
     return out
 
 
+def exchange_profile(agent, epoch0, steps):
+    """Per-exchange timing of the peer-memory kernels (csrc/peer.cu) over the timed region, from the %globaltimer
+    stamps each exchange kernel records on this rank (MJRL_B200_PEER_STAMPS=1): wait = entry -> every peer's flag seen
+    (what a rank spends waiting for the slowest peer), pull = flags seen -> sums pulled over NVLink, rest = the fused
+    CG arithmetic.  None when the exchange runs over NCCL."""
+    import ctypes
+    import numpy as np
+    from mjrl_b200 import _lib
+    pe = agent._engine().dist.peer
+    if pe is None:
+        return None
+    n = min(pe.epoch - epoch0, 4096)
+    if n <= 0:
+        return None
+    buf = (ctypes.c_uint64 * (4 * n))()
+    rc = _lib.load().mjrl_peer_stamps(pe.h, buf, ctypes.c_int64(pe.epoch - n + 1), ctypes.c_int64(n))
+    if rc != 0:
+        return None
+    a = np.frombuffer(buf, dtype=np.uint64).reshape(n, 4).astype(np.int64)
+    a = a[(a > 0).all(axis=1)]
+    if len(a) == 0:
+        return None
+    wait, pull, rest, tot = (a[:, 1] - a[:, 0]) / 1e3, (a[:, 2] - a[:, 1]) / 1e3, (a[:, 3] - a[:, 2]) / 1e3, (a[:, 3] - a[:, 0]) / 1e3
+    q = lambda v: {"median_us": float(np.median(v)), "mean_us": float(np.mean(v)), "p90_us": float(np.percentile(v, 90))}
+    per_update = len(a) / max(1, steps)
+    return {"exchanges_per_update": per_update, "wait_for_peers": q(wait), "pull_over_nvlink": q(pull), "fused_arithmetic": q(rest),
+            "kernel_total": q(tot), "ms_per_update_in_exchange_kernels": float(np.sum(tot)) / 1e3 / max(1, steps),
+            "ms_per_update_waiting": float(np.sum(wait)) / 1e3 / max(1, steps),
+            "source": "%globaltimer stamps inside the exchange kernels of rank 0 over the timed region (mjrl_peer_stamps)"}
+
+
 def rank_invariance(dev, world, rank):
     """Multi-GPU correctness on the bench line itself (the 1-GPU test box skips the torchrun tests): the same small
     batch updated (a) sharded by whole paths over all ranks and (b) on one GPU with no exchange; every rank computes
@@ -359,6 +390,8 @@ def run_b200(args):
     import torch.distributed as td
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        os.environ.setdefault("MJRL_B200_PEER_STAMPS", "1")    # exchange kernels stamp %globaltimer (exchange_profile below)
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -465,6 +498,8 @@ def run_b200(args):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
           for _ in range(args.steps)]
     l0 = ctx.launches
+    _pe = agent._engine().dist.peer if world > 1 else None
+    e0_peer = _pe.epoch if _pe is not None else 0
     barrier()
     for k in range(args.steps):
         reset()
@@ -480,6 +515,7 @@ def run_b200(args):
     barrier()
     launches = ctx.launches - l0
     clk = clocks.stop()
+    xprof = exchange_profile(agent, e0_peer, args.steps) if world > 1 else None
     ms = sum(a.elapsed_time(b) for a, b in ev)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -734,6 +770,7 @@ def run_b200(args):
             **({"value_configs2": configs2.get("value"), "configs2": configs2} if configs2 else {}),
             **({"strong_scaling": strong} if strong else {}),
             **({"rank_invariance": rinv} if rinv else {}),
+            **({"exchange_profile": xprof} if xprof else {}),
             **({"parity": parity} if parity else {}),
             "cpu_baseline": cb, "mlp_baseline": mlp_extra}))
     if world > 1:

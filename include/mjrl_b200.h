@@ -394,6 +394,11 @@ int mjrl_cg_solve(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float* para
                   int32_t jac_fill_after_first, mjrl_peer* peer, int64_t epoch0, void* stream);
 /* synchronous: *err_out = 1 when some wait timed out since creation */
 int mjrl_peer_status(mjrl_peer* peer, int32_t* err_out);
+/* Measurement aid, no reference counterpart: with MJRL_B200_PEER_STAMPS=1 in the environment when the block is created, every
+ * exchange kernel records four %globaltimer values (ns) for its epoch: 0 kernel entry, 1 every peer's flag seen, 2 sums pulled
+ * over NVLink (+ the first dot product in the fused CG variant), 3 kernel end.  Copies the stamps of epochs first_epoch ..
+ * first_epoch + count - 1 (count <= 4096, ring) to the host array out[count][4].  bench.py prints their medians at N > 1. */
+int mjrl_peer_stamps(mjrl_peer* peer, uint64_t* out, int64_t first_epoch, int64_t count);
 int mjrl_peer_destroy(mjrl_peer* peer);
 
 #ifdef __cplusplus

@@ -15,6 +15,7 @@
 //   5. (fused variant) the CG update of cg_solve.py:10-20 runs on those sums in the same kernel.
 // Slot e&1 is rewritten at epoch e+2, which a rank reaches only after every peer raised e+1, i.e. after every
 // peer finished reading epoch e: two slots suffice and flags never need resetting (monotonic epochs).
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -33,7 +34,14 @@ struct View {
   long long max_count;
   int* err;                           // local: 1 = a wait timed out
   unsigned long long timeout_ns;
+  unsigned long long* stamps;         // measurement aid (MJRL_B200_PEER_STAMPS=1), else null: [STAMP_EPOCHS][4] globaltimer ns
 };
+constexpr int STAMP_EPOCHS = 4096;
+__device__ __forceinline__ unsigned long long now_ns();
+// stamp i of this epoch's exchange kernel: 0 entry, 1 every peer's flag seen, 2 sums pulled (+ first dot product), 3 end
+__device__ __forceinline__ void stamp(const View& pv, unsigned long long epoch, int i) {
+  if (pv.stamps != nullptr && threadIdx.x == 0) pv.stamps[(epoch % STAMP_EPOCHS) * 4 + i] = now_ns();
+}
 
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
@@ -57,6 +65,7 @@ __device__ __forceinline__ unsigned long long now_ns() {
 // steps 2-3; all threads of the CTA call it.  On return every peer's slot (epoch & 1) holds its
 // contribution of this epoch (or *err is set).
 __device__ __forceinline__ void handshake(const View& pv, unsigned long long epoch) {
+  stamp(pv, epoch, 0);
   __threadfence_system();
   __syncthreads();
   const int t = threadIdx.x;
@@ -71,6 +80,7 @@ __device__ __forceinline__ void handshake(const View& pv, unsigned long long epo
   }
   __syncthreads();
   __threadfence_system();
+  stamp(pv, epoch, 1);
 }
 
 __device__ __forceinline__ double sum_ranks(const View& pv, long long off) {
@@ -85,6 +95,36 @@ __device__ __forceinline__ double sum_ranks(const View& pv, long long off) {
   return s;
 }
 
+// Pull with every load in flight at once.  A thread that sums W peer values per element in registers stalls on the first
+// use, one NVLink round trip (~2 us) per element it owns: 13 us for d = 5,126 on 2 GPUs (measured, mjrl_peer_stamps).
+// Instead the slots are staged in shared memory by 16-byte cp.async.cg (no registers, bypasses L1, so no stale line
+// of an earlier epoch can be read; peer memory is not cached in the local L2): all copies of a chunk are issued
+// before the first wait, then the sums are formed from shared memory in RANK ORDER as before.
+constexpr long long BUF_ELEMS = 24576;           // 192 KB: [world][chunk] doubles
+__device__ __forceinline__ long long stage_chunk_elems(int world) { return (BUF_ELEMS / world) & ~1023LL; }
+// stage elements [e0, e0 + ce) of every rank's slot; returns after a CTA barrier (data visible to all threads)
+__device__ __forceinline__ void stage_chunk(const View& pv, long long so, long long e0, long long ce, long long chunk,
+                                            double* sbuf) {
+  const long long c2 = (ce + 1) >> 1;            // 16-byte pieces per rank (may read one double past ce: slack exists)
+  const long long total = (long long)pv.world * c2;
+  for (long long c = threadIdx.x; c < total; c += THREADS) {
+    const int r = (int)(c / c2);
+    const long long j = c - (long long)r * c2;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                 :: "r"((uint32_t)__cvta_generic_to_shared(sbuf + r * chunk + 2 * j)), "l"(pv.data[r] + so + e0 + 2 * j) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+}
+__device__ __forceinline__ double staged_sum(const View& pv, const double* sbuf, long long chunk, long long j) {
+  double s = 0.0;
+#pragma unroll
+  for (int r = 0; r < MAXW; ++r)
+    if (r < pv.world) s += sbuf[r * chunk + j];
+  return s;
+}
+
 // dst[i] = sum_r slot_r[i]; src (may be NULL = already in the local slot) is copied into the slot first
 __global__ void __launch_bounds__(THREADS)
 allreduce_kernel(View pv, const double* __restrict__ src, double* __restrict__ dst, long long count,
@@ -94,7 +134,16 @@ allreduce_kernel(View pv, const double* __restrict__ src, double* __restrict__ d
   if (src != nullptr && src != mine)
     for (long long i = threadIdx.x; i < count; i += THREADS) mine[i] = src[i];
   handshake(pv, epoch);
-  for (long long i = threadIdx.x; i < count; i += THREADS) dst[i] = sum_ranks(pv, so + i);
+  extern __shared__ __align__(16) double sbuf[];
+  const long long chunk = stage_chunk_elems(pv.world);
+  for (long long e0 = 0; e0 < count; e0 += chunk) {
+    const long long ce = count - e0 < chunk ? count - e0 : chunk;
+    stage_chunk(pv, so, e0, ce, chunk, sbuf);
+    for (long long j = threadIdx.x; j < ce; j += THREADS) dst[e0 + j] = staged_sum(pv, sbuf, chunk, j);
+    __syncthreads();
+  }
+  stamp(pv, epoch, 2);
+  stamp(pv, epoch, 3);
 }
 
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -126,12 +175,26 @@ cg_update_kernel(View pv, mjrl_cg_state st, long long d, double inv_count, doubl
   const double rdotr = st.scal[0];
   double pz = 0.0;
   double rp[REGS ? CG_E : 1], rz[REGS ? CG_E : 1], rx[REGS ? CG_E : 1], rr[REGS ? CG_E : 1];
+  extern __shared__ __align__(16) double sbuf[];
+  const long long chunk = stage_chunk_elems(pv.world);     // a multiple of THREADS: element i = tid + k THREADS keeps its k
   if (REGS) {
+#pragma unroll
+    for (int k = 0; k < CG_E; ++k) rz[k] = 0.0;
+    for (long long e0 = 0; e0 < d; e0 += chunk) {
+      const long long ce = d - e0 < chunk ? d - e0 : chunk;
+      stage_chunk(pv, so, e0, ce, chunk, sbuf);
+#pragma unroll
+      for (int k = 0; k < CG_E; ++k) {
+        const long long j = threadIdx.x + (long long)k * THREADS - e0;
+        if (j >= 0 && j < ce) rz[k] = staged_sum(pv, sbuf, chunk, j);
+      }
+      __syncthreads();
+    }
 #pragma unroll
     for (int k = 0; k < CG_E; ++k) {
       const long long i = threadIdx.x + (long long)k * THREADS;
       const bool in = i < d;
-      rp[k] = in ? st.p[i] : 0.0; rz[k] = in ? sum_ranks(pv, so + i) : 0.0;
+      rp[k] = in ? st.p[i] : 0.0;
       rx[k] = in ? st.x[i] : 0.0; rr[k] = in ? st.r[i] : 0.0;
     }
 #pragma unroll
@@ -140,14 +203,21 @@ cg_update_kernel(View pv, mjrl_cg_state st, long long d, double inv_count, doubl
       pz = fma(rp[k], rz[k], pz);
     }
   } else {
-    for (long long i = threadIdx.x; i < d; i += THREADS) {
-      const double p = st.p[i];
-      const double z = fma(sum_ranks(pv, so + i), inv_count, damping * p);
-      st.z[i] = z;
-      pz = fma(p, z, pz);
+    for (long long e0 = 0; e0 < d; e0 += chunk) {
+      const long long ce = d - e0 < chunk ? d - e0 : chunk;
+      stage_chunk(pv, so, e0, ce, chunk, sbuf);
+      for (long long j = threadIdx.x; j < ce; j += THREADS) {
+        const long long i = e0 + j;
+        const double p = st.p[i];
+        const double z = fma(staged_sum(pv, sbuf, chunk, j), inv_count, damping * p);
+        st.z[i] = z;
+        pz = fma(p, z, pz);
+      }
+      __syncthreads();
     }
   }
   pz = cta_sum_bcast(pz, red);
+  stamp(pv, epoch, 2);
   const double v = rdotr / pz;
   double nrr = 0.0;
   if (REGS) {
@@ -188,6 +258,7 @@ cg_update_kernel(View pv, mjrl_cg_state st, long long d, double inv_count, doubl
     st.flags[1] += 1;
     if (nrr < tol) st.flags[0] = 1;
   }
+  stamp(pv, epoch, 3);
 }
 
 }  // namespace peer
@@ -201,6 +272,7 @@ struct mjrl_peer {
   bool connected;
   int* err;
   unsigned long long timeout_ns;
+  unsigned long long* stamps;          // device [STAMP_EPOCHS][4] when MJRL_B200_PEER_STAMPS=1 at creation
   peer::View view;
 };
 
@@ -213,6 +285,20 @@ static void fill_view(mjrl_peer* p) {
   }
   v.rank = p->rank; v.world = p->world; v.max_count = p->max_count; v.err = p->err;
   v.timeout_ns = p->timeout_ns;
+  v.stamps = p->stamps;
+}
+
+// the exchange kernels stage the slots in 192 KB of dynamic shared memory
+static int peer_kernel_attrs() {
+  static bool done = false;
+  if (done) return 0;
+  const int bytes = (int)(peer::BUF_ELEMS * sizeof(double));
+  cudaError_t e = cudaFuncSetAttribute(peer::allreduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(peer::cg_update_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(peer::cg_update_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) { mjrl_set_error("cudaFuncSetAttribute(peer kernels): %s", cudaGetErrorString(e)); return (int)e; }
+  done = true;
+  return 0;
 }
 
 extern "C" {
@@ -224,13 +310,18 @@ int mjrl_peer_create(mjrl_ctx* ctx, int32_t rank, int32_t world, int64_t max_cou
   cudaSetDevice(ctx->device);
   mjrl_peer* p = new mjrl_peer();
   memset(p, 0, sizeof(*p));
+  max_count = (max_count + 1) & ~(int64_t)1;      // 16-byte aligned second slot (the exchange kernels copy 16-byte pieces)
   p->device = ctx->device; p->rank = rank; p->world = world; p->max_count = max_count;
   p->timeout_ns = 20ull * 1000ull * 1000ull * 1000ull;
-  const size_t bytes = peer::FLAG_BYTES + 2 * (size_t)max_count * sizeof(double);
+  const size_t bytes = peer::FLAG_BYTES + 2 * (size_t)max_count * sizeof(double) + 16;   // + slack for the last 16-byte piece
   cudaError_t e = cudaMalloc(&p->base, bytes);
   if (e == cudaSuccess) e = cudaMemset(p->base, 0, bytes);
   if (e == cudaSuccess) e = cudaMalloc((void**)&p->err, sizeof(int));
   if (e == cudaSuccess) e = cudaMemset(p->err, 0, sizeof(int));
+  if (e == cudaSuccess && getenv("MJRL_B200_PEER_STAMPS") && getenv("MJRL_B200_PEER_STAMPS")[0] == '1') {
+    e = cudaMalloc((void**)&p->stamps, sizeof(unsigned long long) * 4 * peer::STAMP_EPOCHS);
+    if (e == cudaSuccess) e = cudaMemset(p->stamps, 0, sizeof(unsigned long long) * 4 * peer::STAMP_EPOCHS);
+  }
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e == cudaSuccess && handle_out) {
     cudaIpcMemHandle_t h;
@@ -300,8 +391,10 @@ int mjrl_peer_allreduce_f64(mjrl_ctx* ctx, mjrl_peer* p, const double* src, doub
   MJRL_REQUIRE(ctx && p && dst && p->connected && epoch >= 1, MJRL_E_ARG, "peer_allreduce: bad argument");
   MJRL_REQUIRE(count > 0 && count <= p->max_count, MJRL_E_SHAPE, "peer_allreduce: count %lld exceeds the block (%lld)",
                (long long)count, p->max_count);
-  peer::allreduce_kernel<<<1, peer::THREADS, 0, (cudaStream_t)stream>>>(p->view, src, dst, count,
-                                                                         (unsigned long long)epoch);
+  int rc = peer_kernel_attrs();
+  if (rc) return rc;
+  peer::allreduce_kernel<<<1, peer::THREADS, peer::BUF_ELEMS * sizeof(double), (cudaStream_t)stream>>>(
+      p->view, src, dst, count, (unsigned long long)epoch);
   return mjrl_check_launch("peer allreduce");
 }
 
@@ -309,11 +402,14 @@ int mjrl_cg_update_peer(mjrl_ctx* ctx, mjrl_peer* p, const mjrl_cg_state* st, in
                         double damping, double residual_tol, int64_t epoch, void* stream) {
   MJRL_REQUIRE(ctx && p && st && p->connected && epoch >= 1, MJRL_E_ARG, "cg_update_peer: bad argument");
   MJRL_REQUIRE(d > 0 && d <= p->max_count, MJRL_E_SHAPE, "cg_update_peer: d exceeds the block");
+  int rc = peer_kernel_attrs();
+  if (rc) return rc;
+  const size_t smem = peer::BUF_ELEMS * sizeof(double);
   if (d <= (int64_t)peer::CG_E * peer::THREADS)
-    peer::cg_update_kernel<true><<<1, peer::THREADS, 0, (cudaStream_t)stream>>>(
+    peer::cg_update_kernel<true><<<1, peer::THREADS, smem, (cudaStream_t)stream>>>(
         p->view, *st, d, inv_count, damping, residual_tol, (unsigned long long)epoch);
   else
-    peer::cg_update_kernel<false><<<1, peer::THREADS, 0, (cudaStream_t)stream>>>(
+    peer::cg_update_kernel<false><<<1, peer::THREADS, smem, (cudaStream_t)stream>>>(
         p->view, *st, d, inv_count, damping, residual_tol, (unsigned long long)epoch);
   return mjrl_check_launch("cg_update_peer");
 }
@@ -359,6 +455,18 @@ int mjrl_peer_status(mjrl_peer* p, int32_t* err_out) {
   return 0;
 }
 
+int mjrl_peer_stamps(mjrl_peer* p, uint64_t* out, int64_t first_epoch, int64_t count) {
+  MJRL_REQUIRE(p && out && first_epoch >= 0 && count >= 0 && count <= peer::STAMP_EPOCHS, MJRL_E_ARG, "peer_stamps: bad argument");
+  MJRL_REQUIRE(p->stamps, MJRL_E_STATE, "peer_stamps: the block was created without MJRL_B200_PEER_STAMPS=1");
+  cudaSetDevice(p->device);
+  for (int64_t k = 0; k < count; ++k) {
+    const int64_t e = (first_epoch + k) % peer::STAMP_EPOCHS;
+    cudaError_t er = cudaMemcpy(out + 4 * k, p->stamps + 4 * e, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost);
+    if (er != cudaSuccess) { mjrl_set_error("peer_stamps: %s", cudaGetErrorString(er)); return (int)er; }
+  }
+  return 0;
+}
+
 int mjrl_peer_destroy(mjrl_peer* p) {
   if (!p) return 0;
   cudaSetDevice(p->device);
@@ -367,6 +475,7 @@ int mjrl_peer_destroy(mjrl_peer* p) {
     if (p->opened[r]) cudaIpcCloseMemHandle(p->bases[r]);
   if (p->base) cudaFree(p->base);
   if (p->err) cudaFree(p->err);
+  if (p->stamps) cudaFree(p->stamps);
   delete p;
   return 0;
 }
