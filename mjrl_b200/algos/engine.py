@@ -187,7 +187,9 @@ class UpdateEngine:
         tgt = self.grad if not accumulate else torch.empty_like(self.grad)
         ll_out, mean_out = cache if cache is not None else (None, None)
         # the pass computes h1, h2 of (params, obs) anyway: leave them for the FVPs of the CG solve
-        fcache = self._fvp_cache(N)
+        # (not for an accumulated second term -- DAPG's demonstration batch, dapg.py:93-98: the CG solve runs on the
+        # sampled batch, whose planes the first call left in the cache)
+        fcache = self._fvp_cache(N) if not accumulate else None
         direct_tc = fcache is not None and self._tc_kind() > 0 and N >= TC_MIN_N
         # hidden 64 x 64 at a batch the tensor-memory product takes: h1, h2 go straight into its tile order
         self.ctx.call("mjrl_policy_grad_cached_tc" if direct_tc else "mjrl_policy_grad_cached",
@@ -195,11 +197,12 @@ class UpdateEngine:
                       ptr(old_ll), c_i64(N), ptr(tgt), c_void_p(tgt.data_ptr() + 8 * d),
                       ptr(ll_out), ptr(mean_out), ptr(fcache), stream_ptr())
         # the pass refilled h1|h2 for these tensors; Jacobian rows of any earlier policy / batch are stale
-        key = self._hold(params, obs) if fcache is not None else None
-        self._cache_key = None if direct_tc else key     # fragment-ordered h1|h2 (modes 2, 3)
-        self._tc_key = key if direct_tc else None        # tile-ordered copy (mode 4)
-        self._ximg_key = self._key(obs, obs) if direct_tc and self._tc_kind() == 2 else None   # [x~ | 1] image (wide shapes)
-        self._jac_key = None
+        if not accumulate:
+            key = self._hold(params, obs) if fcache is not None else None
+            self._cache_key = None if direct_tc else key     # fragment-ordered h1|h2 (modes 2, 3)
+            self._tc_key = key if direct_tc else None        # tile-ordered copy (mode 4)
+            self._ximg_key = self._key(obs, obs) if direct_tc and self._tc_kind() == 2 else None   # [x~ | 1] image (wide shapes)
+            self._jac_key = None
         self.launches += 3
         if accumulate:
             self.grad[:d] += tgt[:d]   # demo term: only the gradient, not the surrogate (dapg.py:93,98)

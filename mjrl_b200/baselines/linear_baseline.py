@@ -59,14 +59,14 @@ class LinearBaseline:
         if allreduce is not None:
             allreduce(gram)
         prev = self._coeffs_on(batch.device)
-        new = torch.empty(F, dtype=torch.float64, device=batch.device)
-        info = torch.empty(4, dtype=torch.float64, device=batch.device)
+        both = torch.empty(F + 4, dtype=torch.float64, device=batch.device)    # coefficients | solve info: one read-back
+        new, info = both[:F], both[F:]
         batch.ctx.call("mjrl_linbase_solve", ptr(gram), c_int(F), c_double(copy.deepcopy(self._reg_coeff)),
                        ptr(prev), ptr(new), ptr(info), stream_ptr())
         errs = None
         if sync or return_errors:
-            self._coeffs = _lib.to_host(new)
-            h = _lib.to_host(info)
+            hb = _lib.to_host(both)
+            self._coeffs, h = hb[:F].copy(), hb[F:]
             self.last_fit_info = dict(reg_coeff=h[0], retries=int(h[1]))
             if return_errors:
                 errs = (float(h[2]), float(h[3]))

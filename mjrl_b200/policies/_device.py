@@ -34,6 +34,13 @@ class PolicyOnDevice:
     def refresh_transforms(self):
         mdl = self.policy.model
         vals = [mdl.in_shift, mdl.in_scale, mdl.out_shift, mdl.out_scale]
+        # identity + in-place version of the four tensors first (no host work when nothing was touched: this runs before
+        # every C call that takes the policy description); their bytes only when one of them changed
+        ident = tuple((id(v), v._version) for v in vals)
+        if ident == getattr(self, "_tr_ident", None):
+            return self.desc
+        self._tr_ident = ident
+        self._tr_vals = vals          # keep the tensors alive: a freed one's id could be reused
         key = tuple(v.detach().numpy().tobytes() for v in vals)
         if key != self._tr_key:
             self._tr = [v.detach().float().contiguous().to(self.device) for v in vals]
@@ -46,6 +53,9 @@ class PolicyOnDevice:
         return ctypes.byref(self.refresh_transforms())
 
     def params(self, which="new"):
+        # start of an update / a public call: compare the transforms byte for byte once (catches a tensor edited through a
+        # numpy view, which bumps no version counter); the C calls that follow take the identity fast path
+        self._tr_ident = None
         p = self.policy
         flat = p.get_param_values() if which == "new" else p.get_old_param_values()
         return _f32_dev(flat, self.device)
