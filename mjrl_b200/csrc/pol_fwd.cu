@@ -15,8 +15,8 @@
 //   z2 = h1 W1^T               MMA-2
 //   h2 = tanh(z2 + b1); mu = (h2 W2^T + b2) out_scale + out_shift; LL; c = exp(LL - LL_old) advantage; KL
 //
-// WRITE mode is the forward half of the gradient pass (the backward half is fvp_tc*.cu in its BWD form): it also stores
-// h1 | h2 in the plane cache, u = c dLL/dmu per timestep, and sums c (z^2 - 1) for d log_std.
+// (A gradient pass split into this forward kernel + the product kernel's backward half was measured and is NOT faster than
+// the fused pol_tc_kernel<GRAD>: profiles/probes/r02_grad_split_negative_result.patch.)
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -39,8 +39,8 @@ struct Map {
   static constexpr int W2 = 0, B1 = MJT * H, B2 = B1 + H, SIG = B2 + MJT, LS = SIG + MJT, OS = LS + MJT, OSH = OS + MJT,
                        OLS = OSH + MJT, SOLD = OLS + MJT, ISHIFT = SOLD + MJT, IRCP = ISHIFT + KX;
   static constexpr uint32_t VEC_FLOATS = IRCP + KX;
-  static constexpr uint32_t OFF_RED = (OFF_VEC + 4 * VEC_FLOATS + 15) & ~15u;     // end-of-kernel sums: [256][2] doubles, [256][MJT] floats
-  static constexpr uint32_t OFF_BAR = OFF_RED + NROW_THREADS * 16 + NROW_THREADS * MJT * 4;
+  static constexpr uint32_t OFF_RED = (OFF_VEC + 4 * VEC_FLOATS + 15) & ~15u;     // end-of-kernel sums: [256][2] doubles
+  static constexpr uint32_t OFF_BAR = OFF_RED + NROW_THREADS * 16;
   static constexpr uint32_t BYTES = OFF_BAR + 8 * 8;
   static constexpr uint32_t ALLOC = BYTES + 1024;
 };
@@ -50,8 +50,6 @@ constexpr uint32_t T_SET = 256, T_X = 0, T_D = 32, T_A1 = 96;            // per 
 struct FwdArgs {
   Args a;
   const float* z1;        // wide: z1 image
-  float* planes;          // WRITE: tile-ordered h1 | h2 cache (96-timestep tiles, fvp_tc.cuh)
-  float* uimg;            // WRITE: [N][MJT] u = c dLL/dmu (out_scale folded in)
 };
 
 __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
@@ -61,7 +59,7 @@ __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 
-template <int MJT, bool WRITE, bool WIDE>
+template <int MJT, bool WIDE>
 __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) {
   using M = Map<MJT>;
   const Args& a = fa.a;
@@ -122,7 +120,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) 
       vecs[M::SIG + j] = expf(ls);
       vecs[M::OS + j] = (in && a.out_scale) ? __ldg(a.out_scale + j) : 1.f;
       vecs[M::OSH + j] = (in && a.out_shift) ? __ldg(a.out_shift + j) : 0.f;
-      const float ols = (!WRITE && in && a.old_log_std) ? __ldg(a.old_log_std + j) : 0.f;
+      const float ols = (in && a.old_log_std) ? __ldg(a.old_log_std + j) : 0.f;
       vecs[M::OLS + j] = ols;
       vecs[M::SOLD + j] = expf(ols);
     }
@@ -134,9 +132,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) 
   const uint32_t tb = tslot;
 
   double surr_acc = 0.0, kl_acc = 0.0;
-  float gls[WRITE ? MJT : 1];
-#pragma unroll
-  for (int j = 0; j < (WRITE ? MJT : 1); ++j) gls[j] = 0.f;
 
   if (warp < 8) {
     // ============ row threads: set = warp / 4, TMEM lane quadrant = warp % 4, one thread per timestep ==============
@@ -212,25 +207,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) 
         fence_before();
         mbar_arrive(&bar[B_E1 + set]);
       }
-      // ... while MMA-2 runs: the plane cache row (WRITE) and this row's scalars
-      const long long t96 = t / ROWS;
-      const int r96 = (int)(t - t96 * ROWS);
-      if (WRITE && fa.planes && t < (long long)((a.N + ROWS - 1) / ROWS) * ROWS) {
-        float* pl = fa.planes + (size_t)t96 * (2 * PLANE / 4);
-#pragma unroll
-        for (int qq = 0; qq < 8; ++qq) {
-          float4* p = reinterpret_cast<float4*>(pl + mn_atom(r96, qq) / 4);
-          p[0] = make_float4(h[8 * qq], h[8 * qq + 1], h[8 * qq + 2], h[8 * qq + 3]);
-          p[1] = make_float4(h[8 * qq + 4], h[8 * qq + 5], h[8 * qq + 6], h[8 * qq + 7]);
-        }
-      }
-      float av[MJT], om[WRITE ? 1 : MJT];
+      // ... while MMA-2 runs: this row's scalars
+      float av[MJT], om[MJT];
       float wv = 0.f, oll = 0.f;
       if (valid) {
 #pragma unroll
         for (int j = 0; j < MJT; ++j) {
           av[j] = j < m ? __ldg(a.act + t * m + j) : 0.f;
-          if constexpr (!WRITE) om[j] = j < m ? __ldg(a.old_mean + t * m + j) : 0.f;
+          om[j] = j < m ? __ldg(a.old_mean + t * m + j) : 0.f;
         }
         wv = a.w ? __ldg(a.w + t) : 0.f;
         oll = a.old_ll ? __ldg(a.old_ll + t) : 0.f;
@@ -248,17 +232,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) 
         for (int i = 0; i < 32; ++i) h[32 + i] = tanh_fast(__uint_as_float(d[i]) + vecs[M::B1 + 32 + i]);
       }
       fence_before();
-      if (WRITE && fa.planes && t < (long long)((a.N + ROWS - 1) / ROWS) * ROWS) {
-        float* pl = fa.planes + (size_t)t96 * (2 * PLANE / 4) + PLANE / 4;
-#pragma unroll
-        for (int qq = 0; qq < 8; ++qq) {
-          float4* p = reinterpret_cast<float4*>(pl + mn_atom(r96, qq) / 4);
-          p[0] = make_float4(h[8 * qq], h[8 * qq + 1], h[8 * qq + 2], h[8 * qq + 3]);
-          p[1] = make_float4(h[8 * qq + 4], h[8 * qq + 5], h[8 * qq + 6], h[8 * qq + 7]);
-        }
-      }
       float ss = 0.f, sum_ls = 0.f, kl = 0.f;
-      float zz[WRITE ? MJT : 1];
 #pragma unroll
       for (int j = 0; j < MJT; ++j) {
         const float4* w2 = reinterpret_cast<const float4*>(vecs + M::W2 + j * H);
@@ -277,16 +251,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) 
           const float z = (av[j] - mu) / sg;
           ss = fmaf(z, z, ss);
           sum_ls += vecs[M::LS + j];
-          if constexpr (WRITE) {
-            zz[j] = z;
-          } else {
-            const float so = vecs[M::SOLD + j];
-            const float nr = (om[j] - mu) * (om[j] - mu) + so * so - sg * sg;
-            const float dr = 2.f * sg * sg + 1e-8f;
-            kl += nr / dr + vecs[M::LS + j] - vecs[M::OLS + j];
-          }
-        } else {
-          if constexpr (WRITE) zz[j] = 0.f;
+          // gaussian_mlp.py:137-139, KL(old || new) per dimension
+          const float so = vecs[M::SOLD + j];
+          const float nr = (om[j] - mu) * (om[j] - mu) + so * so - sg * sg;
+          const float dr = 2.f * sg * sg + 1e-8f;
+          kl += nr / dr + vecs[M::LS + j] - vecs[M::OLS + j];
         }
       }
       const float ll = (-0.5f * ss + -sum_ls) + llc;
@@ -295,18 +264,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) 
       if (a.old_ll && valid) lr = expf(ll - oll);
       const float c = valid ? lr * wv : 0.f;
       surr_acc += (double)c;
-      if (!WRITE) kl_acc += valid ? (double)kl : 0.0;
-      if constexpr (WRITE) {
-        if (valid) {
-#pragma unroll
-          for (int j = 0; j < MJT; ++j) {
-            const bool in = j < m;
-            const float uj = in ? c * (zz[j] / vecs[M::SIG + j]) * vecs[M::OS + j] : 0.f;
-            gls[j] += in ? c * (zz[j] * zz[j] - 1.f) : 0.f;
-            fa.uimg[t * MJT + j] = uj;
-          }
-        }
-      }
+      kl_acc += valid ? (double)kl : 0.0;
     }
   } else {
     // ============ MMA issuer: serves whichever set is ready ==========================================================
@@ -360,14 +318,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) 
 
   // ---- sums of the CTA ---------------------------------------------------------------------------------------------
   double* dred = reinterpret_cast<double*>(sm + M::OFF_RED);
-  float* gred = reinterpret_cast<float*>(sm + M::OFF_RED + NROW_THREADS * 16);
-  if (warp < 8) {
-    dred[2 * tid] = surr_acc; dred[2 * tid + 1] = kl_acc;
-    if constexpr (WRITE) {
-#pragma unroll
-      for (int j = 0; j < MJT; ++j) gred[tid * MJT + j] = gls[j];
-    }
-  }
+  if (warp < 8) { dred[2 * tid] = surr_acc; dred[2 * tid + 1] = kl_acc; }
   fence_before();
   __syncthreads();
   if (tid == 0) {
@@ -376,18 +327,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_fwd_kernel(const FwdArgs fa) 
     a.spartials[2 * blockIdx.x] = s0;
     a.spartials[2 * blockIdx.x + 1] = s1;
   }
-  if (WRITE && tid < m) {
-    double s = 0.0;
-    for (int i = 0; i < NROW_THREADS; ++i) s += (double)gred[i * MJT + tid];
-    a.partials[(size_t)blockIdx.x * a.dstride + F.ols + tid] = (float)s;
-  }
   __syncthreads();
   if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tb) : "memory");
 }
 
-template <int MJT, bool WRITE, bool WIDE>
+template <int MJT, bool WIDE>
 static int launch_one(const FwdArgs& fa, int grid, cudaStream_t s) {
-  auto kern = pol_fwd_kernel<MJT, WRITE, WIDE>;
+  auto kern = pol_fwd_kernel<MJT, WIDE>;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Map<MJT>::ALLOC);
@@ -400,24 +346,21 @@ static int launch_one(const FwdArgs& fa, int grid, cudaStream_t s) {
 
 }  // namespace pfw
 
-// evaluation (planes == uimg == nullptr): a.spartials[grid][2] = surrogate, KL sums.  Forward half of the gradient pass
-// (planes, uimg given): also the plane cache, u per timestep and the d log_std slice of a.partials (which the caller
-// has allocated for `grid` CTAs: the backward half runs on the same grid).
-int launch_pol_fwd(mjrl_ctx* ctx, Args& a, float* planes, float* uimg, const TcwRegions* wide, int grid, cudaStream_t s) {
+// a.spartials[grid][2] = surrogate, KL sums of the batch under a.params against the cached old policy
+int launch_pol_fwd(mjrl_ctx* ctx, Args& a, const TcwRegions* wide, int grid, cudaStream_t s) {
   a.spartials = (double*)mjrl_scratch2(ctx, sizeof(double) * 2 * grid);
   if (!a.spartials) return MJRL_E_STATE;
   pfw::FwdArgs fa;
-  fa.a = a; fa.z1 = wide ? wide->z1 : nullptr; fa.planes = planes; fa.uimg = uimg;
-  const bool write = uimg != nullptr;
+  fa.a = a; fa.z1 = wide ? wide->z1 : nullptr;
   if (wide) {
     int rc = launch_tcw_l0_fwd(ctx, *wide, a.params, a.N, a.n, a.m, grid, nullptr, s);
     if (rc) return rc;
-    if (a.m <= 8) return write ? pfw::launch_one<8, true, true>(fa, grid, s) : pfw::launch_one<8, false, true>(fa, grid, s);
-    if (a.m <= 16) return write ? pfw::launch_one<16, true, true>(fa, grid, s) : pfw::launch_one<16, false, true>(fa, grid, s);
-    return write ? pfw::launch_one<24, true, true>(fa, grid, s) : pfw::launch_one<24, false, true>(fa, grid, s);
+    if (a.m <= 8) return pfw::launch_one<8, true>(fa, grid, s);
+    if (a.m <= 16) return pfw::launch_one<16, true>(fa, grid, s);
+    return pfw::launch_one<24, true>(fa, grid, s);
   }
-  if (a.m <= 4) return write ? pfw::launch_one<4, true, false>(fa, grid, s) : pfw::launch_one<4, false, false>(fa, grid, s);
-  return write ? pfw::launch_one<8, true, false>(fa, grid, s) : pfw::launch_one<8, false, false>(fa, grid, s);
+  if (a.m <= 4) return pfw::launch_one<4, false>(fa, grid, s);
+  return pfw::launch_one<8, false>(fa, grid, s);
 }
 
 }  // namespace pol

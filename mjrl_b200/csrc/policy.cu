@@ -1409,7 +1409,7 @@ int mjrl_policy_eval_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float
   } else {
     const int64_t nt = (N + 127) / 128;
     grid = (int)(nt < ctx->sm_count ? nt : ctx->sm_count);
-    rc = launch_pol_fwd(ctx, a, nullptr, nullptr, kind == 2 ? &r : nullptr, grid, s);
+    rc = launch_pol_fwd(ctx, a, kind == 2 ? &r : nullptr, grid, s);
   }
   if (rc) return rc;
   reduce_scalars_kernel<<<1, 32, 0, s>>>(a.spartials, grid, sums2, 3, nullptr);

@@ -367,9 +367,8 @@ int launch_tcw_l0_grad(mjrl_ctx* ctx, const TcwRegions& r, float* partials, int 
                        int grid, const int32_t* stop_flag, cudaStream_t s);
 // gradient / surrogate+KL passes on tcgen05 (pol_tc.cu); `planes` = tile-ordered h1 | h2 region the gradient pass
 // fills (null for an evaluation), `wide` = the regions of the three-pass form or null for the fused narrow form
-// forward pass with two 128-timestep tiles in flight (pol_fwd.cu): the evaluation (planes = uimg = null), or the forward half
-// of the gradient pass (fills the plane cache, u per timestep, the d log_std slice of a.partials[grid])
-int launch_pol_fwd(mjrl_ctx* ctx, Args& a, float* planes, float* uimg, const TcwRegions* wide, int grid, cudaStream_t s);
+// surrogate / KL evaluation as a forward pass with two 128-timestep tiles in flight (pol_fwd.cu)
+int launch_pol_fwd(mjrl_ctx* ctx, Args& a, const TcwRegions* wide, int grid, cudaStream_t s);
 template <int MODE>
 int launch_pol_tc(mjrl_ctx* ctx, Args& a, float* planes, const TcwRegions* wide, int* grid_out, cudaStream_t s);
 
