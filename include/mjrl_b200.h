@@ -251,8 +251,8 @@ int mjrl_policy_grad_cached_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, cons
                                const float* obs, const float* act, const float* w, const float* old_ll,
                                int64_t N, double* grad_sum, double* surr_sum, float* ll_out,
                                float* mean_out, float* fvp_cache, void* stream);
-/* mjrl_policy_eval (surrogate and KL sums of batch_reinforce.py:57-75) on the tcgen05 pass of csrc/pol_tc.cu, for
- * shapes mjrl_policy_fvp_tc_ok accepts.  The gradient pass mjrl_policy_grad_cached_tc runs the same kernel family
+/* mjrl_policy_eval (surrogate and KL sums of batch_reinforce.py:57-75) on the tcgen05 forward pass of csrc/pol_fwd.cu, for
+ * shapes mjrl_policy_fvp_tc_ok accepts.  The gradient pass mjrl_policy_grad_cached_tc runs on tcgen05 too (csrc/pol_tc.cu)
  * unless MJRL_B200_GRAD_TC=0.  Shapes of kind 2 read the [x~ | 1] image that mjrl_policy_grad_cached_tc left in
  * `fvp_cache` for the SAME obs / N / input transforms (fvp_cache may be NULL for kind 1).  Same sums as
  * mjrl_policy_eval to fp32 rounding. */

@@ -12,6 +12,8 @@
 //   gz2 = (u W2)(1 - h2^2); gh1 = gz2 W1 (MMA-5); gz1 = gh1 (1 - h1^2); gW2, gW1, gW0 weight-gradient MMAs
 //
 // The gradient pass leaves h1 | h2 of every tile in the plane order the products of the following CG solve read.
+// Only the GRAD mode is instantiated: the evaluation (MODE = M_EVAL, one tile in flight: 0.30 ms at the Hopper shape) was
+// superseded by the two-tiles-in-flight forward kernel of pol_fwd.cu (0.19 ms).
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -702,6 +704,5 @@ int launch_pol_tc(mjrl_ctx* ctx, Args& a, float* planes, const TcwRegions* wide,
 }
 
 template int launch_pol_tc<M_GRAD>(mjrl_ctx*, Args&, float*, const TcwRegions*, int*, cudaStream_t);
-template int launch_pol_tc<M_EVAL>(mjrl_ctx*, Args&, float*, const TcwRegions*, int*, cudaStream_t);
 
 }  // namespace pol

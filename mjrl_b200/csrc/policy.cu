@@ -1401,16 +1401,11 @@ int mjrl_policy_eval_tc(mjrl_ctx* ctx, const mjrl_policy_desc* desc, const float
   a.old_log_std = old_log_std; a.N = N;
   int grid;
   cudaStream_t s = (cudaStream_t)stream;
-  static const bool v1 = getenv("MJRL_B200_EVAL_V1") != nullptr;      // the one-tile-in-flight kernel of pol_tc.cu (comparison)
   TcwRegions r = {};
   if (kind == 2) r = tcw_regions(fvp_cache, desc->n, N);
-  if (v1) {
-    rc = launch_pol_tc<M_EVAL>(ctx, a, nullptr, kind == 2 ? &r : nullptr, &grid, s);
-  } else {
-    const int64_t nt = (N + 127) / 128;
-    grid = (int)(nt < ctx->sm_count ? nt : ctx->sm_count);
-    rc = launch_pol_fwd(ctx, a, kind == 2 ? &r : nullptr, grid, s);
-  }
+  const int64_t nt = (N + 127) / 128;
+  grid = (int)(nt < ctx->sm_count ? nt : ctx->sm_count);
+  rc = launch_pol_fwd(ctx, a, kind == 2 ? &r : nullptr, grid, s);
   if (rc) return rc;
   reduce_scalars_kernel<<<1, 32, 0, s>>>(a.spartials, grid, sums2, 3, nullptr);
   return mjrl_check_launch("policy_eval_tc reduce");
