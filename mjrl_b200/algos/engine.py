@@ -201,7 +201,7 @@ class UpdateEngine:
             key = self._hold(params, obs) if fcache is not None else None
             self._cache_key = None if direct_tc else key     # fragment-ordered h1|h2 (modes 2, 3)
             self._tc_key = key if direct_tc else None        # tile-ordered copy (mode 4)
-            self._ximg_key = self._key(obs, obs) if direct_tc and self._tc_kind() == 2 else None   # [x~ | 1] image (wide shapes)
+            self._ximg_key = (self._key(obs, obs), self.dv._tr_key) if direct_tc and self._tc_kind() == 2 else None   # [x~ | 1] image (wide shapes)
             self._jac_key = None
         self.launches += 3
         if accumulate:
@@ -398,7 +398,8 @@ class UpdateEngine:
         left in `self.sums2` for `tail()`: the caller divides on the host)."""
         N = obs.shape[0]
         kind = self._tc_kind() if N >= TC_MIN_N and EVAL_TC else 0
-        if kind == 2 and not (self._cache is not None and self._ximg_key is not None and self._ximg_key == self._key(obs, obs)):
+        self.dv.desc_ref()      # refreshes the transform key the image key below is compared with
+        if kind == 2 and not (self._cache is not None and self._ximg_key is not None and self._ximg_key == (self._key(obs, obs), self.dv._tr_key)):
             kind = 0      # wide shapes need the [x~ | 1] image the gradient pass of THIS batch left in the cache
         if kind:
             self.ctx.call("mjrl_policy_eval_tc", self.dv.desc_ref(), ptr(params_new), ptr(obs), ptr(act),
