@@ -428,6 +428,9 @@ linbase_gram_tiles_kernel(const float* __restrict__ obs, const double* __restric
       if (a >= nside) { a = nside - 1; b = nside - 1; }  // past the end: never used (k >= nown)
     }
   }
+  unsigned newrow = 1u;       // bit k: tile k starts a new tile row (its A fragment differs from tile k - 1's)
+#pragma unroll
+  for (int k = 1; k < MAXT; ++k) newrow |= (ti[k] != ti[k - 1]) ? (1u << k) : 0u;
   double acc[MAXT][2];
 #pragma unroll
   for (int k = 0; k < MAXT; ++k) acc[k][0] = acc[k][1] = 0.0;
@@ -443,15 +446,23 @@ linbase_gram_tiles_kernel(const float* __restrict__ obs, const double* __restric
     else
       gram_stage_tile(obs, ret, off, P, (double)P / (double)N, t0, rows, n, TS, FP8, FS, feat, tid);
     __syncthreads();
+    // branch-free inner loop (ncu, obs_dim 111: two thirds of the stall samples sat on the two fragment loads below, issued one
+    // at a time behind warp-uniform branches and per-tile index arithmetic; DMMA pipe 24 % busy): all B fragments of a quad of
+    // timesteps are requested first, the A fragment is reloaded only where the tile row changes (a predicated load on a
+    // precomputed bit), slots k >= nown multiply harmless in-bounds data into accumulators that are never written out.
     for (int qd = 0; qd < nq; ++qd) {
       const double* fr = feat + (4 * qd + q) * FS + g;
+      constexpr int CH = MAXT < 16 ? MAXT : 16;      // B fragments in flight at once
       double fa = 0.0;
 #pragma unroll
-      for (int k = 0; k < MAXT; ++k) {
-        if (k < nown) {  // warp-uniform
-          if (k == 0 || ti[k] != ti[k - 1]) fa = fr[8 * ti[k]];
-          const double fb = fr[8 * tj[k]];
-          dmma_m8n8k4(acc[k][0], acc[k][1], fa, fb);
+      for (int k0 = 0; k0 < MAXT; k0 += CH) {
+        double fb[CH];
+#pragma unroll
+        for (int k = 0; k < CH; ++k) fb[k] = fr[8 * tj[k0 + k]];
+#pragma unroll
+        for (int k = 0; k < CH; ++k) {
+          if ((newrow >> (k0 + k)) & 1u) fa = fr[8 * ti[k0 + k]];
+          dmma_m8n8k4(acc[k0 + k][0], acc[k0 + k][1], fa, fb[k]);
         }
       }
     }

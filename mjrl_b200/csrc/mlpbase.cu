@@ -612,10 +612,23 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
   __syncthreads();
   cluster_sync_all();   // every CTA's barriers are initialised before any peer signals them
 
+  // element i = tid + j PT of a minibatch is (row slot i / F, column i % F) in every step: divide once, not per step
+  // (ncu: the two runtime divisions per element were 8 % of the chain's stall samples)
+  int pfb[4], pfk[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { const int i = tid + j * PT; pfb[j] = i / F; pfk[j] = i - pfb[j] * F; }
   auto prefetch = [&](long long s) {   // minibatch s -> buffer s & 1 (every CTA loads the same rows)
     float* X = sm + L.X + (int)(s & 1) * TS * FP;
     const int32_t* idx = a.perm + s * bs;
     const int cnt = bs * F;
+    if (cnt <= 4 * PT) {
+      long long row[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) row[j] = tid + j * PT < cnt ? (long long)__ldg(idx + pfb[j]) : 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (tid + j * PT < cnt) cp_async4(X + pfb[j] * FP + pfk[j], a.feat + row[j] * F + pfk[j]);
+    } else
     for (int i0 = tid; i0 < cnt; i0 += 4 * PT) {
       long long row[4];
 #pragma unroll
@@ -763,21 +776,20 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
     CL_STAMP(5);
     // ---- (overlaps E3) fc_1 gradient for the owned rows: 8 entries per thread; gb1 -------------
     float g1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float gb1 = 0.f;
     {
       const float* ha = sH0 + (gi0 >> 4) * SS + (gi0 & 15);
       const float* hb = sH0 + ((gi0 + 64) >> 4) * SS + (gi0 & 15);
 #pragma unroll 4
       for (int b = 0; b < TS; ++b) {
         const float d = sH1[b * LDU + gu];
+        gb1 += d;      // fc_1 bias gradient of unit gu, same order over the batch as a separate loop (used by the gi0 == 0 thread)
         const float4 x = *reinterpret_cast<const float4*>(ha + b * UC);
         const float4 y = *reinterpret_cast<const float4*>(hb + b * UC);
         g1[0] = fmaf(d, x.x, g1[0]); g1[1] = fmaf(d, x.y, g1[1]); g1[2] = fmaf(d, x.z, g1[2]); g1[3] = fmaf(d, x.w, g1[3]);
         g1[4] = fmaf(d, y.x, g1[4]); g1[5] = fmaf(d, y.y, g1[5]); g1[6] = fmaf(d, y.z, g1[6]); g1[7] = fmaf(d, y.w, g1[7]);
       }
     }
-    float gb1 = 0.f;
-    if (tid < UC)
-      for (int b = 0; b < TS; ++b) gb1 += sH1[b * LDU + tid];
     // ---- Adam on fc_1 rows (old rows were last read by the dh0 partials above) -----------------
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {
@@ -789,8 +801,8 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
       *reinterpret_cast<float4*>(sW1 + o) = w4; *reinterpret_cast<float4*>(sM1 + o) = m4;
       *reinterpret_cast<float4*>(sV1 + o) = v4;
     }
+    if (gi0 == 0) sb1[gu] = adam(sb1[gu], gb1, sb1m[gu], sb1v[gu], ac);
     if (tid < UC) {
-      sb1[tid] = adam(sb1[tid], gb1, sb1m[tid], sb1v[tid], ac);
       sw2[tid] = adam(sw2[tid], gw2, sw2m[tid], sw2v[tid], ac);
     } else if (tid == 32) {
       sb2[0] = adam(sb2[0], gb2, sb2[1], sb2[2], ac);
@@ -813,19 +825,19 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PT, 1) fit_cluster_
     for (int e = tid; e < UC * FP; e += PT) {
       const int uu = e / FP, k = e - uu * FP;
       if (k < F) {
-        float g = 0.f;
+        float g = 0.f, gb0 = 0.f;
 #pragma unroll 8
-        for (int b = 0; b < TS; ++b) g = fmaf(sDZ0[b * LDU + uu], X[b * FP + k], g);
+        for (int b = 0; b < TS; ++b) {
+          const float dz = sDZ0[b * LDU + uu];
+          g = fmaf(dz, X[b * FP + k], g);
+          gb0 += dz;     // fc_0 bias gradient of unit uu (used by the k == 0 thread), same order over the batch
+        }
         const int o = uu * LD0 + k;
         sW0[o] = adam(sW0[o], g, sM0[o], sV0[o], ac);
+        if (k == 0) sb0[uu] = adam(sb0[uu], gb0, sb0m[uu], sb0v[uu], ac);
       }
     }
     CL_STAMP(10);
-    if (tid < UC) {
-      float gb0 = 0.f;
-      for (int b = 0; b < TS; ++b) gb0 += sDZ0[b * LDU + tid];
-      sb0[tid] = adam(sb0[tid], gb0, sb0m[tid], sb0v[tid], ac);
-    }
     CL_STAMP(8);
     // the __syncthreads at the top of the next step orders these writes before its reads
   }
