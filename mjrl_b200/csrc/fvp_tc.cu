@@ -266,12 +266,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) { h[i] = lo_of(h[i]); u32[i] = __float_as_uint(h[i]); }
         tst32(tl + T_A1 + 64 + 32 * blk, u32);
+        wait_st();
+        fence_before();
+        mbar_arrive(&bar[B_E0]);
+        // after the hand-off: the h1 lo plane is an operand of gW1 only (every thread fences before its B_E2A / B_E2C arrival)
         store_row32(pW, r, blk, h);
       }
-      wait_st();
-      fence_async();
-      fence_before();
-      mbar_arrive(&bar[B_E0]);
       stamp(2);
 
       // ---- E1: dh1 = (1 - h1^2) dz1, in place over dz1 (hi) and next to it (lo) ---------------------------
@@ -352,32 +352,34 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_tc_kernel(const TcArgs a) {
           u[j] = (a0.x + a0.y) + (a1.x + a1.y);
         }
       }
-      // the two halves of a row add their partial sums through the u array (half 1 -> half 0 -> half 1)
-      if (half == 1) {
+      // the two halves of a row swap their partial sums (half 0's through the lo rows of the u^T plane, half 1's through the u
+      // array), ONE barrier, and both form the same u (the sum is commutative); then half 0 files u (u^T hi rows, u array for
+      // the gb2 sums) and half 1 its lo part over the slot it has just read
+      if (half == 0) {
+#pragma unroll
+        for (int j = 0; j < MJT; ++j) *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, 8 + j, r)) = u[j];
+      } else {
 #pragma unroll
         for (int j = 0; j < MJT; ++j) vecs[Vec::UARR + r * MJ + j] = u[j];
       }
       pair_sync();
-      if (half == 0) {
 #pragma unroll
-        for (int j = 0; j < MJT; ++j) {
-          const float dmu = u[j] + vecs[Vec::UARR + r * MJ + j];
-          u[j] = (valid && j < m) ? vecs[Vec::FISHER + j] * (dmu + vecs[Vec::DB2 + j]) : 0.f;
-        }
+      for (int j = 0; j < MJT; ++j) {
+        const float other = half == 0 ? vecs[Vec::UARR + r * MJ + j]
+                                      : *reinterpret_cast<const float*>(sm + OFF_UT + k128_off(16, 8 + j, r));
+        const float dmu = u[j] + other;
+        u[j] = (valid && j < m) ? vecs[Vec::FISHER + j] * (dmu + vecs[Vec::DB2 + j]) : 0.f;
+      }
+      if (half == 0) {
 #pragma unroll
         for (int j = 0; j < MJT; ++j) {
           vecs[Vec::UARR + r * MJ + j] = u[j];
           // u^T planes, K-major over the timestep: rows j (hi) and 8 + j (lo), column r
           *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, j, r)) = u[j];
         }
-      }
-      pair_sync();
-      if (half == 1) {
+      } else {
 #pragma unroll
-        for (int j = 0; j < MJT; ++j) {
-          u[j] = vecs[Vec::UARR + r * MJ + j];
-          *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, 8 + j, r)) = lo_of(u[j]);
-        }
+        for (int j = 0; j < MJT; ++j) *reinterpret_cast<float*>(sm + OFF_UT + k128_off(16, 8 + j, r)) = lo_of(u[j]);
       }
       fence_async();
       mbar_arrive(&bar[B_E2A]);

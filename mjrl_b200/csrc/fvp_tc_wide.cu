@@ -524,12 +524,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_wide_kernel(const WideArgs a)
 #pragma unroll
         for (int i = 0; i < 32; ++i) { h[i] = lo_of(h[i]); u32[i] = __float_as_uint(h[i]); }
         tst32(tl + T_A1 + 64 + 32 * blk, u32);
+        wait_st();
+        fence_before();
+        mbar_arrive(&bar[B_E0]);
+        // after the hand-off: the h1 lo plane is an operand of gW1 only (every thread fences before its B_E2A / B_E2C arrival)
         store_row32(pW, r, blk, h);
       }
-      wait_st();
-      fence_async();
-      fence_before();
-      mbar_arrive(&bar[B_E0]);
       // ---- E1: dh1 = (1 - h1^2) dz1 -------------------------------------------------------------------------
       {
         uint32_t d[32], l[32];
@@ -601,30 +601,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) fvp_wide_kernel(const WideArgs a)
           u[j] += (a0.x + a0.y) + (a1.x + a1.y);
         }
       }
-      // the two halves of a row add their partial sums through the u^T plane (row j = u hi, row MJT + j = u lo,
-      // column = timestep): half 1 -> half 0 -> half 1.  gW2 of the previous tile has read it (B_GW2 + q, E2c).
-      if (half == 1) {
+      // the two halves of a row swap their partial sums through the u^T plane (half 0's in the lo rows MJT + j, half 1's in the
+      // hi rows j, column = timestep), ONE barrier, and both form the same u (the sum is commutative); then half 0 files u in
+      // the hi rows and half 1 its lo part in the lo rows, each over the slot it has just read.  gW2 of the previous tile has
+      // read the plane (B_GW2 + q, E2c).
 #pragma unroll
-        for (int j = 0; j < MJT; ++j) *reinterpret_cast<float*>(pU + k128_off(UR, j, r)) = u[j];
-      }
+      for (int j = 0; j < MJT; ++j) *reinterpret_cast<float*>(pU + k128_off(UR, (half == 0 ? MJT : 0) + j, r)) = u[j];
       pair_sync();
-      if (half == 0) {
 #pragma unroll
-        for (int j = 0; j < MJT; ++j) {
-          float* p = reinterpret_cast<float*>(pU + k128_off(UR, j, r));
-          const float dmu = u[j] + *p;
-          u[j] = (valid && j < m) ? vecs[M::FISHER + j] * (dmu + vecs[M::DB2 + j]) : 0.f;
-          *p = u[j];
-        }
+      for (int j = 0; j < MJT; ++j) {
+        const float other = *reinterpret_cast<const float*>(pU + k128_off(UR, (half == 0 ? 0 : MJT) + j, r));
+        const float dmu = u[j] + other;
+        u[j] = (valid && j < m) ? vecs[M::FISHER + j] * (dmu + vecs[M::DB2 + j]) : 0.f;
       }
-      pair_sync();
-      if (half == 1) {
 #pragma unroll
-        for (int j = 0; j < MJT; ++j) {
-          u[j] = *reinterpret_cast<const float*>(pU + k128_off(UR, j, r));
-          *reinterpret_cast<float*>(pU + k128_off(UR, MJT + j, r)) = lo_of(u[j]);
-        }
-      }
+      for (int j = 0; j < MJT; ++j)
+        *reinterpret_cast<float*>(pU + k128_off(UR, (half == 0 ? 0 : MJT) + j, r)) = half == 0 ? u[j] : lo_of(u[j]);
       fence_async();
       mbar_arrive(&bar[B_E2A]);
       float gz[32];
