@@ -22,6 +22,19 @@ def _pinned(shape, dtype):
     return torch.empty(shape, dtype=dtype, pin_memory=True)
 
 
+# the action block of a large pinned fp32 upload travels on its own stream behind the observations (MJRL_B200_OVERLAP_ACT=0: off)
+import os as _os
+OVERLAP_ACT = _os.environ.get("MJRL_B200_OVERLAP_ACT", "1") != "0"
+_copy_streams = {}
+
+
+def _copy_stream(device):
+    key = (device.index, )
+    if key not in _copy_streams:
+        _copy_streams[key] = torch.cuda.Stream(device=device)
+    return _copy_streams[key]
+
+
 class PathBatch:
     def __init__(self, obs, act, rew, path_offsets, terminated, device=None, paths=None):
         """`obs` [N,n], `act` [N,m], `rew` [N] are HOST arrays (numpy fp64/fp32 or pinned
@@ -39,14 +52,53 @@ class PathBatch:
         self.offsets = torch.from_numpy(off).to(dev, non_blocking=False)
         self.terminated = torch.from_numpy(
             np.ascontiguousarray(np.asarray(terminated), dtype=np.uint8)).to(dev)
-        self.obs = self._upload_f32(obs, (self.N, self.n))
-        self.act = self._upload_f32(act, (self.N, self.m)) if act is not None else None
+        # copy order = order of first use: rewards (returns scan), observations (baseline predictions, GAE, moments), then the
+        # actions, which nothing reads before the policy gradient pass: a pinned fp32 action block goes over a copy stream
+        # behind the observations, and `act` makes the consuming stream wait for it on first use, so ~0.2 ms of a 1M-timestep
+        # upload overlaps with the scans instead of preceding them
         self.rew = self._upload_f64(rew)
+        self.obs = self._upload_f32(obs, (self.N, self.n))
+        self._act = None
+        self._act_event = None
+        if act is not None:
+            h = self._host_tensor(act)
+            if OVERLAP_ACT and h.dtype == torch.float32 and h.is_pinned() and self.N * self.m >= (1 << 20):
+                self._upload_act_behind(h.reshape(self.N, self.m))
+            else:
+                self._act = self._upload_f32(act, (self.N, self.m))
         self.returns = None
         self.baseline = None
         self.adv = None
         self.h2d_bytes = (self._nbytes(obs) + (self._nbytes(act) if act is not None else 0)
                           + self._nbytes(rew) + off.nbytes + self.P)
+
+    # ---- actions: possibly still in flight on the copy stream -----------------------------
+    @property
+    def act(self):
+        ev = self._act_event
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev)     # the consumer's stream, once
+            self._act_event = None
+        return self._act
+
+    @act.setter
+    def act(self, value):
+        self._act, self._act_event = value, None
+
+    def _upload_act_behind(self, h):
+        dev = self.device
+        cur = torch.cuda.current_stream(dev)
+        side = _copy_stream(dev)
+        d = torch.empty(h.shape, dtype=torch.float32, device=dev)     # allocated on the consumer's stream
+        after_obs = torch.cuda.Event()
+        after_obs.record(cur)                 # behind the observation copy (and anything that used this memory before)
+        side.wait_event(after_obs)
+        with torch.cuda.stream(side):
+            d.copy_(h, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(side)
+        d.record_stream(side)
+        self._act, self._act_event = d, done
 
     @staticmethod
     def _nbytes(a):
