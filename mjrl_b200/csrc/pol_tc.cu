@@ -53,6 +53,7 @@ struct PolArgs {
   float* planes;      // gradient: tile-ordered h1 | h2 cache to fill (may be null)
   const float* z1;    // wide: z1 image ([x~ 1] [W0 | b0]^T, pass A)
   float* gz1;         // wide gradient: GZ1 image for pass C
+  long long* dbg;     // debug: per-phase cycle sums of CTA 0, thread 0 (MJRL_B200_TC_PHASES=1), else null
 };
 
 // one row's 32 columns -> a plane in HBM (32-byte atoms in natural order)
@@ -169,6 +170,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
     };
     if (!WIDE) prefetch_obs(blockIdx.x);
     const float llc = (float)(-0.5 * (double)m * 1.8378770664093453);
+    long long ph_sum[12], tprev = 0;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) ph_sum[i] = 0;
+    const bool stamp_on = pa.dbg != nullptr && tid == 0 && blockIdx.x == 0;
+    auto stamp = [&](int i) { if (stamp_on) { const long long c = clock64(); ph_sum[i] += c - tprev; tprev = c; } };
+    if (stamp_on) tprev = clock64();
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
@@ -194,6 +201,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
         wait_st();
         fence_before();
         mbar_arrive(&bar[B_E0]);
+        stamp(0);
       } else {
         const float4* zp = reinterpret_cast<const float4*>(pa.z1) + (size_t)tile * (ROWS * H / 4) + (size_t)(8 * blk) * ROWS + r;
 #pragma unroll
@@ -206,6 +214,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
         uint32_t u32[32];
         if (!WIDE) {
           tma::mbar_wait(&bar[B_M1], ph);
+          stamp(1);
           fence_after();
           tld32w(tl + T_D1 + 32 * blk, u32);
 #pragma unroll
@@ -227,6 +236,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
         wait_st();
         fence_before();
         mbar_arrive(&bar[B_E1]);
+        stamp(2);
         // ... while MMA-2 runs: the planes gW1 reads much later (every thread fences before its B_E2A / B_E2C arrival)
         if (GRAD) {
           store_row32(pX, r, blk, h);
@@ -254,7 +264,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       {
         float h[32];
         uint32_t d[32];
+        stamp(3);
         tma::mbar_wait(&bar[B_M2B], ph);
+        stamp(4);
         fence_after();
         tld32w(tl + T_D2 + 32 * blk, d);
 #pragma unroll
@@ -285,6 +297,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
           store_row32(pZ, r, blk, h);
         }
       }
+      stamp(5);
       // the two threads of a row meet in the u^T plane (row j, column = timestep): half 1 -> half 0 (-> half 1)
       if (half == 1) {
 #pragma unroll
@@ -349,6 +362,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       }
       fence_async();
       mbar_arrive(&bar[B_E2A]);
+      stamp(6);
       float gz[32];
       {
         uint32_t hi[32], lo[32];
@@ -373,6 +387,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       wait_st();
       fence_before();
       mbar_arrive(&bar[B_E2B]);
+      stamp(7);
       tma::mbar_wait(&bar[B_GW2 + q], ph);              // gW2 has read this quadrant's rows of h2 hi | lo: they become gz2
       {
         store_row32(pY, r, blk, gz);
@@ -383,10 +398,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       }
       fence_async();
       mbar_arrive(&bar[B_E2C + q]);
+      stamp(8);
       // ---- P3: gz1 = gh1 (1 - h1^2) ------------------------------------------------------------------------------------
       {
         uint32_t d[32];
         tma::mbar_wait(&bar[B_M5], ph);
+        stamp(9);
         fence_after();
         tld32w(tl + T_D1 + 32 * blk, d);
 #pragma unroll
@@ -402,6 +419,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       }
       tma::mbar_wait(&bar[B_GW1 + q], ph);              // gW1 has read this quadrant's rows of gz2
       tma::mbar_wait(&bar[B_W3 + q], ph);               // warp 3 has summed them for gb1
+      stamp(10);
       store_row32(pY, r, blk, gz);
       if (!WIDE) {
         float gl[32];
@@ -412,8 +430,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       fence_async();
       mbar_arrive(&bar[B_E3 + q]);
       if (!WIDE) prefetch_obs(tile + gridDim.x);
+      stamp(11);
       }
     }
+    if (stamp_on) { for (int i = 0; i < 12; ++i) pa.dbg[i] = ph_sum[i]; pa.dbg[12] = it; }
   } else if (warp == 3) {
     // ============ bias gradients of layers 1 and 2 (gradient pass only) ===========================================
     if (GRAD) {
@@ -688,6 +708,26 @@ int launch_pol_tc(mjrl_ctx* ctx, Args& a, float* planes, const TcwRegions* wide,
   if (!a.spartials) return MJRL_E_STATE;
   ptc::PolArgs pa;
   pa.a = a; pa.planes = planes; pa.z1 = wide ? wide->z1 : nullptr; pa.gz1 = wide ? wide->gz1 : nullptr;
+  static const bool phases = getenv("MJRL_B200_TC_PHASES") != nullptr;
+  static long long* dbg = nullptr;
+  if (phases && !dbg) cudaMalloc(&dbg, 16 * sizeof(long long));
+  pa.dbg = phases ? dbg : nullptr;
+  struct Report {      // debug only: synchronous print of the per-phase cycle stamps when the launcher returns
+    long long* d; cudaStream_t st;
+    ~Report() {
+      if (!d) return;
+      long long h[16];
+      cudaStreamSynchronize(st);
+      cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+      static const char* nm[12] = {"x~ + st", "wait M1", "P1 tanh->tmem", "P1 planes, loads", "wait M2", "P2 tanh, head, planes", "P2 exchange, LL, u^T",
+                                   "gz2->tmem", "wait gW2 + planes", "wait M5", "P3 compute + waits", "P3 planes"};
+      long long tot = 0;
+      for (int i = 0; i < 12; ++i) tot += h[i];
+      fprintf(stderr, "pol_tc phases (CTA 0, %lld tiles, %lld cycles per tile):", h[12], h[12] ? tot / h[12] : 0);
+      for (int i = 0; i < 12; ++i) fprintf(stderr, " [%s %lld]", nm[i], h[12] ? h[i] / h[12] : 0);
+      fprintf(stderr, "\n");
+    }
+  } report{pa.dbg, s};
   int rc;
   if (wide) {
     rc = launch_tcw_l0_fwd(ctx, *wide, a.params, a.N, a.n, a.m, grid, nullptr, s);
