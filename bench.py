@@ -346,8 +346,38 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.rows, self.proc = index, [], None
+        self.nvml, self.stop_flag = None, False
+
+    def _nvml_loop(self):
+        nv, h = self.nvml
+        # NVML clocks-event (throttle) reason bits
+        bits = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                row = [str(self.index), str(sm), str(mx), "", ""] + ["Active" if rs & b else "Not Active" for _, b in bits]
+                self.rows.append(row)
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def start(self):
+        # NVML in-process (a query takes microseconds: 8 ranks each spawning nvidia-smi got no sample inside a 0.1 s timed region),
+        # nvidia-smi as the fallback
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            self.nvml = (nv, nv.nvmlDeviceGetHandleByIndex(self.index))
+            self.th = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20",
@@ -362,13 +392,17 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
-        if not self.proc:
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.th.join(timeout=1)
+        elif not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            pass
+        else:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                pass
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
@@ -382,7 +416,7 @@ class ClockSampler:
         sm.sort()
         busy = [v for v in sm if mx and v > 0.5 * mx] or sm
         return {"sm_mhz": busy[len(busy) // 2] if busy else None, "sm_max_mhz": mx,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def run_b200(args):
