@@ -12,8 +12,8 @@
 //   gz2 = (u W2)(1 - h2^2); gh1 = gz2 W1 (MMA-5); gz1 = gh1 (1 - h1^2); gW2, gW1, gW0 weight-gradient MMAs
 //
 // The gradient pass leaves h1 | h2 of every tile in the plane order the products of the following CG solve read.
-// Only the GRAD mode is instantiated: the evaluation (MODE = M_EVAL, one tile in flight: 0.30 ms at the Hopper shape) was
-// superseded by the two-tiles-in-flight forward kernel of pol_fwd.cu (0.19 ms).
+// The evaluation started as the forward half of this kernel (one tile in flight: 0.30 ms at the Hopper shape) and moved to the
+// two-tiles-in-flight forward kernel of pol_fwd.cu (0.19 ms); this file is the gradient pass only.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -39,7 +39,7 @@ struct Map {
   static constexpr int LOROW = UR / 2;
   static constexpr uint32_t OFF_VEC = OFF_UT + 3 * UR * 128;
   static constexpr int W2 = 0, B1 = MJT * H, B2 = B1 + H, SIG = B2 + MJT, LS = SIG + MJT, OS = LS + MJT, OSH = OS + MJT,
-                       OLS = OSH + MJT, SOLD = OLS + MJT, ISHIFT = SOLD + MJT, IRCP = ISHIFT + KX;
+                       ISHIFT = OSH + MJT, IRCP = ISHIFT + KX;
   static constexpr uint32_t VEC_FLOATS = IRCP + KX;
   static constexpr uint32_t OFF_BAR = (OFF_VEC + 4 * VEC_FLOATS + 15) & ~15u;
   static constexpr uint32_t BYTES = OFF_BAR + 8 * 32;
@@ -66,10 +66,9 @@ __device__ __forceinline__ void gstore_row32(float* plane, int r, int blk, const
   }
 }
 
-template <int MJT, int MODE, bool WIDE>
+template <int MJT, bool WIDE>
 __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
   using M = Map<MJT>;
-  constexpr bool GRAD = MODE == M_GRAD;
   constexpr int UR = M::UR, LOROW = M::LOROW;
   constexpr uint32_t T_ACC2 = WIDE ? 448u : 480u;
   const Args& a = pa.a;
@@ -113,7 +112,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       const int o = i >> 6, k = i & 63;
       const float w = __ldg(P + F.oW1 + i);
       put(OFF_W1, WPLANE, k128_off(H, o, k), w);                 // B[N = o][K = i]: h1 W1^T
-      if (GRAD) put(OFF_W1T, WPLANE, k128_off(H, k, o), w);      // B[N = i][K = o]: gz2 W1
+      put(OFF_W1T, WPLANE, k128_off(H, k, o), w);                // B[N = i][K = o]: gz2 W1
     }
     if (!WIDE) {
       for (int i = tid; i < H * n; i += NTHREADS) {
@@ -136,9 +135,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       vecs[M::SIG + j] = expf(ls);
       vecs[M::OS + j] = (in && a.out_scale) ? __ldg(a.out_scale + j) : 1.f;
       vecs[M::OSH + j] = (in && a.out_shift) ? __ldg(a.out_shift + j) : 0.f;
-      const float ols = (!GRAD && in) ? __ldg(a.old_log_std + j) : 0.f;
-      vecs[M::OLS + j] = ols;
-      vecs[M::SOLD + j] = expf(ols);
     }
   }
   fence_async();
@@ -150,7 +146,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
   unsigned char* pX = sm + OFF_X; unsigned char* pW = sm + OFF_W;
   unsigned char* pY = sm + OFF_Y; unsigned char* pZ = sm + OFF_Z;
   unsigned char* pU = sm + OFF_UT;
-  double surr_acc = 0.0, kl_acc = 0.0;
+  double surr_acc = 0.0;
   float gls[MJT];
 #pragma unroll
   for (int j = 0; j < MJT; ++j) gls[j] = 0.f;
@@ -238,28 +234,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
         mbar_arrive(&bar[B_E1]);
         stamp(2);
         // ... while MMA-2 runs: the planes gW1 reads much later (every thread fences before its B_E2A / B_E2C arrival)
-        if (GRAD) {
-          store_row32(pX, r, blk, h);
-          if (pa.planes) gstore_row32(pa.planes + (size_t)tile * (2 * PLANE / 4), r, blk, h);
+        store_row32(pX, r, blk, h);
+        if (pa.planes) gstore_row32(pa.planes + (size_t)tile * (2 * PLANE / 4), r, blk, h);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) h[i] = __uint_as_float(l32[i]);
-          store_row32(pW, r, blk, h);
-        }
+        for (int i = 0; i < 32; ++i) h[i] = __uint_as_float(l32[i]);
+        store_row32(pW, r, blk, h);
       }
 
       // ---- P2: h2 = tanh(z2 + b1); head ------------------------------------------------------------------------------
-      float av[MJT], om[GRAD ? 1 : MJT];
+      float av[MJT];
       float wv = 0.f, oll = 0.f;
       if (half == 0 && valid) {      // this row's scalars, requested while MMA-2 runs
 #pragma unroll
-        for (int j = 0; j < MJT; ++j) {
-          av[j] = j < m ? __ldg(a.act + t * m + j) : 0.f;
-          if constexpr (!GRAD) om[j] = j < m ? __ldg(a.old_mean + t * m + j) : 0.f;
-        }
+        for (int j = 0; j < MJT; ++j) av[j] = j < m ? __ldg(a.act + t * m + j) : 0.f;
         wv = a.w ? __ldg(a.w + t) : 0.f;
         oll = a.old_ll ? __ldg(a.old_ll + t) : 0.f;
       }
-      float s2[GRAD ? 32 : 1];
+      float s2[32];
       float u[MJT];
       {
         float h[32];
@@ -286,16 +277,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
           }
           u[j] = (a0.x + a0.y) + (a1.x + a1.y);
         }
-        if constexpr (GRAD) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) s2[i] = fmaf(-h[i], h[i], 1.f);
-          if (it > 0) tma::mbar_wait(&bar[B_GW0], (it - 1) & 1);     // the previous tile's gz1 planes have been read
-          store_row32(pY, r, blk, h);
-          if (pa.planes) gstore_row32(pa.planes + (size_t)tile * (2 * PLANE / 4) + PLANE / 4, r, blk, h);
+        for (int i = 0; i < 32; ++i) s2[i] = fmaf(-h[i], h[i], 1.f);
+        if (it > 0) tma::mbar_wait(&bar[B_GW0], (it - 1) & 1);     // the previous tile's gz1 planes have been read
+        store_row32(pY, r, blk, h);
+        if (pa.planes) gstore_row32(pa.planes + (size_t)tile * (2 * PLANE / 4) + PLANE / 4, r, blk, h);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) h[i] = lo_of(h[i]);
-          store_row32(pZ, r, blk, h);
-        }
+        for (int i = 0; i < 32; ++i) h[i] = lo_of(h[i]);
+        store_row32(pZ, r, blk, h);
       }
       stamp(5);
       // the two threads of a row meet in the u^T plane (row j, column = timestep): half 1 -> half 0 (-> half 1)
@@ -305,8 +294,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       }
       pair_sync();
       if (half == 0) {
-        float ss = 0.f, sum_ls = 0.f, kl = 0.f;
-        float zz[GRAD ? MJT : 1];
+        float ss = 0.f, sum_ls = 0.f;
+        float zz[MJT];
 #pragma unroll
         for (int j = 0; j < MJT; ++j) {
           const float dot = u[j] + *reinterpret_cast<const float*>(pU + k128_off(UR, j, r));
@@ -317,17 +306,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
             const float z = (av[j] - mu) / sg;
             ss = fmaf(z, z, ss);
             sum_ls += vecs[M::LS + j];
-            if constexpr (GRAD) {
-              zz[j] = z;
-            } else {
-              // gaussian_mlp.py:137-139, KL(old || new) per dimension
-              const float so = vecs[M::SOLD + j];
-              const float nr = (om[j] - mu) * (om[j] - mu) + so * so - sg * sg;
-              const float dr = 2.f * sg * sg + 1e-8f;
-              kl += nr / dr + vecs[M::LS + j] - vecs[M::OLS + j];
-            }
+            zz[j] = z;
           } else {
-            if constexpr (GRAD) zz[j] = 0.f;
+            zz[j] = 0.f;
           }
         }
         // gaussian_mlp.py:107-109
@@ -337,21 +318,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
         if (a.old_ll && valid) lr = expf(ll - oll);
         const float c = valid ? lr * wv : 0.f;
         surr_acc += (double)c;
-        if (!GRAD) kl_acc += valid ? (double)kl : 0.0;
-        if constexpr (GRAD) {
 #pragma unroll
-          for (int j = 0; j < MJT; ++j) {
-            const bool in = j < m && valid;
-            u[j] = in ? c * (zz[j] / vecs[M::SIG + j]) * vecs[M::OS + j] : 0.f;     // dL / dy_j
-            gls[j] += in ? c * (zz[j] * zz[j] - 1.f) : 0.f;                         // dL / dlog_std_j
-            *reinterpret_cast<float*>(pU + k128_off(UR, j, r)) = u[j];
-          }
+        for (int j = 0; j < MJT; ++j) {
+          const bool in = j < m && valid;
+          u[j] = in ? c * (zz[j] / vecs[M::SIG + j]) * vecs[M::OS + j] : 0.f;     // dL / dy_j
+          gls[j] += in ? c * (zz[j] * zz[j] - 1.f) : 0.f;                         // dL / dlog_std_j
+          *reinterpret_cast<float*>(pU + k128_off(UR, j, r)) = u[j];
         }
       }
-      if constexpr (!GRAD) {
-        if (!WIDE) prefetch_obs(tile + gridDim.x);
-        continue;
-      } else {
       pair_sync();
       if (half == 1) {
 #pragma unroll
@@ -431,53 +405,50 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       mbar_arrive(&bar[B_E3 + q]);
       if (!WIDE) prefetch_obs(tile + gridDim.x);
       stamp(11);
-      }
     }
     if (stamp_on) { for (int i = 0; i < 12; ++i) pa.dbg[i] = ph_sum[i]; pa.dbg[12] = it; }
   } else if (warp == 3) {
-    // ============ bias gradients of layers 1 and 2 (gradient pass only) ===========================================
-    if (GRAD) {
-      double gb1a = 0.0, gb1b = 0.0, gb2 = 0.0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const uint32_t ph = it & 1;
-        tma::mbar_wait(&bar[B_E2A], ph);            // u of the tile is complete; rewritten only after this warp's B_W3 arrivals
-        if (lane < MJT) {
-          float f[4] = {0.f, 0.f, 0.f, 0.f};
+    // ============ bias gradients of layers 1 and 2 ================================================================
+    double gb1a = 0.0, gb1b = 0.0, gb2 = 0.0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const uint32_t ph = it & 1;
+      tma::mbar_wait(&bar[B_E2A], ph);            // u of the tile is complete; rewritten only after this warp's B_W3 arrivals
+      if (lane < MJT) {
+        float f[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
-          for (int rr = 0; rr < ROWS; rr += 4) {
+        for (int rr = 0; rr < ROWS; rr += 4) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) f[k] += *reinterpret_cast<const float*>(pU + k128_off(UR, lane, rr + k));
-          }
-          gb2 += (double)((f[0] + f[1]) + (f[2] + f[3]));
+          for (int k = 0; k < 4; ++k) f[k] += *reinterpret_cast<const float*>(pU + k128_off(UR, lane, rr + k));
         }
-        const int c0 = 2 * lane, qa = c0 >> 3;
-        float sx = 0.f, sy = 0.f;
-#pragma unroll 1
-        for (int qq = 0; qq < 3; ++qq) {
-          tma::mbar_wait(&bar[B_E2C + qq], ph);
-          float2 acc[8];
-#pragma unroll
-          for (int k = 0; k < 8; ++k) acc[k] = make_float2(0.f, 0.f);
-#pragma unroll
-          for (int rr = 0; rr < 32; rr += 8) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              const float2 v = *reinterpret_cast<const float2*>(pY + mn_atom(32 * qq + rr + k, qa) + (c0 & 7) * 4);
-              acc[k].x += v.x; acc[k].y += v.y;
-            }
-          }
-          mbar_arrive(&bar[B_W3 + qq]);
-          sx += ((acc[0].x + acc[1].x) + (acc[2].x + acc[3].x)) + ((acc[4].x + acc[5].x) + (acc[6].x + acc[7].x));
-          sy += ((acc[0].y + acc[1].y) + (acc[2].y + acc[3].y)) + ((acc[4].y + acc[5].y) + (acc[6].y + acc[7].y));
-        }
-        gb1a += (double)sx; gb1b += (double)sy;
+        gb2 += (double)((f[0] + f[1]) + (f[2] + f[3]));
       }
-      float* out = a.partials + (size_t)blockIdx.x * a.dstride;
-      out[F.ob1 + 2 * lane] = (float)gb1a;
-      out[F.ob1 + 2 * lane + 1] = (float)gb1b;
-      if (lane < m) out[F.ob2 + lane] = (float)gb2;
+      const int c0 = 2 * lane, qa = c0 >> 3;
+      float sx = 0.f, sy = 0.f;
+#pragma unroll 1
+      for (int qq = 0; qq < 3; ++qq) {
+        tma::mbar_wait(&bar[B_E2C + qq], ph);
+        float2 acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int rr = 0; rr < 32; rr += 8) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float2 v = *reinterpret_cast<const float2*>(pY + mn_atom(32 * qq + rr + k, qa) + (c0 & 7) * 4);
+            acc[k].x += v.x; acc[k].y += v.y;
+          }
+        }
+        mbar_arrive(&bar[B_W3 + qq]);
+        sx += ((acc[0].x + acc[1].x) + (acc[2].x + acc[3].x)) + ((acc[4].x + acc[5].x) + (acc[6].x + acc[7].x));
+        sy += ((acc[0].y + acc[1].y) + (acc[2].y + acc[3].y)) + ((acc[4].y + acc[5].y) + (acc[6].y + acc[7].y));
+      }
+      gb1a += (double)sx; gb1b += (double)sy;
     }
+    float* out = a.partials + (size_t)blockIdx.x * a.dstride;
+    out[F.ob1 + 2 * lane] = (float)gb1a;
+    out[F.ob1 + 2 * lane + 1] = (float)gb1b;
+    if (lane < m) out[F.ob2 + lane] = (float)gb2;
   } else {
     // ============ MMA issuer (one elected lane of warp 7) ==========================================================
     const uint32_t ID_FWD = idesc_tf32(128, 64, 0, 0);
@@ -524,7 +495,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
         commit(&bar[B_M2B]);
       }
       __syncwarp();
-      if (!GRAD) continue;
       tma::mbar_wait(&bar[B_E2A], ph);
       fence_after();
       if (elect_one()) {
@@ -589,21 +559,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
         __syncwarp();
       }
     }
-    if (GRAD && WIDE && lane == 0) bulk_wait_all();
+    if (WIDE && lane == 0) bulk_wait_all();
   }
 
   // ---- all tiles done: sums and accumulators -> per-CTA partials ------------------------------------------------------
   {
     int nit = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) ++nit;
-    if (GRAD && nit > 0) tma::mbar_wait(&bar[B_GW0], (nit - 1) & 1);
+    if (nit > 0) tma::mbar_wait(&bar[B_GW0], (nit - 1) & 1);
     fence_after();
     __syncthreads();
     constexpr int SW = 160 + UR + 1;
     float* stage = reinterpret_cast<float*>(sm);          // [128 lanes][SW]: the plane and weight regions are free now
     float* gst = stage + 128 * SW;                        // [96 rows][MJT] d log_std terms of the half-0 threads
     double* dst = reinterpret_cast<double*>(gst + ROWS * MJT);   // [96 rows][2] surrogate, KL
-    if (GRAD && warp < 4 && nit > 0) {
+    if (warp < 4 && nit > 0) {
       const uint32_t tl = tb + ((uint32_t)(32 * warp) << 16);
       float* row = stage + (size_t)tid * SW;
 #pragma unroll 1
@@ -630,11 +600,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
     }
     if ((warp & 3) != 3 && (warp >> 2) == 0) {
       const int r = 32 * (warp & 3) + lane;
-      dst[2 * r] = surr_acc; dst[2 * r + 1] = kl_acc;
-      if (GRAD) {
+      dst[2 * r] = surr_acc; dst[2 * r + 1] = 0.0;
 #pragma unroll
-        for (int j = 0; j < MJT; ++j) gst[r * MJT + j] = gls[j];
-      }
+      for (int j = 0; j < MJT; ++j) gst[r * MJT + j] = gls[j];
     }
     fence_before();
     __syncthreads();
@@ -644,7 +612,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
       a.spartials[2 * blockIdx.x] = s0;
       a.spartials[2 * blockIdx.x + 1] = s1;
     }
-    if (GRAD) {
+    {
       float* out = a.partials + (size_t)blockIdx.x * a.dstride;
       if (tid < m) {
         double s = 0.0;
@@ -677,9 +645,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) pol_tc_kernel(const PolArgs pa) {
   }
 }
 
-template <int MJT, int MODE, bool WIDE>
+template <int MJT, bool WIDE>
 static int launch_one(const PolArgs& pa, int grid, cudaStream_t s) {
-  auto kern = pol_tc_kernel<MJT, MODE, WIDE>;
+  auto kern = pol_tc_kernel<MJT, WIDE>;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Map<MJT>::ALLOC);
@@ -699,11 +667,10 @@ int launch_pol_tc(mjrl_ctx* ctx, Args& a, float* planes, const TcwRegions* wide,
   int grid = (int)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
   if (grid < 1) grid = 1;
   *grid_out = grid;
+  static_assert(MODE == M_GRAD, "pol_tc.cu holds the gradient pass; the evaluation is launch_pol_fwd (pol_fwd.cu)");
   a.dstride = (F.d + 31) & ~31;
-  if (MODE == M_GRAD) {
-    a.partials = (float*)mjrl_scratch(ctx, sizeof(float) * (size_t)grid * a.dstride);
-    if (!a.partials) return MJRL_E_STATE;
-  }
+  a.partials = (float*)mjrl_scratch(ctx, sizeof(float) * (size_t)grid * a.dstride);
+  if (!a.partials) return MJRL_E_STATE;
   a.spartials = (double*)mjrl_scratch2(ctx, sizeof(double) * 2 * grid);
   if (!a.spartials) return MJRL_E_STATE;
   ptc::PolArgs pa;
@@ -732,15 +699,15 @@ int launch_pol_tc(mjrl_ctx* ctx, Args& a, float* planes, const TcwRegions* wide,
   if (wide) {
     rc = launch_tcw_l0_fwd(ctx, *wide, a.params, a.N, a.n, a.m, grid, nullptr, s);
     if (rc) return rc;
-    if (a.m <= 8) rc = ptc::launch_one<8, MODE, true>(pa, grid, s);
-    else if (a.m <= 16) rc = ptc::launch_one<16, MODE, true>(pa, grid, s);
-    else rc = ptc::launch_one<24, MODE, true>(pa, grid, s);
+    if (a.m <= 8) rc = ptc::launch_one<8, true>(pa, grid, s);
+    else if (a.m <= 16) rc = ptc::launch_one<16, true>(pa, grid, s);
+    else rc = ptc::launch_one<24, true>(pa, grid, s);
     if (rc) return rc;
-    if (MODE == M_GRAD) rc = launch_tcw_l0_grad(ctx, *wide, a.partials, a.dstride, a.N, a.n, a.m, grid, nullptr, s);
+    rc = launch_tcw_l0_grad(ctx, *wide, a.partials, a.dstride, a.N, a.n, a.m, grid, nullptr, s);
     return rc;
   }
-  if (a.m <= 4) return ptc::launch_one<4, MODE, false>(pa, grid, s);
-  return ptc::launch_one<8, MODE, false>(pa, grid, s);
+  if (a.m <= 4) return ptc::launch_one<4, false>(pa, grid, s);
+  return ptc::launch_one<8, false>(pa, grid, s);
 }
 
 template int launch_pol_tc<M_GRAD>(mjrl_ctx*, Args&, float*, const TcwRegions*, int*, cudaStream_t);
